@@ -1,0 +1,130 @@
+/*
+ * srag_b200.h — C ABI of the B200 hybrid-retrieval kernels (libsrag_b200.so).
+ *
+ * The reference (promoteAI/super-rag, 100% Python) has no FFI; each entry point below
+ * names the reference interface whose arithmetic it replaces. Paths are relative to the
+ * reference root. INTEGRATION.md shows the ctypes binding a maintainer would add.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller (a torch.Tensor's data_ptr())
+ *     unless the name ends in _host; the library never allocates or frees caller-visible
+ *     memory; scratch space is a caller-provided workspace sized by *_workspace_bytes();
+ *   - `stream` is a cudaStream_t passed as void*; launches are asynchronous with respect
+ *     to the host, the caller synchronises;
+ *   - return value: 0 = ok, negative = error (SRAG_E_*); srag_last_error() gives the text
+ *     for the calling thread. No exceptions cross the boundary;
+ *   - ordering everywhere: score descending, id ascending on ties (north_star);
+ *   - empty result slots are (score = -inf, id = -1).
+ */
+#ifndef SRAG_B200_H
+#define SRAG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRAG_ABI_VERSION 1
+
+#define SRAG_OK              0
+#define SRAG_E_INVALID      -1   /* bad argument (null pointer, size, alignment, k) */
+#define SRAG_E_CUDA         -2   /* a CUDA runtime / driver call failed */
+#define SRAG_E_WORKSPACE    -3   /* workspace too small */
+#define SRAG_E_UNSUPPORTED  -4   /* device is not sm_100 or driver lacks a needed entry point */
+
+#define SRAG_METRIC_COSINE 0     /* seekdb_connector.py:38  distance="cosine" */
+#define SRAG_METRIC_IP     1
+
+#define SRAG_FUSE_RRF      0     /* graphiti_core/search/search_utils.py:1763-1778 */
+#define SRAG_FUSE_WEIGHTED 1
+
+#define SRAG_MAX_TOPK      128   /* k <= 128 for vector search */
+#define SRAG_MAX_BM25_K    256
+#define SRAG_MAX_LISTS     8     /* fused lists */
+
+int         srag_abi_version(void);
+const char* srag_last_error(void);
+/* sm count, compute capability of the current device */
+int         srag_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- K0: ingest -------------------------------------------------------------------
+ * Replaces the server side of `collection.add(ids, embeddings=...)`
+ * (super_rag/vectorstore/seekdb_connector.py:68-85): cast fp32 rows to bf16 and compute the
+ * per-row score multiplier (1/|row| of the bf16-ROUNDED row for cosine, 0 for a zero row —
+ * graphiti_core/search/search_utils.py:63-64; 1.0 for ip).
+ *   src_f32  [n, dim] fp32      dst_bf16 [n, dim] bf16      scale [n] fp32            */
+int srag_rows_ingest_f32(const float* src_f32, int64_t n, int dim, void* dst_bf16,
+                         float* scale, int metric, void* stream);
+/* same, for rows that are already bf16 */
+int srag_rows_scale_bf16(const void* rows_bf16, int64_t n, int dim, float* scale,
+                         int metric, void* stream);
+
+/* ---- K1: exact top-k vector search --------------------------------------------------
+ * Replaces `collection.query(query_embeddings, n_results)` called at
+ * super_rag/vectorstore/seekdb_connector.py:103-107 (one query) with a batched exact scan:
+ *   score[b, r] = (q_b . c_r) * q_scale[b] * row_scale[r]
+ * computed as a tcgen05 bf16 GEMM with fp32 accumulation in TMEM; scores never reach HBM.
+ * A row whose row_scale is NaN is a tombstone (connector.delete, seekdb_connector.py:90-96)
+ * and is never returned.
+ *   corpus_bf16 [n_rows, dim] bf16 row-major, 16-byte aligned, dim % 8 == 0
+ *   queries_bf16 [n_queries, dim] bf16, same constraints
+ *   out_scores [n_queries, k] fp32, out_ids [n_queries, k] int64 = id_base + row
+ *   1 <= k <= SRAG_MAX_TOPK                                                           */
+int srag_topk_workspace_bytes(int64_t n_rows, int n_queries, int k, size_t* bytes);
+int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                     const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                     int64_t id_base, float* out_scores, int64_t* out_ids,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K2: BM25 -----------------------------------------------------------------------
+ * The `fulltext_search` node the reference declares but does not implement
+ * (super_rag/nodeflow/runners/merge.py:18-20, super_rag/schema/view_models.py:1043-1047).
+ * Index layout (CSR by term): term_ptr int64 [vocab+1]; post_doc int32 [nnz] ascending
+ * inside a term; post_imp fp32 [nnz]. Numeric contract: oracle/bm25.py docstring.
+ *
+ * srag_bm25_impacts: imp = idf[term] * tf*(k1+1) / (tf + k1*(1-b+b*dl/avgdl)), one IEEE
+ * fp32 op per step; the term of posting p is found by bisection in term_ptr.
+ * post_tf int32 [nnz]; idf fp32 [vocab]; dl int32 [n_docs].                                */
+int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32_t* post_doc,
+                      const int32_t* post_tf, int64_t nnz, const float* idf, const int32_t* dl,
+                      float avgdl, float* post_imp, void* stream);
+/* block_ptr int64 [vocab, n_blocks+1]: absolute offset of the first posting of term t whose
+ * doc >= j * block_docs (j = n_blocks gives term_ptr[t+1]).                               */
+int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* post_doc, int vocab,
+                          int64_t n_docs, int block_docs, int64_t* block_ptr, void* stream);
+int srag_bm25_block_docs(void);   /* doc-range width one CTA accumulates in shared memory */
+int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes);
+/* q_terms int32 [n_queries, max_terms]: unique term ids in ASCENDING order, -1 padded.
+ * out_* [n_queries, k]; only documents matching >= 1 term are candidates.               */
+int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,
+                     int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries,
+                     int max_terms, int k, int64_t id_base, float* out_scores, int64_t* out_ids,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K3: fusion ---------------------------------------------------------------------
+ * RRF exactly as graphiti_core/search/search_utils.py:1763-1778 (float64,
+ * score[id] += 1/(i + rank_const), lists accumulated in order, keep score >= min_score) or
+ * weighted fp32 fusion, for the `merge` node (super_rag/nodeflow/runners/merge.py:40-65)
+ * strategies "rrf" / "weighted". Final order (score desc, id asc), cut to k_out.
+ *   ids    int64 [n_lists, n_queries, list_len]  (id < 0 = padding)
+ *   scores fp32  [n_lists, n_queries, list_len]  (may be NULL for RRF)
+ *   weights_host  double[n_lists] on the HOST (NULL for RRF)
+ *   out_ids int64 [n_queries, k_out], out_scores double [n_queries, k_out]
+ *   n_lists <= SRAG_MAX_LISTS, n_lists * list_len <= 2048                               */
+int srag_fuse(const int64_t* ids, const float* scores, int n_lists, int n_queries, int list_len,
+              int mode, int rank_const, double min_score, const double* weights_host,
+              int k_out, int64_t* out_ids, double* out_scores, void* stream);
+
+/* ---- K4: cross-shard candidate merge -------------------------------------------------
+ * Final step after the all-gather of per-shard candidates.
+ *   scores fp32 [n_shards, n_queries, kk], ids int64 same shape (id < 0 = padding)
+ *   out_* [n_queries, k];  n_shards * kk <= 2048                                        */
+int srag_merge_candidates(const float* scores, const int64_t* ids, int n_shards, int n_queries,
+                          int kk, int k, float* out_scores, int64_t* out_ids, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRAG_B200_H */

@@ -1,0 +1,318 @@
+// K2: BM25 scoring over CSR postings. HBM-bound integer/float streaming work — no tensor cores.
+//
+//   bm25_block_kernel  grid (doc blocks, queries). A CTA owns one query and one range of
+//                      BM25_BLOCK_DOCS consecutive documents whose fp32 accumulators live in
+//                      shared memory. Query terms are visited in ASCENDING term id; inside a
+//                      term every posting hits a distinct document, so plain (non-atomic)
+//                      read-add-write is race-free and the per-document sum order is fixed ->
+//                      bit-exact with oracle/bm25.py. The CTA then selects its exact top-k with
+//                      an 11/11/10-bit radix select over the accumulator tile (ties -> lowest
+//                      doc id) and writes k sortable keys.
+//   srag_launch_finalize (topk_gemm.cu) merges the per-block lists of a query.
+//
+// Algorithmic bytes per query = 8 * sum_t df(t)  (int32 doc + fp32 impact per posting).
+// The reference has no BM25 arithmetic; contract: oracle/bm25.py docstring.
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM25_BLOCK_DOCS = 16384;  // 64 KB of fp32 accumulators per CTA
+constexpr int BM25_THREADS = 256;
+constexpr int RADIX_BINS = 2048;
+constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots
+
+struct Bm25Smem {
+    float acc[BM25_BLOCK_DOCS];
+    uint32_t hist[RADIX_BINS];
+    uint32_t warp_tmp[BM25_THREADS / 32];
+    uint32_t sel_bin;
+    uint32_t sel_above;
+    uint32_t out_count;
+    uint32_t nonzero;
+};
+
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_tmp, uint32_t* total) {
+    // exclusive prefix sum over the CTA in thread order
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();  // protect warp_tmp reuse
+    if (lane == 31) warp_tmp[w] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int i = 0; i < BM25_THREADS / 32; ++i) {
+        const uint32_t x = warp_tmp[i];
+        if (i < w) base += x;
+        tot += x;
+    }
+    *total = tot;
+    return base + inc - v;
+}
+
+// One radix pass: histogram digit (bits >> shift) & mask of the accumulator entries whose bits
+// above this digit equal `prefix` (prefix_mask selects them), then locate the bin in which the
+// `want`-th largest such entry falls. Returns through smem: sel_bin, sel_above (# in higher bins).
+__device__ void radix_pass(Bm25Smem* sm, uint32_t prefix, uint32_t prefix_mask, int shift, uint32_t mask,
+                           uint32_t want) {
+    for (int i = threadIdx.x; i < RADIX_BINS; i += BM25_THREADS) sm->hist[i] = 0;
+    __syncthreads();
+    const float4* a4 = reinterpret_cast<const float4*>(sm->acc);
+    for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+        const float4 v = a4[i];
+        const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (b[j] != 0 && (b[j] & prefix_mask) == prefix) atomicAdd(&sm->hist[(b[j] >> shift) & mask], 1u);
+    }
+    __syncthreads();
+    // suffix scan from the top bin: thread t owns bins [2047 - 8t - 7, 2047 - 8t]
+    constexpr int PER = RADIX_BINS / BM25_THREADS;
+    uint32_t mine = 0;
+    const int top = RADIX_BINS - 1 - threadIdx.x * PER;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) mine += sm->hist[top - i];
+    uint32_t total;
+    const uint32_t above = block_excl_scan(mine, sm->warp_tmp, &total);
+    if (above < want && above + mine >= want) {
+        uint32_t run = above;
+        for (int i = 0; i < PER; ++i) {
+            const uint32_t h = sm->hist[top - i];
+            if (run + h >= want) {
+                sm->sel_bin = (uint32_t)(top - i);
+                sm->sel_above = run;
+                break;
+            }
+            run += h;
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(BM25_THREADS)
+bm25_block_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
+                  const float* __restrict__ post_imp, int n_blocks, int64_t n_docs,
+                  const int32_t* __restrict__ q_terms, int max_terms, int k, int q_offset,
+                  uint64_t* __restrict__ partial /* [q_chunk][n_blocks][k] */) {
+    extern __shared__ uint8_t bm25_smem_raw[];
+    Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
+    const int blk = blockIdx.x;
+    const int ql = blockIdx.y;  // query index inside this chunk
+    const int q = q_offset + ql;
+    const int32_t doc_base = blk * BM25_BLOCK_DOCS;
+
+    float4* a4 = reinterpret_cast<float4*>(sm->acc);
+    for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (threadIdx.x == 0) { sm->out_count = 0; sm->nonzero = 0; }
+    __syncthreads();
+
+    // ---- term-sequential scatter-accumulate ------------------------------------------------
+    const int32_t* terms = q_terms + (size_t)q * max_terms;
+    for (int j = 0; j < max_terms; ++j) {
+        const int32_t t = terms[j];
+        if (t < 0) continue;  // padding (uniform across the CTA)
+        const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk;
+        const int64_t lo = bp[0], hi = bp[1];
+        // 128-bit body over 4-aligned groups, scalar edges
+        const int64_t g0 = lo & ~(int64_t)3;
+        for (int64_t g = g0 + 4 * (int64_t)threadIdx.x; g < hi; g += 4 * BM25_THREADS) {
+            if (g >= lo && g + 4 <= hi) {
+                const int4 d = __ldg(reinterpret_cast<const int4*>(post_doc + g));
+                const float4 w = __ldg(reinterpret_cast<const float4*>(post_imp + g));
+                float* p0 = &sm->acc[d.x - doc_base];
+                float* p1 = &sm->acc[d.y - doc_base];
+                float* p2 = &sm->acc[d.z - doc_base];
+                float* p3 = &sm->acc[d.w - doc_base];
+                *p0 = __fadd_rn(*p0, w.x);
+                *p1 = __fadd_rn(*p1, w.y);
+                *p2 = __fadd_rn(*p2, w.z);
+                *p3 = __fadd_rn(*p3, w.w);
+            } else {
+                for (int e = 0; e < 4; ++e) {
+                    const int64_t p = g + e;
+                    if (p >= lo && p < hi) {
+                        float* a = &sm->acc[__ldg(post_doc + p) - doc_base];
+                        *a = __fadd_rn(*a, __ldg(post_imp + p));
+                    }
+                }
+            }
+        }
+        __syncthreads();  // next term may touch the same documents
+    }
+
+    // ---- exact block top-k -------------------------------------------------------------------
+    // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
+    uint32_t nz = 0;
+    const int s0 = threadIdx.x * SLOTS_PER_THREAD;
+    for (int i = 0; i < SLOTS_PER_THREAD; i += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(&sm->acc[s0 + i]);
+        nz += (v.x != 0.f) + (v.y != 0.f) + (v.z != 0.f) + (v.w != 0.f);
+    }
+    uint32_t total_nz;
+    (void)block_excl_scan(nz, sm->warp_tmp, &total_nz);
+    uint64_t* out = partial + ((size_t)ql * n_blocks + blk) * k;
+    if (total_nz == 0) return;  // partial is pre-zeroed (= empty keys)
+
+    uint32_t thr_bits = 0;      // k-th largest value; everything above it is taken
+    uint32_t need_eq = 0xFFFFFFFFu;  // how many entries == thr_bits to take (lowest doc ids first)
+    if (total_nz > (uint32_t)k) {
+        radix_pass(sm, 0u, 0u, 21, 0x7FFu, (uint32_t)k);
+        const uint32_t b1 = sm->sel_bin, above1 = sm->sel_above;
+        __syncthreads();
+        radix_pass(sm, b1 << 21, 0xFFE00000u, 10, 0x7FFu, (uint32_t)k - above1);
+        const uint32_t b2 = sm->sel_bin, above2 = above1 + sm->sel_above;
+        __syncthreads();
+        radix_pass(sm, (b1 << 21) | (b2 << 10), 0xFFFFFC00u, 0, 0x3FFu, (uint32_t)k - above2);
+        const uint32_t b3 = sm->sel_bin, above3 = above2 + sm->sel_above;
+        __syncthreads();
+        thr_bits = (b1 << 21) | (b2 << 10) | b3;
+        need_eq = (uint32_t)k - above3;
+    }
+    // emit: > thr in any order (finalize sorts), == thr in ascending doc order up to need_eq
+    uint32_t eq = 0;
+    for (int i = 0; i < SLOTS_PER_THREAD; ++i) eq += (__float_as_uint(sm->acc[s0 + i]) == thr_bits && thr_bits != 0);
+    uint32_t eq_total;
+    uint32_t eq_rank = block_excl_scan(eq, sm->warp_tmp, &eq_total);
+    for (int i = 0; i < SLOTS_PER_THREAD; ++i) {
+        const uint32_t b = __float_as_uint(sm->acc[s0 + i]);
+        if (b == 0) continue;
+        bool take = b > thr_bits;
+        if (b == thr_bits) { take = eq_rank < need_eq; ++eq_rank; }
+        if (take) {
+            const uint32_t slot = atomicAdd(&sm->out_count, 1u);
+            if (slot < (uint32_t)k) out[slot] = srag_pack_key(b, (uint32_t)(doc_base + s0 + i));
+        }
+    }
+}
+
+// imp = idf[t] * (tf * (k1 + 1)) / (tf + k1 * ((1 - b) + b * (dl / avgdl))), one rounding per op
+__global__ void bm25_impacts_kernel(const int64_t* __restrict__ term_ptr, int vocab,
+                                    const int32_t* __restrict__ post_doc, const int32_t* __restrict__ post_tf,
+                                    int64_t nnz, const float* __restrict__ idf, const int32_t* __restrict__ dl,
+                                    float avgdl, float* __restrict__ post_imp) {
+    const float k1 = 1.2f, b = 0.75f;
+    const float one_minus_b = __fadd_rn(1.0f, -b);
+    const float k1p1 = __fadd_rn(k1, 1.0f);
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < nnz; p += (int64_t)gridDim.x * blockDim.x) {
+        int lo = 0, hi = vocab;  // largest t with term_ptr[t] <= p
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(term_ptr + mid) <= p) lo = mid; else hi = mid;
+        }
+        const float tf = (float)post_tf[p];
+        const float r = __fdiv_rn((float)dl[post_doc[p]], avgdl);
+        const float t = __fmul_rn(b, r);
+        const float u = __fadd_rn(one_minus_b, t);
+        const float nrm = __fmul_rn(k1, u);
+        const float a = __fmul_rn(tf, k1p1);
+        const float num = __fmul_rn(idf[lo], a);
+        const float den = __fadd_rn(tf, nrm);
+        post_imp[p] = __fdiv_rn(num, den);
+    }
+}
+
+__global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, const int32_t* __restrict__ post_doc,
+                                        int vocab, int n_blocks, int block_docs, int64_t* __restrict__ block_ptr) {
+    const int64_t total = (int64_t)vocab * (n_blocks + 1);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int t = (int)(i / (n_blocks + 1));
+        const int j = (int)(i - (int64_t)t * (n_blocks + 1));
+        int64_t lo = term_ptr[t], hi = term_ptr[t + 1];
+        const int64_t target = (int64_t)j * block_docs;  // first posting with doc >= target
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if ((int64_t)__ldg(post_doc + mid) < target) lo = mid + 1; else hi = mid;
+        }
+        block_ptr[i] = lo;
+    }
+}
+
+int bm25_blocks(int64_t n_docs) { return (int)((n_docs + BM25_BLOCK_DOCS - 1) / BM25_BLOCK_DOCS); }
+constexpr int BM25_Q_CHUNK = 256;  // queries whose per-block lists are resident at once
+
+}  // namespace
+
+extern "C" int srag_bm25_block_docs(void) { return BM25_BLOCK_DOCS; }
+
+extern "C" int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32_t* post_doc, const int32_t* post_tf,
+                                 int64_t nnz, const float* idf, const int32_t* dl, float avgdl, float* post_imp,
+                                 void* stream) {
+    SRAG_CHECK_ARG(nnz >= 0 && vocab >= 1 && avgdl > 0.f, "bad sizes nnz=%lld vocab=%d avgdl=%f", (long long)nnz,
+                   vocab, (double)avgdl);
+    if (nnz == 0) return SRAG_OK;
+    SRAG_CHECK_ARG(term_ptr && post_doc && post_tf && idf && dl && post_imp, "null pointer argument");
+    int64_t blocks = (nnz + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    bm25_impacts_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        term_ptr, vocab, post_doc, post_tf, nnz, idf, dl, avgdl, post_imp);
+    SRAG_CUDA(cudaGetLastError());
+    return SRAG_OK;
+}
+
+extern "C" int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* post_doc, int vocab, int64_t n_docs,
+                                     int block_docs, int64_t* block_ptr, void* stream) {
+    SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF && block_docs == BM25_BLOCK_DOCS,
+                   "bad sizes vocab=%d n_docs=%lld block_docs=%d", vocab, (long long)n_docs, block_docs);
+    SRAG_CHECK_ARG(term_ptr && block_ptr, "null pointer argument");
+    const int nb = bm25_blocks(n_docs);
+    int64_t total = (int64_t)vocab * (nb + 1);
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    bm25_block_index_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        term_ptr, post_doc, vocab, nb, block_docs, block_ptr);
+    SRAG_CUDA(cudaGetLastError());
+    return SRAG_OK;
+}
+
+extern "C" int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes) {
+    SRAG_CHECK_ARG(bytes && n_queries >= 1 && k >= 1 && k <= SRAG_MAX_BM25_K && n_docs >= 0, "bad sizes");
+    const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
+    const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
+    *bytes = (size_t)qc * nb * k * sizeof(uint64_t) + 256;
+    return SRAG_OK;
+}
+
+extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp, int vocab,
+                                int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms, int k,
+                                int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+    SRAG_CHECK_ARG(n_queries >= 1 && max_terms >= 1 && k >= 1 && k <= SRAG_MAX_BM25_K, "bad sizes n_queries=%d k=%d",
+                   n_queries, k);
+    SRAG_CHECK_ARG(n_docs >= 0 && n_docs < 0x7FFFFFFF && vocab >= 1, "bad index sizes");
+    SRAG_CHECK_ARG(block_ptr && q_terms && out_scores && out_ids && workspace, "null pointer argument");
+    SRAG_CHECK_ARG(n_docs == 0 || (post_doc && post_imp), "null postings");
+    SRAG_CHECK_ARG(((uintptr_t)post_doc & 15) == 0 && ((uintptr_t)post_imp & 15) == 0 && ((uintptr_t)workspace & 15) == 0,
+                   "postings / workspace must be 16-byte aligned");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
+    const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
+    const size_t need = (size_t)qc * nb * k * sizeof(uint64_t);
+    if (workspace_bytes < need) {
+        srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
+        return SRAG_E_WORKSPACE;
+    }
+    static bool attr_done = false;
+    if (!attr_done) {
+        SRAG_CUDA(cudaFuncSetAttribute(bm25_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(Bm25Smem)));
+        attr_done = true;
+    }
+    uint64_t* partial = reinterpret_cast<uint64_t*>(workspace);
+    for (int q0 = 0; q0 < n_queries; q0 += qc) {
+        const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
+        SRAG_CUDA(cudaMemsetAsync(partial, 0, (size_t)nq * nb * k * sizeof(uint64_t), st));
+        if (n_docs > 0) {
+            bm25_block_kernel<<<dim3(nb, nq), BM25_THREADS, sizeof(Bm25Smem), st>>>(
+                block_ptr, post_doc, post_imp, nb, n_docs, q_terms, max_terms, k, q0, partial);
+            SRAG_CUDA(cudaGetLastError());
+        }
+        int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, id_base, out_scores + (size_t)q0 * k,
+                                      out_ids + (size_t)q0 * k, st);
+        if (rc) return rc;
+    }
+    return SRAG_OK;
+}

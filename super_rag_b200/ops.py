@@ -1,0 +1,198 @@
+"""Thin torch-tensor front end of the C ABI (include/srag_b200.h). PyTorch supplies device
+memory and streams only; every computation below is a libsrag_b200 kernel. No CPU fallback:
+tensors must be CUDA tensors and failures raise ``SragError``."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import SragError
+
+METRIC_COSINE, METRIC_IP = 0, 1
+FUSE_RRF, FUSE_WEIGHTED = 0, 1
+MAX_TOPK, MAX_BM25_K, MAX_LISTS = 128, 256, 8
+# one srag_topk_search launch handles at most (SMs/2) query tiles of 256; chunk above this
+MAX_QUERIES_PER_CALL = 2048
+
+
+def metric_code(metric) -> int:
+    if metric in (METRIC_COSINE, "cosine"):
+        return METRIC_COSINE
+    if metric in (METRIC_IP, "ip", "inner_product", "dot"):
+        return METRIC_IP
+    raise ValueError(f"unsupported distance {metric!r} (cosine | ip)")
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise SragError("libsrag_b200 operates on CUDA tensors only (no CPU fallback)")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def device_info() -> Tuple[int, int, int]:
+    lib = _lib.load()
+    a, b, c = C.c_int(), C.c_int(), C.c_int()
+    _lib.check(lib.srag_device_info(C.byref(a), C.byref(b), C.byref(c)), "srag_device_info")
+    return a.value, b.value, c.value
+
+
+# ---- K0 ---------------------------------------------------------------------------------
+def ingest_rows(rows: torch.Tensor, metric=METRIC_COSINE, out_bf16: Optional[torch.Tensor] = None,
+                out_scale: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """fp32 (cast + multiplier) or bf16 (multiplier only) rows -> (bf16 rows, fp32 row multipliers)."""
+    _need_cuda(rows)
+    lib = _lib.load()
+    rows = rows.contiguous()
+    n, dim = rows.shape
+    m = metric_code(metric)
+    with torch.cuda.device(rows.device):
+        scale = out_scale if out_scale is not None else torch.empty(n, dtype=torch.float32, device=rows.device)
+        if rows.dtype == torch.bfloat16:
+            _lib.check(lib.srag_rows_scale_bf16(_ptr(rows), n, dim, _ptr(scale), m, _stream(rows.device)),
+                       "srag_rows_scale_bf16")
+            if out_bf16 is not None:
+                out_bf16.copy_(rows)
+                return out_bf16, scale
+            return rows, scale
+        if rows.dtype != torch.float32:
+            raise SragError(f"rows must be float32 or bfloat16, got {rows.dtype}")
+        dst = out_bf16 if out_bf16 is not None else torch.empty(n, dim, dtype=torch.bfloat16, device=rows.device)
+        _lib.check(lib.srag_rows_ingest_f32(_ptr(rows), n, dim, _ptr(dst), _ptr(scale), m, _stream(rows.device)),
+                   "srag_rows_ingest_f32")
+    return dst, scale
+
+
+# ---- K1 ---------------------------------------------------------------------------------
+def topk_workspace_bytes(n_rows: int, n_queries: int, k: int) -> int:
+    lib = _lib.load()
+    out = C.c_size_t()
+    _lib.check(lib.srag_topk_workspace_bytes(n_rows, n_queries, k, C.byref(out)), "srag_topk_workspace_bytes")
+    return out.value
+
+
+def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Tensor, q_scale: torch.Tensor,
+                k: int, id_base: int = 0, workspace: Optional[torch.Tensor] = None,
+                out_scores: Optional[torch.Tensor] = None, out_ids: Optional[torch.Tensor] = None):
+    """Exact top-k of bf16 queries [B,D] against a bf16 corpus [N,D]; returns (scores fp32 [B,k], ids int64 [B,k])."""
+    _need_cuda(corpus, row_scale, queries, q_scale)
+    if corpus.dtype != torch.bfloat16 or queries.dtype != torch.bfloat16:
+        raise SragError("corpus and queries must be bfloat16 (use ingest_rows)")
+    lib = _lib.load()
+    B, D = queries.shape
+    N = corpus.shape[0]
+    if N and corpus.shape[1] != D:
+        raise SragError(f"dimension mismatch: corpus {tuple(corpus.shape)} vs queries {tuple(queries.shape)}")
+    dev = queries.device
+    with torch.cuda.device(dev):
+        scores = out_scores if out_scores is not None else torch.empty(B, k, dtype=torch.float32, device=dev)
+        ids = out_ids if out_ids is not None else torch.empty(B, k, dtype=torch.int64, device=dev)
+        for b0 in range(0, B, MAX_QUERIES_PER_CALL):
+            nb = min(MAX_QUERIES_PER_CALL, B - b0)
+            need = topk_workspace_bytes(N, nb, k)
+            if workspace is None or workspace.numel() < need:
+                workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+            q = queries[b0:b0 + nb]
+            _lib.check(lib.srag_topk_search(_ptr(corpus), _ptr(row_scale), N, D, _ptr(q), _ptr(q_scale[b0:b0 + nb]),
+                                            nb, k, id_base, _ptr(scores[b0:b0 + nb]), _ptr(ids[b0:b0 + nb]),
+                                            _ptr(workspace), workspace.numel(), _stream(dev)), "srag_topk_search")
+    return scores, ids
+
+
+# ---- K2 ---------------------------------------------------------------------------------
+def bm25_block_docs() -> int:
+    return _lib.load().srag_bm25_block_docs()
+
+
+def bm25_impacts(term_ptr, post_doc, post_tf, idf, dl, avgdl: float) -> torch.Tensor:
+    _need_cuda(term_ptr, post_doc, post_tf, idf, dl)
+    lib = _lib.load()
+    nnz = post_doc.numel()
+    dev = post_doc.device
+    with torch.cuda.device(dev):
+        imp = torch.empty(nnz + 4, dtype=torch.float32, device=dev)[:nnz]
+        _lib.check(lib.srag_bm25_impacts(_ptr(term_ptr), term_ptr.numel() - 1, _ptr(post_doc), _ptr(post_tf), nnz,
+                                         _ptr(idf), _ptr(dl), float(avgdl), _ptr(imp), _stream(dev)),
+                   "srag_bm25_impacts")
+    return imp
+
+
+def bm25_block_index(term_ptr, post_doc, n_docs: int) -> torch.Tensor:
+    _need_cuda(term_ptr, post_doc)
+    lib = _lib.load()
+    vocab = term_ptr.numel() - 1
+    bd = bm25_block_docs()
+    nb = max(1, (n_docs + bd - 1) // bd)
+    dev = term_ptr.device
+    with torch.cuda.device(dev):
+        bp = torch.empty(vocab, nb + 1, dtype=torch.int64, device=dev)
+        _lib.check(lib.srag_bm25_block_index(_ptr(term_ptr), _ptr(post_doc), vocab, n_docs, bd, _ptr(bp), _stream(dev)),
+                   "srag_bm25_block_index")
+    return bp
+
+
+def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tensor, k: int, id_base: int = 0,
+                workspace: Optional[torch.Tensor] = None):
+    """q_terms int32 [B, T]: unique ascending term ids, -1 padded."""
+    _need_cuda(block_ptr, post_doc, post_imp, q_terms)
+    lib = _lib.load()
+    B, T = q_terms.shape
+    dev = q_terms.device
+    vocab = block_ptr.shape[0]
+    with torch.cuda.device(dev):
+        out = C.c_size_t()
+        _lib.check(lib.srag_bm25_workspace_bytes(n_docs, B, k, C.byref(out)), "srag_bm25_workspace_bytes")
+        if workspace is None or workspace.numel() < out.value:
+            workspace = torch.empty(out.value, dtype=torch.uint8, device=dev)
+        scores = torch.empty(B, k, dtype=torch.float32, device=dev)
+        ids = torch.empty(B, k, dtype=torch.int64, device=dev)
+        _lib.check(lib.srag_bm25_search(_ptr(block_ptr), _ptr(post_doc), _ptr(post_imp), vocab, n_docs,
+                                        _ptr(q_terms.contiguous()), B, T, k, id_base, _ptr(scores), _ptr(ids),
+                                        _ptr(workspace), workspace.numel(), _stream(dev)), "srag_bm25_search")
+    return scores, ids
+
+
+# ---- K3 / K4 ----------------------------------------------------------------------------
+def fuse(ids: torch.Tensor, scores: Optional[torch.Tensor], mode: int, k_out: int, rank_const: int = 1,
+         min_score: float = 0.0, weights: Optional[Sequence[float]] = None):
+    """ids int64 [L, B, K] (id < 0 = padding), scores fp32 [L, B, K] -> (ids int64 [B,k_out], scores f64 [B,k_out])."""
+    _need_cuda(ids, scores)
+    lib = _lib.load()
+    L, B, K = ids.shape
+    dev = ids.device
+    ids = ids.contiguous()
+    if scores is not None:
+        scores = scores.contiguous().to(torch.float32)
+    w = None
+    if weights is not None:
+        w = (C.c_double * L)(*[float(x) for x in weights])
+    with torch.cuda.device(dev):
+        oi = torch.empty(B, k_out, dtype=torch.int64, device=dev)
+        os_ = torch.empty(B, k_out, dtype=torch.float64, device=dev)
+        _lib.check(lib.srag_fuse(_ptr(ids), _ptr(scores), L, B, K, mode, rank_const, float(min_score), w, k_out,
+                                 _ptr(oi), _ptr(os_), _stream(dev)), "srag_fuse")
+    return oi, os_
+
+
+def merge_candidates(scores: torch.Tensor, ids: torch.Tensor, k: int):
+    """scores fp32 [G, B, KK], ids int64 [G, B, KK] -> global top-k (scores [B,k], ids [B,k])."""
+    _need_cuda(scores, ids)
+    lib = _lib.load()
+    G, B, KK = ids.shape
+    dev = ids.device
+    with torch.cuda.device(dev):
+        os_ = torch.empty(B, k, dtype=torch.float32, device=dev)
+        oi = torch.empty(B, k, dtype=torch.int64, device=dev)
+        _lib.check(lib.srag_merge_candidates(_ptr(scores.contiguous()), _ptr(ids.contiguous()), G, B, KK, k,
+                                             _ptr(os_), _ptr(oi), _stream(dev)), "srag_merge_candidates")
+    return os_, oi

@@ -1,0 +1,142 @@
+"""K0 + K1 parity on the GPU, through the C ABI (super_rag_b200.ops -> libsrag_b200.so)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from parity import TIGHT, TOL, check_topk_against_full_scores
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(C32, Q32, k, metric="cosine", cta_group=None, deleted=None, id_base=0):
+    import torch
+    from super_rag_b200 import ops
+    if cta_group is None:
+        os.environ.pop("SRAG_TOPK_CTA_GROUP", None)
+    else:
+        os.environ["SRAG_TOPK_CTA_GROUP"] = str(cta_group)
+    dev = torch.device("cuda:0")
+    c = torch.from_numpy(C32).to(dev)
+    q = torch.from_numpy(Q32).to(dev)
+    cb, cs = ops.ingest_rows(c, metric)
+    qb, qs = ops.ingest_rows(q, metric)
+    if deleted is not None and len(deleted):
+        cs[torch.as_tensor(deleted, device=dev)] = float("nan")
+    s, i = ops.topk_search(cb, cs, qb, qs, k, id_base=id_base)
+    torch.cuda.synchronize()
+    os.environ.pop("SRAG_TOPK_CTA_GROUP", None)
+    return s.cpu().numpy(), i.cpu().numpy(), cb.float().cpu().numpy(), qb.float().cpu().numpy(), cs.cpu().numpy()
+
+
+def _check(C32, Q32, k, metric="cosine", cta_group=None, deleted=None, id_base=0, tight=True):
+    s, i, cr, qr, cs = _run(C32, Q32, k, metric, cta_group, deleted, id_base)
+    assert (cr == oracle.bf16_round(C32)).all() and (qr == oracle.bf16_round(Q32)).all(), "bf16 cast differs"
+    full = oracle.exact_topk_scores_f64(cr, qr, metric)
+    valid = None
+    if deleted is not None and len(deleted):
+        valid = np.ones(C32.shape[0], bool)
+        valid[np.asarray(deleted)] = False
+    check_topk_against_full_scores(s, i, full, k, TOL, id_base, valid)
+    if tight:
+        check_topk_against_full_scores(s, i, full, k, TIGHT, id_base, valid)
+    # the fp32 oracle itself (blocked BLAS) agrees under the same rule
+    os_, oi = oracle.exact_topk(cr, qr, k, metric, id_base=id_base, valid=valid)
+    same = (oi == i).mean()
+    assert same > 0.98, f"only {same:.3f} of ids equal the fp32 oracle's"
+    return s, i
+
+
+def _data(n, d, b, seed, planted=True):
+    rng = np.random.default_rng(seed)
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    Q = rng.standard_normal((b, d)).astype(np.float32)
+    if planted and n > 0:
+        h = b // 2
+        src = rng.integers(0, n, size=h)
+        Q[:h] = C[src] + 0.1 * rng.standard_normal((h, d)).astype(np.float32)
+    return C, Q
+
+
+def test_ingest_scale_matches_oracle():
+    import torch
+    from super_rag_b200 import ops
+    C, _ = _data(1000, 256, 4, 0)
+    C[3] = 0
+    c = torch.from_numpy(C).cuda()
+    cb, cs = ops.ingest_rows(c, "cosine")
+    cr = cb.float().cpu().numpy()
+    assert (cr == oracle.bf16_round(C)).all()
+    want = oracle.row_scales(cr, "cosine")
+    got = cs.cpu().numpy()
+    assert got[3] == 0.0
+    assert np.allclose(got, want, rtol=2e-6, atol=0)
+    _, cs2 = ops.ingest_rows(cb, "cosine")           # bf16 source path
+    assert np.allclose(cs2.cpu().numpy(), want, rtol=2e-6, atol=0)
+    _, ci = ops.ingest_rows(c, "ip")
+    assert (ci.cpu().numpy() == 1.0).all()
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+def test_small_edge_cases(cta_group):
+    C, Q = _data(3000, 64, 8, 1)
+    C[17] = 0.0                 # zero-norm row scores 0
+    C[2000] = C[5]              # exact duplicate -> tie broken by id
+    Q[0] = C[5] * 2.0
+    Q[7] = 0.0                  # zero query: all scores 0, ids ascending
+    s, i = _check(C, Q, 7, cta_group=cta_group)
+    assert i[0, 0] == 5 and i[0, 1] == 2000
+    assert (s[7] == 0).all() and i[7].tolist() == list(range(7))
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("n,d,b,k", [(5000, 1024, 100, 10), (777, 200, 3, 5), (256, 64, 1, 1),
+                                      (40000, 1024, 130, 100), (1000, 128, 260, 128)])
+def test_parity_shapes(n, d, b, k, cta_group):
+    C, Q = _data(n, d, b, n + d + b)
+    _check(C, Q, k, cta_group=cta_group)
+
+
+def test_auto_group_large_batch():
+    C, Q = _data(30000, 1024, 1024, 5)
+    _check(C, Q, 10)
+
+
+def test_inner_product_and_id_base():
+    C, Q = _data(4000, 256, 20, 9)
+    _check(C, Q, 10, metric="ip", id_base=1_000_000_000_000, tight=False)
+
+
+def test_tombstones_and_short_corpus():
+    C, Q = _data(600, 64, 5, 11)
+    deleted = [0, 5, 17, 599]
+    Q[0] = C[5]
+    s, i = _check(C, Q, 10, deleted=deleted)
+    assert not set(i.reshape(-1).tolist()) & set(deleted)
+    C2, Q2 = _data(6, 64, 3, 12)
+    s, i = _check(C2, Q2, 10)       # N < k -> padded with (-inf, -1)
+    assert (i[:, 6:] == -1).all() and np.isinf(s[:, 6:]).all()
+
+
+def test_many_duplicates_tie_by_id():
+    rng = np.random.default_rng(3)
+    base = rng.standard_normal((50, 128)).astype(np.float32)
+    C = np.tile(base, (40, 1))                     # every row appears 40 times
+    Q = base[:10].copy()
+    s, i = _check(C, Q, 64)
+    for b in range(10):
+        assert i[b, :40].tolist() == [b + 50 * j for j in range(40)]
+
+
+def test_bad_arguments_raise():
+    import torch
+    from super_rag_b200 import ops, SragError
+    c = torch.zeros(10, 64, device="cuda", dtype=torch.bfloat16)
+    s = torch.ones(10, device="cuda")
+    with pytest.raises(SragError):
+        ops.topk_search(c, s, c[:2], s[:2], 129)
+    with pytest.raises(SragError):
+        ops.topk_search(c.cpu(), s, c[:2], s[:2], 5)
+    with pytest.raises(SragError):
+        ops.topk_search(c, s, torch.zeros(2, 32, device="cuda", dtype=torch.bfloat16), s[:2], 5)
