@@ -1,0 +1,132 @@
+"""BM25 inverted index resident in HBM + search through K2 (csrc/bm25.cu).
+
+The reference declares a ``fulltext_search`` recall but ships no implementation
+(super_rag/nodeflow/runners/merge.py:18-20; super_rag/schema/view_models.py:1043-1047;
+docs/design/nodeflow/nodeflow.md:83 names "BM25"). Layout and numeric contract are in
+include/srag_b200.h and DESIGN.md §4.2.
+
+Host logic here is limited to: collection statistics (df, avgdl, idf in float64 -> fp32, as the
+contract requires), sorting tokens into CSR postings with torch device ops, and shaping query
+term lists. Scoring, impacts, block index and top-k are CUDA kernels.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Iterable, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import ops
+
+
+def idf_from_df(df: np.ndarray, n_docs: int) -> np.ndarray:
+    """idf(t) = ln(1 + (N - df + 0.5)/(df + 0.5)), float64 then ONE rounding to fp32."""
+    df = np.asarray(df, dtype=np.float64)
+    return np.log(1.0 + (float(n_docs) - df + 0.5) / (df + 0.5)).astype(np.float32)
+
+
+def prepare_query_terms(queries: Sequence[Iterable[int]], vocab: int, max_terms: Optional[int] = None) -> np.ndarray:
+    """Unique, in-vocabulary term ids per query in ascending order, -1 padded: int32 [B, T]."""
+    cleaned = [sorted({int(t) for t in q if 0 <= int(t) < vocab}) for q in queries]
+    width = max([len(c) for c in cleaned] + [1])
+    if max_terms is not None:
+        if width > max_terms:
+            raise ValueError(f"a query has {width} unique terms > max_terms={max_terms}")
+        width = max_terms
+    out = np.full((len(cleaned), width), -1, dtype=np.int32)
+    for b, c in enumerate(cleaned):
+        out[b, :len(c)] = c
+    return out
+
+
+@dataclass
+class Bm25Stats:
+    """Collection statistics; pass the GLOBAL ones to every doc-range shard."""
+    n_docs: int
+    df: np.ndarray          # int64 [vocab]
+    avgdl: float            # float32(sum(dl) / n_docs), division in float64
+
+
+class Bm25Index:
+    """CSR-by-term postings (int32 doc, fp32 impact) + per-term doc-block offsets, all on one GPU."""
+
+    def __init__(self, term_ptr, post_doc, post_imp, block_ptr, n_docs: int, vocab: int, dl, stats: Bm25Stats,
+                 id_base: int = 0):
+        self.term_ptr, self.post_doc, self.post_imp, self.block_ptr = term_ptr, post_doc, post_imp, block_ptr
+        self.n_docs, self.vocab, self.dl, self.stats, self.id_base = n_docs, vocab, dl, stats, id_base
+        self._ws = None
+
+    @property
+    def nnz(self) -> int:
+        return int(self.post_doc.numel())
+
+    @property
+    def device(self):
+        return self.post_doc.device
+
+    # ---- build -----------------------------------------------------------------------------
+    @staticmethod
+    def postings_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int):
+        """Sort (term, doc) pairs on the device -> (term_ptr int64 [V+1], post_doc int32, post_tf int32, dl int32)."""
+        dev = tokens.device
+        n_docs = doc_ptr.numel() - 1
+        dl = (doc_ptr[1:] - doc_ptr[:-1]).to(torch.int32)
+        doc_of_tok = torch.repeat_interleave(torch.arange(n_docs, device=dev, dtype=torch.int64), dl.to(torch.int64))
+        key = tokens.to(torch.int64) * n_docs + doc_of_tok
+        key, _ = torch.sort(key)
+        uniq, counts = torch.unique_consecutive(key, return_counts=True)
+        term = torch.div(uniq, n_docs, rounding_mode="floor")
+        post_doc = (uniq - term * n_docs).to(torch.int32)
+        df = torch.bincount(term, minlength=vocab)
+        term_ptr = torch.zeros(vocab + 1, dtype=torch.int64, device=dev)
+        term_ptr[1:] = torch.cumsum(df, 0)
+        return term_ptr, post_doc, counts.to(torch.int32), dl
+
+    @classmethod
+    def from_postings(cls, term_ptr, post_doc, post_tf, dl, stats: Optional[Bm25Stats] = None, id_base: int = 0):
+        dev = post_doc.device
+        vocab = term_ptr.numel() - 1
+        n_docs = dl.numel()
+        if stats is None:
+            df = (term_ptr[1:] - term_ptr[:-1]).cpu().numpy().astype(np.int64)
+            total = float(dl.to(torch.int64).sum().item())
+            stats = Bm25Stats(n_docs=n_docs, df=df, avgdl=float(np.float32(total / max(1, n_docs))))
+        idf = torch.from_numpy(idf_from_df(stats.df, stats.n_docs)).to(dev)
+        # keep the postings 16-byte aligned and padded so 128-bit loads never leave the buffer
+        nnz = post_doc.numel()
+        pd = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)
+        pd[:nnz] = post_doc
+        post_doc = pd[:nnz]
+        imp = ops.bm25_impacts(term_ptr, post_doc, post_tf, idf, dl, stats.avgdl)
+        block_ptr = ops.bm25_block_index(term_ptr, post_doc, n_docs)
+        return cls(term_ptr, post_doc, imp, block_ptr, n_docs, vocab, dl, stats, id_base)
+
+    @classmethod
+    def from_tokens(cls, tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int, stats: Optional[Bm25Stats] = None,
+                    id_base: int = 0):
+        term_ptr, post_doc, post_tf, dl = cls.postings_from_tokens(tokens, doc_ptr, vocab)
+        return cls.from_postings(term_ptr, post_doc, post_tf, dl, stats, id_base)
+
+    # ---- search ----------------------------------------------------------------------------
+    def search_terms(self, q_terms: torch.Tensor, k: int):
+        """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids)."""
+        if self._ws is None:
+            self._ws = torch.empty(0, dtype=torch.uint8, device=self.device)
+        B = q_terms.shape[0]
+        need = 256 * max(1, -(-self.n_docs // ops.bm25_block_docs())) * k * 8 + 256
+        if self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return ops.bm25_search(self.block_ptr, self.post_doc, self.post_imp, self.n_docs, q_terms, k,
+                               id_base=self.id_base, workspace=self._ws)
+
+    def search(self, queries: Sequence[Iterable[int]], k: int):
+        qt = torch.from_numpy(prepare_query_terms(queries, self.vocab)).to(self.device)
+        return self.search_terms(qt, k)
+
+    def query_posting_bytes(self, q_terms: torch.Tensor) -> int:
+        """Algorithmic bytes of a batch: 8 B per posting of every query term."""
+        df = (self.term_ptr[1:] - self.term_ptr[:-1])
+        t = q_terms.to(torch.int64)
+        m = t >= 0
+        return int(df[t.clamp(min=0)][m].sum().item()) * 8

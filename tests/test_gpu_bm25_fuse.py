@@ -1,0 +1,159 @@
+"""K2 (BM25), K3 (fusion) and K4 (shard merge) parity on the GPU through the C ABI. Bit-exact."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def zipf_corpus(n_docs, vocab, mean_len, seed, s=1.0):
+    rng = np.random.default_rng(seed)
+    dl = np.clip(np.round(rng.normal(mean_len, mean_len / 10, n_docs)), 1, 2 * mean_len).astype(np.int64)
+    p = 1.0 / np.arange(1, vocab + 1) ** s
+    p /= p.sum()
+    tokens = rng.choice(vocab, size=int(dl.sum()), p=p).astype(np.int64)
+    doc_ptr = np.zeros(n_docs + 1, dtype=np.int64)
+    np.cumsum(dl, out=doc_ptr[1:])
+    return tokens, doc_ptr
+
+
+def _build(tokens, doc_ptr, vocab):
+    import torch
+    from super_rag_b200.bm25 import Bm25Index
+    idx = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
+    tp, pd, ptf, dl = oracle.build_postings(tokens, doc_ptr, vocab)
+    imp = oracle.bm25_impacts(tp, pd, ptf, dl)
+    return idx, (tp, pd, ptf, dl, imp)
+
+
+@pytest.mark.parametrize("n_docs,vocab,mean_len,k", [(50_000, 5000, 100, 100), (20_000, 300, 40, 10), (3000, 50, 20, 256)])
+def test_bm25_bit_exact(n_docs, vocab, mean_len, k):
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, mean_len, seed=n_docs)
+    idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    assert (idx.term_ptr.cpu().numpy() == tp).all()
+    assert (idx.post_doc.cpu().numpy() == pd).all()
+    assert (idx.post_imp.cpu().numpy().view(np.uint32) == imp.view(np.uint32)).all(), "impacts not bit-exact"
+    rng = np.random.default_rng(4)
+    queries = [rng.integers(0, vocab, size=int(rng.integers(1, 9))).tolist() for _ in range(40)]
+    queries += [[0], [vocab - 1], [], [0, 1, 2, 3, 4, 5, 6, 7], [5, 5, 5, -3, vocab + 10]]
+    s, i = idx.search(queries, k)
+    os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, k)
+    assert (i.cpu().numpy() == oi).all()
+    assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all()
+
+
+def test_bm25_massive_ties_lowest_doc_id_wins():
+    # every doc is the same single token -> identical impacts everywhere
+    n_docs, vocab = 40_000, 8
+    tokens = np.zeros(n_docs * 3, dtype=np.int64)
+    tokens[1::3] = 1
+    doc_ptr = np.arange(0, 3 * n_docs + 1, 3, dtype=np.int64)
+    idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    s, i = idx.search([[0], [0, 1], [2]], 100)
+    os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, [[0], [0, 1], [2]], 100)
+    assert (i.cpu().numpy() == oi).all() and i[0].tolist() == list(range(100))
+    assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all()
+    assert (i[2].cpu().numpy() == -1).all()
+
+
+def test_bm25_shard_uses_global_stats():
+    """Doc-range shards with GLOBAL df/N/avgdl give the single-index scores bit for bit."""
+    import torch
+    from super_rag_b200.bm25 import Bm25Index, Bm25Stats
+    from super_rag_b200 import ops
+    n_docs, vocab = 30_000, 1000
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, 60, seed=77)
+    full, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    stats = Bm25Stats(n_docs=n_docs, df=np.diff(tp), avgdl=float(oracle.bm25.bm25_avgdl(dl)))
+    queries = [[3, 17, 256], [0, 1], [999, 500, 12, 7]]
+    k = 20
+    parts_s, parts_i = [], []
+    half = n_docs // 2
+    for lo, hi in [(0, half), (half, n_docs)]:
+        t = torch.from_numpy(tokens[doc_ptr[lo]:doc_ptr[hi]]).cuda()
+        dp = torch.from_numpy(doc_ptr[lo:hi + 1] - doc_ptr[lo]).cuda()
+        shard = Bm25Index.from_tokens(t, dp, vocab, stats=stats, id_base=lo)
+        s, i = shard.search(queries, k)
+        parts_s.append(s)
+        parts_i.append(i)
+    ms, mi = ops.merge_candidates(torch.stack(parts_s), torch.stack(parts_i), k)
+    fs, fi = full.search(queries, k)
+    assert (mi == fi).all() and (ms.view(torch.int32) == fs.view(torch.int32)).all()
+    os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, k)
+    assert (mi.cpu().numpy() == oi).all()
+
+
+def _pad_lists(lists, width, dtype, fill):
+    out = np.full((len(lists), width), fill, dtype=dtype)
+    for r, l in enumerate(lists):
+        out[r, :len(l)] = l
+    return out
+
+
+def test_rrf_matches_reference_golden(golden):
+    """K3 on the reference's own rrf() outputs (int-id cases of tests/golden/fusion_golden.json)."""
+    import torch
+    from super_rag_b200 import ops
+    n = 0
+    for c in golden["rrf"]:
+        if not c["lists"] or not all(isinstance(x, int) for l in c["lists"] for x in l):
+            continue
+        width = max([len(l) for l in c["lists"]] + [1])
+        ids = torch.from_numpy(_pad_lists(c["lists"], width, np.int64, -1)).cuda()[:, None, :].contiguous()
+        k_out = max(1, len(c["ids"]) + 3)
+        oi, osc = ops.fuse(ids, None, ops.FUSE_RRF, k_out, rank_const=c["rank_const"], min_score=c["min_score"])
+        oi, osc = oi.cpu().numpy()[0], osc.cpu().numpy()[0]
+        m = len(c["ids"])
+        ref = dict(zip(c["ids"], c["scores"]))
+        assert sorted(oi[:m].tolist()) == sorted(c["ids"]) and (oi[m:] == -1).all()
+        assert [ref[i] for i in oi[:m].tolist()] == osc[:m].tolist()          # float64 bit-exact
+        want_i, want_s = oracle.rrf_fuse_topk([np.array(l, dtype=np.int64) for l in c["lists"]],
+                                              c["rank_const"], c["min_score"], k_out)
+        assert oi[:m].tolist() == want_i.tolist()
+        n += 1
+    assert n >= 20
+
+
+def test_fuse_batched_hybrid_shape():
+    """C4 shape: vector top-100 + BM25 top-100 -> top-10, 64 queries, rrf (rank_const 1 and 60) and weighted."""
+    import torch
+    from super_rag_b200 import ops
+    rng = np.random.default_rng(8)
+    B, K = 64, 100
+    a = np.stack([rng.choice(400, K, replace=False) for _ in range(B)]).astype(np.int64)
+    b = np.stack([rng.choice(400, K, replace=False) for _ in range(B)]).astype(np.int64)
+    b[:, 90:] = -1                                                 # ragged second list
+    sa = np.sort(rng.random((B, K)).astype(np.float32))[:, ::-1].copy()
+    sb = np.sort(rng.random((B, K)).astype(np.float32) * 20)[:, ::-1].copy()
+    ids = torch.from_numpy(np.stack([a, b])).cuda()
+    sc = torch.from_numpy(np.stack([sa, sb])).cuda()
+    for rc in (1, 60):
+        oi, osc = ops.fuse(ids, None, ops.FUSE_RRF, 10, rank_const=rc)
+        for q in range(B):
+            wi, ws = oracle.rrf_fuse_topk([a[q], b[q]], rc, 0.0, 10)
+            assert oi[q].cpu().numpy().tolist() == wi.tolist()
+            assert osc[q].cpu().numpy().tolist() == ws.tolist()
+    oi, osc = ops.fuse(ids, sc, ops.FUSE_WEIGHTED, 10, min_score=float("-inf"), weights=[0.7, 0.015])
+    for q in range(B):
+        wi, ws = oracle.weighted_fuse_topk([a[q], b[q]], [sa[q], sb[q]], [0.7, 0.015], 10)
+        assert oi[q].cpu().numpy().tolist() == wi.tolist()
+        assert osc[q].cpu().numpy().astype(np.float32).tolist() == ws.tolist()
+
+
+def test_merge_candidates_matches_oracle():
+    import torch
+    from super_rag_b200 import ops
+    rng = np.random.default_rng(9)
+    G, B, KK = 8, 33, 100
+    s = rng.random((G, B, KK)).astype(np.float32)
+    s[:, :, 50:60] = s[:, :, 40:50]                   # ties across positions
+    s[1] = s[0]                                       # ties across shards
+    i = rng.permutation(G * B * KK).reshape(G, B, KK).astype(np.int64)
+    i[3, :, 90:] = -1
+    ms, mi = ops.merge_candidates(torch.from_numpy(s).cuda(), torch.from_numpy(i).cuda(), 100)
+    ws, wi = oracle.merge_shard_candidates(s, i, 100)
+    assert (mi.cpu().numpy() == wi).all() and (ms.cpu().numpy() == ws).all()
