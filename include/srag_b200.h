@@ -78,6 +78,12 @@ int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_
                      int64_t id_base, float* out_scores, int64_t* out_ids,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* Device-side timing of K1 for roofline reporting: when enabled, srag_topk_search records CUDA
+ * events around its main kernel (memset + fused GEMM/top-k) and its finalize kernel on the
+ * launching stream (up to 256 calls). srag_prof_read waits for them and returns the sums.      */
+int srag_prof_enable(int on);
+int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int* n_calls);
+
 /* ---- K2: BM25 -----------------------------------------------------------------------
  * The `fulltext_search` node the reference declares but does not implement
  * (super_rag/nodeflow/runners/merge.py:18-20, super_rag/schema/view_models.py:1043-1047).

@@ -76,25 +76,14 @@ def row_scales(x: np.ndarray, metric="cosine") -> np.ndarray:
     x = np.asarray(x, dtype=np.float32)
     if _metric_code(metric) == METRIC_IP:
         return np.ones(x.shape[0], dtype=np.float32)
-    n = np.sqrt(np.einsum("ij,ij->i", x.astype(np.float64), x.astype(np.float64)))
+    n = np.empty(x.shape[0], dtype=np.float64)
+    for r0 in range(0, x.shape[0], 65536):                     # bounded fp64 temporaries
+        x64 = x[r0:r0 + 65536].astype(np.float64)
+        n[r0:r0 + 65536] = np.sqrt(np.einsum("ij,ij->i", x64, x64))
     out = np.zeros(x.shape[0], dtype=np.float64)
     nz = n > 0
     out[nz] = 1.0 / n[nz]
     return out.astype(np.float32)
-
-
-def _select_topk_row(scores: np.ndarray, ids: np.ndarray, k: int):
-    """Top-k of one row under (score desc, id asc). scores/ids are 1-D."""
-    n = scores.shape[0]
-    k = min(k, n)
-    if k == 0:
-        return scores[:0], ids[:0]
-    if n > 4 * k + 64:
-        kth = np.partition(scores, n - k)[n - k]
-        keep = scores >= kth  # superset of the answer; ties at kth resolved by the sort
-        scores, ids = scores[keep], ids[keep]
-    order = np.lexsort((ids, -scores.astype(np.float64)))[:k]
-    return scores[order], ids[order]
 
 
 def exact_topk(corpus: np.ndarray, queries: np.ndarray, k: int, metric="cosine",
@@ -111,8 +100,10 @@ def exact_topk(corpus: np.ndarray, queries: np.ndarray, k: int, metric="cosine",
     N = corpus.shape[0]
     mc = _metric_code(metric)
     qs = row_scales(queries, mc)
-    best_s = np.full((B, 0), -np.inf, dtype=np.float32)
-    best_i = np.full((B, 0), -1, dtype=np.int64)
+    # running candidates as flat arrays (query, score, id); reduced to k per query after each block
+    cq = np.zeros(0, dtype=np.int64)
+    cs_ = np.zeros(0, dtype=np.float32)
+    ci = np.zeros(0, dtype=np.int64)
     for r0 in range(0, N, block_rows):
         blk = corpus[r0:r0 + block_rows]
         dots = queries @ blk.T  # fp32 BLAS
@@ -121,31 +112,31 @@ def exact_topk(corpus: np.ndarray, queries: np.ndarray, k: int, metric="cosine",
             s = (dots * cs[None, :]) * qs[:, None]
         else:
             s = dots
-        s = s.astype(np.float32, copy=False)
-        ids = np.arange(r0, r0 + blk.shape[0], dtype=np.int64) + id_base
+        s = np.ascontiguousarray(s, dtype=np.float32)
         if valid is not None:
-            v = valid[r0:r0 + blk.shape[0]]
-            s = s[:, v]
-            ids = ids[v]
-        ns, ni = [], []
-        for b in range(B):
-            cs_, ci_ = _select_topk_row(s[b], ids, k)
-            ms = np.concatenate([best_s[b], cs_])
-            mi = np.concatenate([best_i[b], ci_])
-            o = np.lexsort((mi, -ms.astype(np.float64)))[:k]
-            ns.append(ms[o])
-            ni.append(mi[o])
-        w = max(len(x) for x in ns) if ns else 0
-        best_s = np.full((B, w), -np.inf, dtype=np.float32)
-        best_i = np.full((B, w), -1, dtype=np.int64)
-        for b in range(B):
-            best_s[b, :len(ns[b])] = ns[b]
-            best_i[b, :len(ni[b])] = ni[b]
+            s[:, ~valid[r0:r0 + blk.shape[0]]] = -np.inf
+        n = s.shape[1]
+        kk = min(k, n)
+        kth = np.partition(s, n - kk, axis=1)[:, n - kk]      # k-th largest of each row
+        rows, cols = np.nonzero(s >= kth[:, None])             # superset incl. ties at the k-th
+        sc = s[rows, cols]
+        keep = np.isfinite(sc)
+        cq = np.concatenate([cq, rows[keep]])
+        cs_ = np.concatenate([cs_, sc[keep]])
+        ci = np.concatenate([ci, cols[keep].astype(np.int64) + r0 + id_base])
+        order = np.lexsort((ci, -cs_.astype(np.float64), cq))   # query, score desc, id asc
+        cq, cs_, ci = cq[order], cs_[order], ci[order]
+        start = np.searchsorted(cq, np.arange(B), side="left")
+        rank = np.arange(cq.shape[0]) - start[cq]
+        top = rank < k
+        cq, cs_, ci = cq[top], cs_[top], ci[top]
     out_s = np.full((B, k), -np.inf, dtype=np.float32)
     out_i = np.full((B, k), -1, dtype=np.int64)
-    w = best_s.shape[1]
-    out_s[:, :w] = best_s
-    out_i[:, :w] = best_i
+    if cq.shape[0]:
+        start = np.searchsorted(cq, np.arange(B), side="left")
+        rank = np.arange(cq.shape[0]) - start[cq]
+        out_s[cq, rank] = cs_
+        out_i[cq, rank] = ci
     return out_s, out_i
 
 

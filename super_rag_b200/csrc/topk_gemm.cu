@@ -488,6 +488,16 @@ int make_plan(int sms, int n_queries, int k, Plan* pl) {
     return SRAG_OK;
 }
 
+// Optional device-side timing of the two K1 kernels (bench.py's roofline leg): events are
+// recorded on the launching stream, never synchronised here.
+constexpr int PROF_RING = 256;
+struct ProfState {
+    bool on = false;
+    int n = 0;
+    cudaEvent_t ev[PROF_RING][3];
+    bool created = false;
+} g_prof;
+
 template <int G>
 int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, const TopkParams& prm,
                 cudaStream_t st) {
@@ -567,6 +577,8 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
     prm.cand = reinterpret_cast<uint2*>(ws);
     prm.partial = reinterpret_cast<uint64_t*>(ws + pl.cand_bytes);
     SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes, st));
+    const bool prof = g_prof.on && g_prof.n < PROF_RING;
+    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][0], st));
     if (n_rows > 0) {
         CUtensorMap tq, tc;
         rc = make_tmap(&tq, queries_bf16, n_queries, dim, BLOCK_M, false);
@@ -576,8 +588,41 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
         rc = (pl.cta_group == 2) ? launch_main<2>(pl, tq, tc, prm, st) : launch_main<1>(pl, tq, tc, prm, st);
         if (rc) return rc;
     }
-    return srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * k, k, q_scale, id_base, out_scores, out_ids,
-                                st);
+    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][1], st));
+    rc = srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * k, k, q_scale, id_base, out_scores, out_ids, st);
+    if (rc) return rc;
+    if (prof) {
+        SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][2], st));
+        ++g_prof.n;
+    }
+    return SRAG_OK;
+}
+
+extern "C" int srag_prof_enable(int on) {
+    if (on && !g_prof.created) {
+        for (int i = 0; i < PROF_RING; ++i)
+            for (int j = 0; j < 3; ++j) SRAG_CUDA(cudaEventCreate(&g_prof.ev[i][j]));
+        g_prof.created = true;
+    }
+    g_prof.on = on != 0;
+    g_prof.n = 0;
+    return SRAG_OK;
+}
+
+extern "C" int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int* n_calls) {
+    double a = 0, b = 0;
+    for (int i = 0; i < g_prof.n; ++i) {
+        float x = 0, y = 0;
+        SRAG_CUDA(cudaEventSynchronize(g_prof.ev[i][2]));
+        SRAG_CUDA(cudaEventElapsedTime(&x, g_prof.ev[i][0], g_prof.ev[i][1]));
+        SRAG_CUDA(cudaEventElapsedTime(&y, g_prof.ev[i][1], g_prof.ev[i][2]));
+        a += x;
+        b += y;
+    }
+    if (main_ms_sum) *main_ms_sum = a;
+    if (finalize_ms_sum) *finalize_ms_sum = b;
+    if (n_calls) *n_calls = g_prof.n;
+    return SRAG_OK;
 }
 
 // Shared with K2 (bm25.cu): per-query lists of sortable keys -> sorted top-k (score, id).

@@ -109,6 +109,17 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
     return scores, ids
 
 
+def prof_enable(on: bool):
+    _lib.check(_lib.load().srag_prof_enable(1 if on else 0), "srag_prof_enable")
+
+
+def prof_read():
+    """(sum of main-kernel ms, sum of finalize ms, calls) since prof_enable(True)."""
+    a, b, n = C.c_double(), C.c_double(), C.c_int()
+    _lib.check(_lib.load().srag_prof_read(C.byref(a), C.byref(b), C.byref(n)), "srag_prof_read")
+    return a.value, b.value, n.value
+
+
 # ---- K2 ---------------------------------------------------------------------------------
 def bm25_block_docs() -> int:
     return _lib.load().srag_bm25_block_docs()

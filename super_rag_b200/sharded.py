@@ -1,0 +1,80 @@
+"""Row-sharded corpus across the GPUs of one box: one process per GPU, rank r owns a
+contiguous row range, every rank scans its shard with K1, the per-shard (score, id) candidates
+are all-gathered over NCCL/NVLink and every rank runs the K4 merge kernel.
+
+The only exchange step is that all-gather: 12 * B * k bytes per rank (120 KiB at B=1024, k=10) —
+latency-bound, so scores and ids travel in ONE packed int64 buffer and one collective.
+The reference has no collective to compare with.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_rows: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous row range of ``rank``: [r*N/g, (r+1)*N/g) with integer floor."""
+    return (rank * n_rows) // world, ((rank + 1) * n_rows) // world
+
+
+def pack_candidates(scores: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
+    """(fp32 [B,k], int64 [B,k]) -> int64 [2,B,k]: plane 0 holds the score bits, plane 1 the ids."""
+    out = torch.empty((2,) + tuple(ids.shape), dtype=torch.int64, device=ids.device)
+    out[0] = scores.contiguous().view(torch.int32).to(torch.int64)
+    out[1] = ids
+    return out
+
+
+def unpack_candidates(packed: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """int64 [g,2,B,k] -> (scores fp32 [g,B,k], ids int64 [g,B,k])."""
+    scores = packed[:, 0].to(torch.int32).contiguous().view(torch.float32)
+    ids = packed[:, 1].contiguous()
+    return scores, ids
+
+
+def exchange_candidates(scores: torch.Tensor, ids: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """All-gather every rank's [B,k] candidates -> ([g,B,k] scores, [g,B,k] ids) on every rank.
+    Works on NCCL (device tensors) and gloo (CPU tensors: the world_size-2 CPU tests)."""
+    world = dist.get_world_size(group)
+    packed = pack_candidates(scores, ids)
+    gathered = torch.empty((world,) + tuple(packed.shape), dtype=torch.int64, device=packed.device)
+    dist.all_gather_into_tensor(gathered, packed, group=group)
+    return unpack_candidates(gathered)
+
+
+class ShardedVectorIndex:
+    """This rank's shard of a row-sharded corpus plus the exchange + merge step."""
+
+    def __init__(self, rows_bf16: torch.Tensor, row_scale: torch.Tensor, id_base: int, metric="cosine", group=None):
+        from . import ops
+        self.ops = ops
+        self.rows, self.row_scale, self.id_base = rows_bf16, row_scale, int(id_base)
+        self.metric = ops.metric_code(metric)
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self._ws: Optional[torch.Tensor] = None
+
+    def local_topk(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
+        need = self.ops.topk_workspace_bytes(self.rows.shape[0], min(q_bf16.shape[0], self.ops.MAX_QUERIES_PER_CALL), k)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.rows.device)
+        return self.ops.topk_search(self.rows, self.row_scale, q_bf16, q_scale, k, id_base=self.id_base,
+                                    workspace=self._ws)
+
+    def search_device(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
+        """Queries already resident (bf16 + multipliers, replicated on every rank)."""
+        s, i = self.local_topk(q_bf16, q_scale, k)
+        if self.world == 1:
+            return s, i
+        gs, gi = exchange_candidates(s, i, self.group)
+        return self.ops.merge_candidates(gs, gi, k)
+
+    def search_batch(self, queries: torch.Tensor, k: int):
+        """Public API: fp32/bf16 queries on host (pinned) or device -> global top-k on this rank's device."""
+        q = queries.to(self.rows.device, non_blocking=True)
+        if q.dtype not in (torch.float32, torch.bfloat16):
+            q = q.to(torch.float32)
+        qb, qs = self.ops.ingest_rows(q.contiguous(), self.metric)
+        return self.search_device(qb, qs, k)

@@ -1,0 +1,276 @@
+"""Drop-in vector-store connector: same duck type as the reference's
+``SeekDBVectorStoreConnector`` (super_rag/vectorstore/seekdb_connector.py:31-156), with the
+``collection.query`` round-trip to an external HNSW server replaced by the exact B200 scan (K1).
+
+Selected with ``VECTOR_DB_TYPE=b200`` through ``VectorStoreConnectorAdaptor``
+(super_rag/vectorstore/connector.py:4-15 gains ``case "b200"``). The reference
+constructs a fresh connector per query (nodeflow/runners/vector_search.py:74 ->
+context/context.py:12), so device state lives in a process-global registry keyed by collection
+name, not in the connector instance.
+
+Scores are similarities (higher is better): cosine or inner product, order (score desc, chunk
+row asc). ``score_threshold`` / ``filter`` kwargs are accepted and ignored exactly as the
+reference does (seekdb_connector.py:99-100) unless ctx["apply_score_threshold"] is set.
+"""
+from __future__ import annotations
+
+import logging
+import threading
+import uuid
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import ops
+from ._lib import SragError
+from .models import DocumentWithScore, QueryResult, QueryWithEmbedding
+
+logger = logging.getLogger(__name__)
+
+
+class HostDocTable:
+    """Row -> (uuid, text, metadata) on the host; uuid -> row for deletes. Pure Python."""
+
+    def __init__(self):
+        self.ids: List[str] = []
+        self.texts: List[Optional[str]] = []
+        self.metas: List[Optional[dict]] = []
+        self.row_of: Dict[str, int] = {}
+        self.deleted: set = set()
+
+    def __len__(self):
+        return len(self.ids)
+
+    @property
+    def live(self) -> int:
+        return len(self.ids) - len(self.deleted)
+
+    def append(self, ids: Sequence[str], texts: Sequence[Optional[str]], metas: Sequence[Optional[dict]]) -> range:
+        start = len(self.ids)
+        for i, t, m in zip(ids, texts, metas):
+            if i in self.row_of:
+                raise ValueError(f"duplicate id {i!r}")
+            self.row_of[i] = len(self.ids)
+            self.ids.append(i)
+            self.texts.append(t)
+            self.metas.append(m)
+        return range(start, len(self.ids))
+
+    def delete(self, ids: Sequence[str]) -> List[int]:
+        rows = []
+        for i in ids:
+            r = self.row_of.pop(i, None)
+            if r is not None and r not in self.deleted:
+                self.deleted.add(r)
+                rows.append(r)
+        return rows
+
+    def get(self, row: int) -> Tuple[str, Optional[str], Optional[dict]]:
+        return self.ids[row], self.texts[row], self.metas[row]
+
+
+class DeviceCollection:
+    """bf16 corpus matrix + fp32 row multipliers resident in HBM, growable, with tombstones."""
+
+    def __init__(self, name: str, dim: int, metric="cosine", device: Optional[str] = None, capacity: int = 0):
+        if dim % 8 != 0 or dim < 8:
+            raise ValueError(f"vector_size={dim} must be a positive multiple of 8")
+        self.name, self.dim, self.metric = name, dim, ops.metric_code(metric)
+        self.device = torch.device(device) if device else None
+        self.docs = HostDocTable()
+        self.n = 0
+        self.id_base = 0
+        self._rows: Optional[torch.Tensor] = None
+        self._scale: Optional[torch.Tensor] = None
+        self._ws: Optional[torch.Tensor] = None
+        self._reserve = capacity
+        self.lock = threading.Lock()
+
+    # -- storage ------------------------------------------------------------------------------
+    def _dev(self) -> torch.device:
+        if self.device is None:
+            if not torch.cuda.is_available():
+                raise SragError("B200VectorStoreConnector needs a CUDA device: there is no CPU fallback")
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        return self.device
+
+    def _grow(self, need: int):
+        cap = 0 if self._rows is None else self._rows.shape[0]
+        if need <= cap:
+            return
+        new_cap = max(need, 2 * cap, self._reserve, 1024)
+        dev = self._dev()
+        rows = torch.empty(new_cap, self.dim, dtype=torch.bfloat16, device=dev)
+        scale = torch.empty(new_cap, dtype=torch.float32, device=dev)
+        if self.n:
+            rows[:self.n].copy_(self._rows[:self.n])
+            scale[:self.n].copy_(self._scale[:self.n])
+        self._rows, self._scale = rows, scale
+
+    @property
+    def rows(self) -> torch.Tensor:
+        return self._rows[:self.n] if self._rows is not None else torch.empty(0, self.dim, dtype=torch.bfloat16,
+                                                                              device=self._dev())
+
+    @property
+    def row_scale(self) -> torch.Tensor:
+        return self._scale[:self.n] if self._scale is not None else torch.empty(0, dtype=torch.float32,
+                                                                                device=self._dev())
+
+    def append(self, embeddings, ids=None, texts=None, metas=None) -> List[str]:
+        """embeddings: [m, dim] tensor (any device, fp32 or bf16) or nested lists."""
+        emb = embeddings if isinstance(embeddings, torch.Tensor) else torch.tensor(embeddings, dtype=torch.float32)
+        if emb.ndim != 2 or emb.shape[1] != self.dim:
+            raise ValueError(f"embeddings must be [m, {self.dim}], got {tuple(emb.shape)}")
+        m = emb.shape[0]
+        ids = list(ids) if ids is not None else [str(uuid.uuid4()) for _ in range(m)]
+        texts = list(texts) if texts is not None else [None] * m
+        metas = list(metas) if metas is not None else [None] * m
+        with self.lock:
+            dev = self._dev()
+            self._grow(self.n + m)
+            if emb.dtype not in (torch.float32, torch.bfloat16):
+                emb = emb.to(torch.float32)
+            emb = emb.to(dev, non_blocking=True).contiguous()
+            ops.ingest_rows(emb, self.metric, out_bf16=self._rows[self.n:self.n + m],
+                            out_scale=self._scale[self.n:self.n + m])
+            self.docs.append(ids, texts, metas)
+            self.n += m
+        return ids
+
+    def delete(self, ids: Sequence[str]) -> int:
+        with self.lock:
+            rows = self.docs.delete(ids)
+            if rows:
+                idx = torch.tensor(rows, dtype=torch.int64, device=self._dev())
+                self._scale[idx] = float("nan")  # tombstone: K1 never returns a NaN-scaled row
+        return len(rows)
+
+    # -- search -------------------------------------------------------------------------------
+    def search_batch(self, queries: torch.Tensor, top_k: int):
+        """queries [B, dim] (host or device, fp32 or bf16) -> (scores fp32 [B,k], ids int64 [B,k]) on device."""
+        dev = self._dev()
+        q = queries.to(dev, non_blocking=True)
+        if q.dtype not in (torch.float32, torch.bfloat16):
+            q = q.to(torch.float32)
+        qb, qs = ops.ingest_rows(q.contiguous(), self.metric)
+        need = ops.topk_workspace_bytes(self.n, min(q.shape[0], ops.MAX_QUERIES_PER_CALL), top_k)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        return ops.topk_search(self.rows, self.row_scale, qb, qs, top_k, id_base=self.id_base, workspace=self._ws)
+
+
+_REGISTRY: Dict[str, DeviceCollection] = {}
+_REGISTRY_LOCK = threading.Lock()
+
+
+class B200Client:
+    """What ``connector.client`` exposes (the reference hands out its pyseekdb client there,
+    seekdb_connector.py:49-55): collection lifecycle in the process-global registry."""
+
+    def create_collection(self, name: str, dim: int, metric="cosine", device=None, capacity: int = 0):
+        with _REGISTRY_LOCK:
+            if name in _REGISTRY:
+                raise ValueError(f"collection {name!r} already exists")
+            _REGISTRY[name] = DeviceCollection(name, dim, metric, device, capacity)
+            return _REGISTRY[name]
+
+    def get_or_create_collection(self, name: str, dim: int = 1024, metric="cosine", device=None):
+        with _REGISTRY_LOCK:
+            if name not in _REGISTRY:
+                _REGISTRY[name] = DeviceCollection(name, dim, metric, device)
+            return _REGISTRY[name]
+
+    def get_collection(self, name: str) -> DeviceCollection:
+        return _REGISTRY[name]
+
+    def has_collection(self, name: str) -> bool:
+        return name in _REGISTRY
+
+    def delete_collection(self, name: str):
+        with _REGISTRY_LOCK:
+            _REGISTRY.pop(name, None)
+
+
+class B200VectorStoreConnector:
+    """Same constructor, attributes and methods as SeekDBVectorStoreConnector."""
+
+    def __init__(self, ctx: Dict[str, Any], **kwargs: Any):
+        self.ctx = ctx
+        self.vector_size = ctx.get("vector_size", 1024)      # seekdb_connector.py:37
+        self.distance = ctx.get("distance", "cosine")        # seekdb_connector.py:38
+        self.collection_name = self.ctx["collection"]        # KeyError like the reference
+        self.device = ctx.get("device")
+        self.apply_score_threshold = bool(ctx.get("apply_score_threshold", False))
+        self.store = self                                    # seekdb_connector.py:45
+        self.client = B200Client()
+
+    def _collection(self) -> DeviceCollection:
+        return self.client.get_or_create_collection(self.collection_name, self.vector_size, self.distance, self.device)
+
+    def create_collection(self, **kwargs: Any):
+        vector_size = kwargs.get("vector_size") or self.vector_size
+        self.vector_size = vector_size
+        if not self.client.has_collection(self.collection_name):
+            self.client.create_collection(self.collection_name, vector_size, self.distance, self.device)
+
+    def add(self, nodes) -> List[str]:
+        """nodes: objects with .text/.metadata/.embedding (models.TextNode); returns new uuid4 ids."""
+        nodes = list(nodes)
+        if not nodes:
+            return []
+        emb = [n.embedding for n in nodes]
+        if isinstance(emb[0], torch.Tensor):
+            emb = torch.stack([e.to(torch.float32) for e in emb])
+        return self._collection().append(emb, texts=[n.text for n in nodes], metas=[n.metadata for n in nodes])
+
+    def delete_collection(self):
+        self.client.delete_collection(self.collection_name)
+
+    def delete(self, **delete_kwargs: Any):
+        ids = delete_kwargs.get("ids")
+        if ids:
+            self._collection().delete(ids)
+        else:
+            raise ValueError("ids is required")              # seekdb_connector.py:95-96
+
+    def search(self, query: QueryWithEmbedding, **kwargs) -> QueryResult:
+        score_threshold = kwargs.get("score_threshold", 0.1)
+        col = self._collection()
+        top_k = int(query.top_k or 0)
+        results: List[DocumentWithScore] = []
+        if top_k > 0 and col.n > 0:
+            k = min(top_k, ops.MAX_TOPK)
+            q = torch.tensor([query.embedding], dtype=torch.float32)
+            scores, rows = col.search_batch(q, k)
+            scores, rows = scores[0].tolist(), rows[0].tolist()
+            for s, r in zip(scores, rows):
+                if r < 0:
+                    break
+                if self.apply_score_threshold and s < score_threshold:
+                    break
+                _id, text, meta = col.docs.get(r - col.id_base)
+                results.append(DocumentWithScore(text=text, metadata=meta, score=s))
+        return QueryResult(query=query.query, results=results)
+
+    # batched tensor API used by benchmarks and the sharded index
+    def search_batch(self, queries: torch.Tensor, top_k: int):
+        return self._collection().search_batch(queries, top_k)
+
+
+class VectorStoreConnectorAdaptor:
+    """super_rag/vectorstore/connector.py:4-15 with the extra ``case "b200"``; any other type is
+    delegated to the reference adaptor when it is importable."""
+
+    def __init__(self, vector_store_type, ctx: Dict[str, Any], **kwargs: Any) -> None:
+        self.ctx = ctx
+        self.vector_store_type = vector_store_type
+        match vector_store_type:
+            case "b200":
+                self.connector = B200VectorStoreConnector(ctx, **kwargs)
+            case _:
+                try:
+                    from super_rag.vectorstore.connector import VectorStoreConnectorAdaptor as _Ref  # type: ignore
+                except Exception:
+                    raise ValueError("unsupported vector store type:", vector_store_type)
+                self.connector = _Ref(vector_store_type, ctx, **kwargs).connector

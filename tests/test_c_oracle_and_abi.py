@@ -1,0 +1,91 @@
+"""CPU-only: the plain-C oracle agrees with the numpy oracle and the reference golden vectors;
+the C-ABI library builds, loads and exports every symbol include/srag_b200.h declares."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import c_oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_c_scores_and_topk_match_numpy_oracle():
+    rng = np.random.default_rng(5)
+    C = oracle.bf16_round(rng.standard_normal((700, 96)).astype(np.float32))
+    Q = oracle.bf16_round(rng.standard_normal((9, 96)).astype(np.float32))
+    C[3] = 0
+    C[600] = C[10]
+    Q[0] = C[10]
+    Q[8] = 0
+    for metric in ("cosine", "ip"):
+        s_c = c_oracle.scores(C, Q, metric)
+        s64 = oracle.exact_topk_scores_f64(C, Q, metric)
+        assert np.abs(s_c - s64).max() < (1e-5 if metric == "cosine" else 1e-3)
+        ts, ti = c_oracle.topk(s_c, 6)
+        ns, ni = oracle.exact_topk(C, Q, 6, metric)
+        for b in range(Q.shape[0]):
+            for j in range(6):
+                if ti[b, j] != ni[b, j]:
+                    assert abs(s64[b, ti[b, j]] - s64[b, ni[b, j]]) < 1e-5
+    assert ti[0, 0] == 10 and ti[0, 1] == 600
+
+
+def test_c_rrf_matches_reference_golden(golden):
+    for c in golden["rrf"]:
+        if not all(isinstance(x, int) for l in c["lists"] for x in l):
+            continue
+        ids, sc = c_oracle.rrf(c["lists"], c["rank_const"], c["min_score"])
+        ref = dict(zip(c["ids"], c["scores"]))
+        assert sorted(ids.tolist()) == sorted(c["ids"])
+        assert [ref[i] for i in ids.tolist()] == sc.tolist()
+        want_i, _ = oracle.rrf_fuse_topk([np.array(l, dtype=np.int64) for l in c["lists"]], c["rank_const"],
+                                         c["min_score"])
+        assert ids.tolist() == want_i.tolist()
+
+
+def test_c_bm25_matches_numpy_oracle_bit_exact():
+    rng = np.random.default_rng(6)
+    n_docs, vocab = 4000, 200
+    dl = rng.integers(5, 60, n_docs)
+    p = 1.0 / np.arange(1, vocab + 1)
+    tokens = rng.choice(vocab, size=int(dl.sum()), p=p / p.sum())
+    doc_ptr = np.concatenate([[0], np.cumsum(dl)])
+    tp, pd, ptf, dl32 = oracle.build_postings(tokens, doc_ptr, vocab)
+    imp = oracle.bm25_impacts(tp, pd, ptf, dl32)
+    idf = oracle.bm25_idf(np.diff(tp), n_docs)
+    imp_c = c_oracle.bm25_impacts(tp, pd, ptf, idf, dl32, float(oracle.bm25.bm25_avgdl(dl32)))
+    assert (imp.view(np.uint32) == imp_c.view(np.uint32)).all()
+    for q in ([0, 5, 17], [199], [3, 3, 4, 150, 20, 21, 22, 23]):
+        acc, hit = oracle.bm25.bm25_scores_one(tp, pd, imp, n_docs, q)
+        acc_c, hit_c = c_oracle.bm25_scores(tp, pd, imp, n_docs, q)
+        assert (acc.view(np.uint32) == acc_c.view(np.uint32)).all() and (hit == hit_c).all()
+
+
+def test_abi_library_builds_loads_and_exports_header_symbols():
+    import ctypes
+    from super_rag_b200 import build as b, _lib
+    path = b.build()
+    lib = ctypes.CDLL(path)            # loads without a GPU (no compute call is made)
+    header = open(os.path.join(ROOT, "include", "srag_b200.h")).read()
+    declared = set(re.findall(r"\b(srag_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 16
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/srag_b200.h but not exported"
+    assert declared == set(_lib.SIGNATURES), "python binding and header disagree"
+    assert lib.srag_abi_version() == 1
+
+
+def test_sass_has_tcgen05_and_tma():
+    """cuobjdump evidence that K1 is a tcgen05/TMEM/TMA kernel (B200_PROFILING.md mnemonics)."""
+    import shutil
+    import subprocess
+    from super_rag_b200 import build as b
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.run(["cuobjdump", "-sass", b.build()], capture_output=True, text=True).stdout
+    for mnemonic in ("UTCHMMA", "UTMALDG", "LDTM", "UTCBAR"):
+        assert mnemonic in sass, mnemonic
+    assert "HMMA.16816" not in sass          # no legacy mma.sync path
