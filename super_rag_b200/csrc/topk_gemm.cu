@@ -274,35 +274,58 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             ptx::tc_fence_after();
             const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)buf * BLOCK_N;
             const uint32_t row_base = (uint32_t)c * BLOCK_N;
-#pragma unroll 1
-            for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32(t_addr + ch * 32, v);
-                ptx::tmem_ld_wait();
+            // Software-pipelined TMEM reads: chunk ch+1 is in flight while chunk ch is filtered.
+            // Fast path per chunk: 32 x (FMUL, FMNMX) and one compare; the append scan only runs
+            // when some score of the chunk beats this thread's threshold.
+            const uint32_t sc_addr = ptx::smem_u32(sc);
+            uint32_t va[32], vb[32];
+            ptx::tmem_ld_32x32(t_addr, va);
+            auto process = [&](uint32_t (&v)[32], int ch) {
+                float sv[32];
+                float mx = -INFINITY;
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4) {
-                    const float4 m = *reinterpret_cast<const float4*>(sc + ch * 32 + j4 * 4);
-                    const float mm[4] = {m.x, m.y, m.z, m.w};
+                    float m0, m1, m2, m3;
+                    ptx::lds_v4(sc_addr + (uint32_t)(ch * 32 + j4 * 4) * 4u, m0, m1, m2, m3);
+                    sv[j4 * 4 + 0] = __uint_as_float(v[j4 * 4 + 0]) * m0;
+                    sv[j4 * 4 + 1] = __uint_as_float(v[j4 * 4 + 1]) * m1;
+                    sv[j4 * 4 + 2] = __uint_as_float(v[j4 * 4 + 2]) * m2;
+                    sv[j4 * 4 + 3] = __uint_as_float(v[j4 * 4 + 3]) * m3;
+                }
 #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        const float s = __uint_as_float(v[j4 * 4 + jj]) * mm[jj];
-                        if (s > thr) {  // NaN (tombstone / out-of-range row) never passes
-                            my_buf[cnt] = make_uint2(__float_as_uint(s), row_base + ch * 32 + j4 * 4 + jj);
-                            ++cnt;
+                for (int j = 0; j < 32; ++j) mx = fmaxf(mx, sv[j]);  // NaN (tombstone / padding row) is ignored
+                if (__any_sync(0xFFFFFFFFu, mx > thr)) {
+                    if (mx > thr) {
+                        const uint32_t r0 = row_base + (uint32_t)ch * 32u;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (sv[j] > thr) {
+                                my_buf[cnt] = make_uint2(__float_as_uint(sv[j]), r0 + j);
+                                ++cnt;
+                            }
                         }
                     }
+                    uint32_t need = __ballot_sync(0xFFFFFFFFu, cnt > p.trigger);
+                    while (need) {
+                        const int src = __ffs(need) - 1;
+                        need &= need - 1;
+                        uint2* b = reinterpret_cast<uint2*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_buf, src));
+                        const int n = __shfl_sync(0xFFFFFFFFu, cnt, src);
+                        const float t0 = __shfl_sync(0xFFFFFFFFu, thr, src);
+                        int ncnt;
+                        const float t1 = warp_compact(b, n, p.k, t0, scratch, thr_x, nullptr, &ncnt);
+                        if (lane == src) { thr = t1; cnt = ncnt; }
+                    }
                 }
-                uint32_t need = __ballot_sync(0xFFFFFFFFu, cnt > p.trigger);
-                while (need) {
-                    const int src = __ffs(need) - 1;
-                    need &= need - 1;
-                    uint2* b = reinterpret_cast<uint2*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_buf, src));
-                    const int n = __shfl_sync(0xFFFFFFFFu, cnt, src);
-                    const float t0 = __shfl_sync(0xFFFFFFFFu, thr, src);
-                    int ncnt;
-                    const float t1 = warp_compact(b, n, p.k, t0, scratch, thr_x, nullptr, &ncnt);
-                    if (lane == src) { thr = t1; cnt = ncnt; }
-                }
+            };
+#pragma unroll 1
+            for (int ch = 0; ch < BLOCK_N / 32; ch += 2) {
+                ptx::tmem_ld_wait_dep(va);
+                ptx::tmem_ld_32x32(t_addr + (ch + 1) * 32, vb);
+                process(va, ch);
+                ptx::tmem_ld_wait_dep(vb);
+                if (ch + 2 < BLOCK_N / 32) ptx::tmem_ld_32x32(t_addr + (ch + 2) * 32, va);
+                process(vb, ch + 1);
             }
             // hand the accumulator back to the MMA issuer (leader CTA's barrier)
             ptx::tc_fence_before();
