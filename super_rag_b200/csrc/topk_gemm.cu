@@ -9,12 +9,22 @@
 // Work decomposition
 //   unit      = one CTA (cta_group 1) or one CTA pair (cta_group 2, tcgen05.mma M = 256)
 //   q-tile    = 128 * cta_group consecutive queries; unit u owns q-tile (u % T_q) for the whole
-//               kernel, so one epilogue thread == one query (TMEM lane == query)
+//               kernel, so one TMEM lane == one query
 //   slab      = u / T_q; the unit scans corpus tiles  slab, slab + S, slab + 2S, ...
-//               (256 rows each), ids ascending, so "score > threshold" is the exact tie rule
-//   warps     0: TMA producer   1: MMA issuer + TMEM owner   2..5: epilogue (one TMEM lane
-//               quadrant each)
+//               ids ascending, so "score > threshold" is the exact tie rule
+//   warps     0: TMA producer   1: MMA issuer + TMEM owner   2..9: epilogue. Epilogue warp w may
+//               read TMEM lane quadrant w % 4; the two warps of a quadrant split the tile's columns,
+//               so a query is filtered by two threads with independent thresholds / candidate lists
 //   pipelines smem full/empty ring (TMA <-> MMA), TMEM full/empty x2 (MMA <-> epilogue)
+//
+// Two operand plans (template RQ):
+//   RQ = true  (dim <= 1024) "resident queries": the unit's q-tile never moves again after
+//              set-up — k-blocks 0..7 sit in TMEM columns 256..511 (tcgen05.mma with A from TMEM),
+//              k-blocks 8..15 in 128 KB of shared memory. Only corpus tiles (128 rows) stream
+//              through the ring, which halves the bytes every SM has to ingest per flop: the
+//              streaming plan needs 64 B/clk/SM at full tensor rate — the whole L2->SM port.
+//   RQ = false streaming: query and corpus k-blocks both go through the ring (256-row tiles);
+//              any dim.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -22,117 +32,101 @@
 namespace {
 
 constexpr int BLOCK_M = 128;  // queries per CTA  (TMEM lanes)
-constexpr int BLOCK_N = 256;  // corpus rows per tile (TMEM fp32 columns per accumulator)
 constexpr int BLOCK_K = 64;   // bf16 per 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int CAND_CAP = 256;  // candidate entries per (CTA, query)
-constexpr int NUM_THREADS = 192;
-constexpr int NUM_EPI_WARPS = 4;
-constexpr int TMEM_COLS = 512;  // two 256-column accumulators
+constexpr int MAX_EPI_WARPS = 8;  // epilogue warps per CTA: 4 or 8 (template EW)
+constexpr int TMEM_COLS = 512;
+constexpr int PROG_SLOTS = 8;   // q-tile units per slab that pace each other (one 32-byte sector)
+constexpr int MAX_STAGES = 12;
+constexpr int RQ_TMEM_KB = 8;   // query k-blocks resident in TMEM (8 * 32 columns at column 256)
+constexpr int RQ_SMEM_KB = 8;   // query k-blocks resident in shared memory
+constexpr int RQ_MAX_DIM = (RQ_TMEM_KB + RQ_SMEM_KB) * BLOCK_K;
+constexpr int RQ_A_TMEM_COL = 256;
 
-template <int G>
+template <int G, bool RQ>
 struct Cfg {
-    static constexpr int B_ROWS = BLOCK_N / G;  // corpus rows THIS CTA stages per k-block
+    static constexpr int BLOCK_N = RQ ? 128 : 256;  // corpus rows per tile = fp32 columns per accumulator
+    static constexpr int B_ROWS = BLOCK_N / G;      // corpus rows THIS CTA stages per k-block
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
     static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (G == 1) ? 4 : 6;  // 192 KB of operand staging either way
+    static constexpr int STAGE_BYTES = RQ ? B_BYTES : A_BYTES + B_BYTES;
+    static constexpr int QRES_BYTES = RQ ? RQ_SMEM_KB * A_BYTES : 0;
+    static constexpr int STAGES = RQ ? (G == 2 ? 11 : 5) : (G == 1 ? 4 : 6);
     static constexpr int RING_BYTES = STAGES * STAGE_BYTES;
+    static_assert(STAGES <= MAX_STAGES, "barrier arrays too small");
 };
 
 struct __align__(16) SmemTail {
-    uint64_t full[8];
-    uint64_t empty[8];
+    uint64_t full[MAX_STAGES];
+    uint64_t empty[MAX_STAGES];
     uint64_t tmem_full[2];
     uint64_t tmem_empty[2];
+    uint64_t q_full;   // resident query k-blocks landed in shared memory (TMA)
+    uint64_t q_tmem;   // resident query k-blocks written to TMEM by the epilogue warps
     uint32_t tmem_base;
     uint32_t pad;
-    float thr_xchg[NUM_EPI_WARPS];
-    alignas(16) float scale[NUM_EPI_WARPS][BLOCK_N];     // per-warp copy of the tile's row multipliers
-    alignas(16) uint64_t keys[NUM_EPI_WARPS][CAND_CAP];  // per-warp compaction scratch
+    alignas(16) float scale[1024];  // per-warp copies of the row multipliers of its columns (EW * BLOCK_N / (EW / 4))
 };
 
-template <int G>
+template <int G, bool RQ>
 constexpr size_t smem_bytes() {
-    return 1024 /*alignment slack*/ + Cfg<G>::RING_BYTES + sizeof(SmemTail);
+    return 1024 /*alignment slack*/ + Cfg<G, RQ>::QRES_BYTES + Cfg<G, RQ>::RING_BYTES + sizeof(SmemTail);
 }
 
 struct TopkParams {
     const float* row_scale;  // [n_rows]
+    const __nv_bfloat16* queries;  // [n_queries][dim] (RQ: read directly for the TMEM-resident part)
     int64_t n_rows;
     int dim;
     int n_queries;
     int k;
     int num_q_tiles;  // T_q
     int num_slabs;    // S
-    int trigger;      // compaction trigger (entries)
-    uint2* cand;      // [grid * 128][CAND_CAP]  (score bits, local row)
-    uint64_t* partial;  // [n_queries][S][k] sortable keys, pre-zeroed (= empty)
+    uint64_t* partial;  // [n_queries][S * EW/4][k] per-thread min-heaps of sortable keys, pre-zeroed (= empty)
+    int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
+    int window;       // tiles the leader may run ahead of the slowest follower
+    int debug;        // SRAG_TOPK_DEBUG perf-dissection bits (results are WRONG when set): 2 no MMA, 4 no epilogue work
 };
 
 // ---------------------------------------------------------------------------------------
-// Warp-cooperative compaction of lane `src`'s candidate buffer: keep the k best under
-// (score desc, row asc), sorted. Rank-by-counting: keys are unique (rows are unique), so
-// ranks are a permutation. Cost ~ n * ceil(n/32) comparisons per lane.
-// If out_keys != nullptr the sorted keys go there (final flush), else the sorted raw pairs
-// go back to the front of the buffer. Returns the new threshold for lane src (all lanes
-// return the same value; only src uses it) and the new count through *new_cnt.
+// Per-thread running top-k: a binary MIN-heap of k sortable keys that lives directly in this
+// thread's slice of `partial` (pre-zeroed = k EMPTY keys, which is a valid heap). A candidate
+// that beats the threshold replaces the root (the current k-th best) and sifts down: O(log k)
+// thread-private, L1-resident loads/stores, no warp cooperation, and the threshold is always
+// the exact k-th best seen so far. Precondition: key > heap[0]. Returns the new threshold.
 // ---------------------------------------------------------------------------------------
-__device__ __noinline__ float warp_compact(uint2* buf, int n, int k, float old_thr, uint64_t* scratch,
-                                           float* thr_xchg, uint64_t* out_keys, int* new_cnt) {
-    const int lane = ptx::lane_id();
-    uint64_t key[CAND_CAP / 32];
-    uint2 raw[CAND_CAP / 32];
-#pragma unroll
-    for (int i = 0; i < CAND_CAP / 32; ++i) {
-        int e = lane + 32 * i;
-        key[i] = SRAG_KEY_EMPTY;
-        if (e < n) {
-            raw[i] = __ldcv(buf + e);  // written by another lane of this warp: bypass L1
-            key[i] = srag_pack_key(raw[i].x, raw[i].y);
-            scratch[e] = key[i];
+__device__ __noinline__ float heap_replace_root(uint64_t* heap, int k, uint32_t score_bits, uint32_t row) {
+    const uint64_t key = srag_pack_key(score_bits, row);
+    uint64_t root = key;
+    int i = 0;
+    for (;;) {
+        const int l = 2 * i + 1;
+        if (l >= k) break;
+        uint64_t kc = heap[l];
+        int c = l;
+        if (l + 1 < k) {
+            const uint64_t kr = heap[l + 1];
+            if (kr < kc) { kc = kr; c = l + 1; }
         }
+        if (kc >= key) break;
+        heap[i] = kc;
+        if (i == 0) root = kc;
+        i = c;
     }
-    __syncwarp();
-    int rank[CAND_CAP / 32];
-#pragma unroll
-    for (int i = 0; i < CAND_CAP / 32; ++i) rank[i] = 0;
-    const int groups = (n + 31) >> 5;
-    for (int j = 0; j < n; ++j) {
-        uint64_t kj = scratch[j];
-#pragma unroll
-        for (int i = 0; i < CAND_CAP / 32; ++i)
-            if (i < groups) rank[i] += (kj > key[i]) ? 1 : 0;
-    }
-    __syncwarp();
-#pragma unroll
-    for (int i = 0; i < CAND_CAP / 32; ++i) {
-        int e = lane + 32 * i;
-        if (e < n && rank[i] < k) {
-            if (out_keys != nullptr)
-                out_keys[rank[i]] = key[i];
-            else
-                buf[rank[i]] = raw[i];
-            if (rank[i] == k - 1) *thr_xchg = __uint_as_float(raw[i].x);
-        }
-    }
-    __syncwarp();
-    float thr = old_thr;
-    if (n >= k) thr = *(volatile float*)thr_xchg;
-    *new_cnt = n < k ? n : k;
-    __syncwarp();
-    return thr;
+    heap[i] = key;
+    return root == SRAG_KEY_EMPTY ? -INFINITY : __uint_as_float(srag_key_score_bits(root));
 }
 
 
 // ---------------------------------------------------------------------------------------
 // main kernel
 // ---------------------------------------------------------------------------------------
-template <int G>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <int G, bool RQ, int EW>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                  const TopkParams p) {
-    using C = Cfg<G>;
+    using C = Cfg<G, RQ>;
+    constexpr int BLOCK_N = C::BLOCK_N;
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t cta_rank = (G == 2) ? ptx::cluster_ctarank() : 0u;
@@ -143,9 +137,11 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
     const int num_kb = (p.dim + BLOCK_K - 1) / BLOCK_K;
     const int num_c_tiles = (int)((p.n_rows + BLOCK_N - 1) / BLOCK_N);
+    const int q_row = (q_tile * G + (int)cta_rank) * BLOCK_M;  // first query of this CTA
 
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* qres = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* ring = qres + C::QRES_BYTES;
     SmemTail* tail = reinterpret_cast<SmemTail*>(ring + C::RING_BYTES);
 
     // ---- one-time setup ----------------------------------------------------------------
@@ -158,8 +154,10 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(&tail->tmem_full[b], 1);
-            ptx::mbar_init(&tail->tmem_empty[b], NUM_EPI_WARPS * G);
+            ptx::mbar_init(&tail->tmem_empty[b], EW * G);
         }
+        ptx::mbar_init(&tail->q_full, 1);
+        ptx::mbar_init(&tail->q_tmem, EW * G);
         ptx::fence_mbar_init();
     }
     if (warp == 1) {
@@ -170,40 +168,92 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if constexpr (G == 2) ptx::cluster_sync_all(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *(volatile uint32_t*)&tail->tmem_base;
+    const int num_qres = RQ ? max(0, num_kb - RQ_TMEM_KB) : 0;  // query k-blocks resident in shared memory
 
+    // Producer and MMA warps run their loops warp-uniformly and predicate only the single-thread
+    // instructions with elect.sync: addresses and descriptors then live in uniform registers and the
+    // issue loop is a handful of SASS instructions per tcgen05.mma / TMA (one thread looping alone
+    // paid an ELECT + R2UR per operand, ~130 instructions per k-block: issue-bound).
     if (warp == 0) {
-        // ===== TMA producer (one lane) ====================================================
-        if (lane == 0) {
-            const int q_row = (q_tile * G + (int)cta_rank) * BLOCK_M;
-            uint32_t stage = 0, phase = 0;
-            for (int c = slab; c < num_c_tiles; c += p.num_slabs) {
-                const int c_row = c * BLOCK_N + (int)cta_rank * C::B_ROWS;
-                for (int kb = 0; kb < num_kb; ++kb) {
-                    ptx::mbar_wait(&tail->empty[stage], phase ^ 1);
-                    uint8_t* a_dst = ring + stage * C::STAGE_BYTES;
-                    uint8_t* b_dst = a_dst + C::A_BYTES;
+        // ===== TMA producer ===============================================================
+        if (RQ && num_qres > 0) {
+            if (ptx::elect_one()) {
+                if constexpr (G == 1) {
+                    ptx::mbar_arrive_expect_tx(&tail->q_full, (uint32_t)num_qres * C::A_BYTES);
+                    for (int j = 0; j < num_qres; ++j)
+                        ptx::tma_load_2d(qres + j * C::A_BYTES, &tmap_q, &tail->q_full, (RQ_TMEM_KB + j) * BLOCK_K,
+                                         q_row);
+                } else {
+                    if (cta_rank == 0) ptx::mbar_arrive_expect_tx(&tail->q_full, 2u * (uint32_t)num_qres * C::A_BYTES);
+                    for (int j = 0; j < num_qres; ++j)
+                        ptx::tma_load_2d_2sm(qres + j * C::A_BYTES, &tmap_q, &tail->q_full,
+                                             (RQ_TMEM_KB + j) * BLOCK_K, q_row, 0x1000000000000000ull);
+                }
+            }
+            __syncwarp();
+        }
+        uint32_t stage = 0, phase = 0;
+        // L2 pacing: the T_q units of a slab stream the SAME corpus tiles. Unit 0
+        // (leader) pulls a tile from HBM; the others (followers) start it one tile later, when it
+        // sits in L2, and the leader never runs more than `window` tiles ahead of the slowest
+        // follower. A hint only: waits are bounded, correctness never depends on them.
+        volatile int* prog = p.progress ? p.progress + ((size_t)slab * 2 + cta_rank) * PROG_SLOTS : nullptr;
+        const bool paced = prog != nullptr && p.num_q_tiles > 1 && p.num_q_tiles <= PROG_SLOTS;
+        int it = 0;
+        for (int c = slab; c < num_c_tiles; c += p.num_slabs, ++it) {
+            const int c_row = c * BLOCK_N + (int)cta_rank * C::B_ROWS;
+            if (paced) {
+                uint32_t spins = 0;
+                if (q_tile == 0) {
+                    for (;;) {
+                        int lo = 0x7FFFFFFF;
+                        for (int j = 1; j < p.num_q_tiles; ++j) lo = min(lo, prog[j]);
+                        if (lo >= it - p.window || ++spins > 4096u) break;
+                        __nanosleep(64);
+                    }
+                } else {
+                    while (prog[0] < it + 1 && ++spins <= 4096u) __nanosleep(64);
+                }
+            }
+            for (int kb = 0; kb < num_kb; ++kb) {
+                ptx::mbar_wait(&tail->empty[stage], phase ^ 1);
+                if (ptx::elect_one()) {
+                    uint8_t* s_dst = ring + stage * C::STAGE_BYTES;
+                    uint8_t* b_dst = RQ ? s_dst : s_dst + C::A_BYTES;
                     if constexpr (G == 1) {
                         ptx::mbar_arrive_expect_tx(&tail->full[stage], C::STAGE_BYTES);
-                        ptx::tma_load_2d_hint(a_dst, &tmap_q, &tail->full[stage], kb * BLOCK_K, q_row,
-                                              SRAG_L2_EVICT_LAST);
+                        if constexpr (!RQ)
+                            ptx::tma_load_2d_hint(s_dst, &tmap_q, &tail->full[stage], kb * BLOCK_K, q_row,
+                                                  SRAG_L2_EVICT_LAST);
                         ptx::tma_load_2d(b_dst, &tmap_c, &tail->full[stage], kb * BLOCK_K, c_row);
                     } else {
                         // bytes of BOTH CTAs are counted on the leader's barrier
                         if (cta_rank == 0) ptx::mbar_arrive_expect_tx(&tail->full[stage], 2 * C::STAGE_BYTES);
-                        ptx::tma_load_2d_2sm(a_dst, &tmap_q, &tail->full[stage], kb * BLOCK_K, q_row,
-                                             SRAG_L2_EVICT_LAST);
+                        if constexpr (!RQ)
+                            ptx::tma_load_2d_2sm(s_dst, &tmap_q, &tail->full[stage], kb * BLOCK_K, q_row,
+                                                 SRAG_L2_EVICT_LAST);
                         ptx::tma_load_2d_2sm(b_dst, &tmap_c, &tail->full[stage], kb * BLOCK_K, c_row,
                                              0x1000000000000000ull /* evict normal */);
                     }
-                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
             }
+            if (paced && lane == 0) prog[q_tile] = it + 1;
         }
-        __syncwarp();
     } else if (warp == 1) {
-        // ===== MMA issuer (one lane of the leader CTA) ====================================
-        if (cta_rank == 0 && lane == 0) {
+        // ===== MMA issuer (leader CTA) =====================================================
+        if (cta_rank == 0) {
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_M * G, BLOCK_N);
+            constexpr uint32_t KSTEP = (UMMA_K * 2) >> 4;  // descriptor start-address units per UMMA_K
+            if constexpr (RQ) {
+                ptx::mbar_wait(&tail->q_tmem, 0);
+                if (num_qres > 0) ptx::mbar_wait(&tail->q_full, 0);
+                ptx::tc_fence_after();
+            }
+            const uint64_t desc0 = ptx::umma_desc_k128(0);
+            const uint32_t ring_lo = (ptx::smem_u32(ring) & 0x3FFFFu) >> 4;
+            const uint32_t qres_lo = (ptx::smem_u32(qres) & 0x3FFFFu) >> 4;
             uint32_t stage = 0, phase = 0;
             int it = 0;
             for (int c = slab; c < num_c_tiles; c += p.num_slabs, ++it) {
@@ -215,136 +265,216 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 for (int kb = 0; kb < num_kb; ++kb) {
                     ptx::mbar_wait(&tail->full[stage], phase);
                     ptx::tc_fence_after();
-                    const uint32_t a_addr = ptx::smem_u32(ring + stage * C::STAGE_BYTES);
-                    const uint32_t b_addr = a_addr + C::A_BYTES;
+                    const uint32_t s_lo = ring_lo + stage * (uint32_t)(C::STAGE_BYTES >> 4);
+                    if (ptx::elect_one()) {
+                        if (!(p.debug & 2)) {
+                            if constexpr (RQ) {
+                                const uint64_t bd = desc0 | (uint64_t)s_lo;
+                                if (kb < RQ_TMEM_KB) {
+                                    const uint32_t a_tmem = tmem_base + RQ_A_TMEM_COL + (uint32_t)kb * (BLOCK_K / 2);
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        ptx::umma_bf16<G>(d_tmem, ptx::umma_desc_k128(a_addr + k * UMMA_K * 2),
-                                          ptx::umma_desc_k128(b_addr + k * UMMA_K * 2), idesc,
-                                          (uint32_t)((kb | k) != 0));
+                                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                                        ptx::umma_bf16_ts<G>(d_tmem, a_tmem + k * (UMMA_K / 2), bd + k * KSTEP, idesc,
+                                                             (uint32_t)((kb | k) != 0));
+                                } else {
+                                    const uint64_t ad =
+                                        desc0 | (uint64_t)(qres_lo + (uint32_t)(kb - RQ_TMEM_KB) * (C::A_BYTES >> 4));
+#pragma unroll
+                                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                                        ptx::umma_bf16<G>(d_tmem, ad + k * KSTEP, bd + k * KSTEP, idesc, 1u);
+                                }
+                            } else {
+                                const uint64_t ad = desc0 | (uint64_t)s_lo;
+                                const uint64_t bd = ad + (uint64_t)(C::A_BYTES >> 4);
+#pragma unroll
+                                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                                    ptx::umma_bf16<G>(d_tmem, ad + k * KSTEP, bd + k * KSTEP, idesc,
+                                                      (uint32_t)((kb | k) != 0));
+                            }
+                        }
+                        ptx::umma_commit<G>(&tail->empty[stage]);  // smem slot reusable once these MMAs retire
+                        if (kb == num_kb - 1) ptx::umma_commit<G>(&tail->tmem_full[buf]);  // accumulator ready
                     }
-                    ptx::umma_commit<G>(&tail->empty[stage]);  // smem slot reusable once these MMAs retire
+                    __syncwarp();
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
-                ptx::umma_commit<G>(&tail->tmem_full[buf]);  // accumulator ready for the epilogue
             }
         }
-        __syncwarp();
     } else {
-        // ===== epilogue: thread == query =================================================
-        const int ew = warp - 2;        // 0..3: private scratch index
-        const int quad = warp & 3;      // TMEM lane quadrant this warp may read
+        // ===== epilogue: lane == query; EW/4 warps (column slices) per TMEM lane quadrant ======
+        constexpr int H = EW / 4;             // warps (threads) that share one query
+        constexpr int CPW = BLOCK_N / H;      // tile columns per warp
+        constexpr int CHUNKS = CPW / 32;      // 32-column TMEM reads per warp and tile
+        constexpr int SPL = CPW / 32;         // consecutive row multipliers each lane fetches
+        constexpr int LPC = 32 / SPL;         // lanes whose multipliers cover one 32-column chunk
+        const int ew = warp - 2;        // 0..EW-1
+        const int quad = warp & 3;      // TMEM lane quadrant this warp may access
+        const int half = ew >> 2;       // which column slice of the tile
         const int row_in_cta = quad * 32 + lane;
-        const int q_global = (q_tile * G + (int)cta_rank) * BLOCK_M + row_in_cta;
-        uint2* my_buf = p.cand + ((size_t)blockIdx.x * BLOCK_M + row_in_cta) * CAND_CAP;
-        float* sc = tail->scale[ew];
-        uint64_t* scratch = tail->keys[ew];
-        float* thr_x = &tail->thr_xchg[ew];
+        const int q_global = q_row + row_in_cta;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+
+        if constexpr (RQ) {
+            // park query k-blocks 0..7 in TMEM: each thread copies ITS row, 64 bf16 (32 columns) at a time
+            const uint4* qsrc = reinterpret_cast<const uint4*>(p.queries + (size_t)q_global * p.dim);
+            constexpr int PER = RQ_TMEM_KB / H;
+            for (int cch = half * PER; cch < half * PER + PER; ++cch) {
+                if (cch * BLOCK_K >= p.dim) break;  // warp-uniform
+                uint32_t r[32];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                    if (q_global < p.n_queries && cch * BLOCK_K + j * 8 < p.dim) v = __ldg(qsrc + cch * 8 + j);
+                    r[4 * j + 0] = v.x; r[4 * j + 1] = v.y; r[4 * j + 2] = v.z; r[4 * j + 3] = v.w;
+                }
+                ptx::tmem_st_32x32(lane_addr + RQ_A_TMEM_COL + (uint32_t)cch * 32u, r);
+            }
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if constexpr (G == 2) ptx::mbar_arrive_cluster(&tail->q_tmem, 0);
+                else ptx::mbar_arrive(&tail->q_tmem);
+            }
+        }
+
+        // this thread's heap: partial[q][slab * H + half][k]; threads of padding queries never insert
+        uint64_t* heap = p.partial + ((size_t)min(q_global, p.n_queries - 1) * (p.num_slabs * H) + slab * H + half) * p.k;
+        float* sc = tail->scale + ew * CPW;
         const float nanf_ = __uint_as_float(0x7FC00000u);
+        const int col0 = half * CPW;
+        float thr = q_global < p.n_queries ? -INFINITY : INFINITY;
 
-        float thr = -INFINITY;
-        int cnt = 0;
-
-        auto load_scales = [&](int c, float (&r)[8]) {
-            const int64_t row0 = (int64_t)c * BLOCK_N + lane * 8;
-            if (row0 + 8 <= p.n_rows) {
-                const float4* src = reinterpret_cast<const float4*>(p.row_scale + row0);
-                float4 a = __ldg(src), b = __ldg(src + 1);
-                r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
-                r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
+        auto load_scales = [&](int c, float (&r)[SPL]) {
+            const int64_t row0 = (int64_t)c * BLOCK_N + col0 + lane * SPL;
+            if (row0 + SPL <= p.n_rows) {
+                if constexpr (SPL == 2) {
+                    const float2 a = __ldg(reinterpret_cast<const float2*>(p.row_scale + row0));
+                    r[0] = a.x; r[1] = a.y;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < SPL; i += 4) {
+                        const float4 a = __ldg(reinterpret_cast<const float4*>(p.row_scale + row0 + i));
+                        r[i] = a.x; r[i + 1] = a.y; r[i + 2] = a.z; r[i + 3] = a.w;
+                    }
+                }
             } else {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) r[i] = (row0 + i < p.n_rows) ? __ldg(p.row_scale + row0 + i) : nanf_;
+                for (int i = 0; i < SPL; ++i) r[i] = (row0 + i < p.n_rows) ? __ldg(p.row_scale + row0 + i) : nanf_;
             }
         };
 
-        float nxt[8];
+        float nxt[SPL];
         if (slab < num_c_tiles) load_scales(slab, nxt);
         int it = 0;
         for (int c = slab; c < num_c_tiles; c += p.num_slabs, ++it) {
             const int buf = it & 1;
             const uint32_t use = (uint32_t)(it >> 1);
             __syncwarp();
-            *reinterpret_cast<float4*>(sc + lane * 8) = make_float4(nxt[0], nxt[1], nxt[2], nxt[3]);
-            *reinterpret_cast<float4*>(sc + lane * 8 + 4) = make_float4(nxt[4], nxt[5], nxt[6], nxt[7]);
+            if constexpr (SPL == 2) {
+                *reinterpret_cast<float2*>(sc + lane * 2) = make_float2(nxt[0], nxt[1]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < SPL; i += 4)
+                    *reinterpret_cast<float4*>(sc + lane * SPL + i) = make_float4(nxt[i], nxt[i + 1], nxt[i + 2], nxt[i + 3]);
+            }
+            // per-chunk bounds of the row multipliers (NaN = tombstone / padding is ignored by fmaxf/fminf;
+            // a chunk of only such rows gets NaN bounds and is skipped by the filter below)
+            float s_hi_l = nxt[0], s_lo_l = nxt[0];  // after the butterfly: bounds of this lane's chunk
+#pragma unroll
+            for (int i = 1; i < SPL; ++i) { s_hi_l = fmaxf(s_hi_l, nxt[i]); s_lo_l = fminf(s_lo_l, nxt[i]); }
+#pragma unroll
+            for (int o = 1; o < LPC; o <<= 1) {
+                s_hi_l = fmaxf(s_hi_l, __shfl_xor_sync(0xFFFFFFFFu, s_hi_l, o));
+                s_lo_l = fminf(s_lo_l, __shfl_xor_sync(0xFFFFFFFFu, s_lo_l, o));
+            }
             __syncwarp();
             if (c + p.num_slabs < num_c_tiles) load_scales(c + p.num_slabs, nxt);
 
             ptx::mbar_wait(&tail->tmem_full[buf], use & 1);
             ptx::tc_fence_after();
-            const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)buf * BLOCK_N;
-            const uint32_t row_base = (uint32_t)c * BLOCK_N;
-            // Software-pipelined TMEM reads: chunk ch+1 is in flight while chunk ch is filtered.
-            // Fast path per chunk: 32 x (FMUL, FMNMX) and one compare; the append scan only runs
-            // when some score of the chunk beats this thread's threshold.
+            const uint32_t t_addr = lane_addr + (uint32_t)buf * BLOCK_N + (uint32_t)col0;
+            const uint32_t row_base = (uint32_t)c * BLOCK_N + (uint32_t)col0;
             const uint32_t sc_addr = ptx::smem_u32(sc);
-            uint32_t va[32], vb[32];
-            ptx::tmem_ld_32x32(t_addr, va);
-            auto process = [&](uint32_t (&v)[32], int ch) {
-                float sv[32];
-                float mx = -INFINITY;
-#pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4) {
-                    float m0, m1, m2, m3;
-                    ptx::lds_v4(sc_addr + (uint32_t)(ch * 32 + j4 * 4) * 4u, m0, m1, m2, m3);
-                    sv[j4 * 4 + 0] = __uint_as_float(v[j4 * 4 + 0]) * m0;
-                    sv[j4 * 4 + 1] = __uint_as_float(v[j4 * 4 + 1]) * m1;
-                    sv[j4 * 4 + 2] = __uint_as_float(v[j4 * 4 + 2]) * m2;
-                    sv[j4 * 4 + 3] = __uint_as_float(v[j4 * 4 + 3]) * m3;
+            // hand the accumulator back to the MMA issuer (leader CTA's barrier) as soon as this warp's
+            // last TMEM read has landed in registers
+            auto release = [&]() {
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if constexpr (G == 2) ptx::mbar_arrive_cluster(&tail->tmem_empty[buf], 0);
+                    else ptx::mbar_arrive(&tail->tmem_empty[buf]);
                 }
+            };
+            // Filter per 32-column chunk: m = max of the RAW accumulators (FMNMX3 tree only). Every scaled
+            // score of the chunk is <= max(m * smax, m * smin) (IEEE multiply is monotone), so the exact
+            // per-element scaling + append scan only runs when that bound beats this thread's threshold.
+            auto process = [&](uint32_t (&v)[32], int ch, float s_hi, float s_lo) {
+                float t0 = __uint_as_float(v[0]), t1 = __uint_as_float(v[1]);
+                float t2 = __uint_as_float(v[2]), t3 = __uint_as_float(v[3]);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) mx = fmaxf(mx, sv[j]);  // NaN (tombstone / padding row) is ignored
-                if (__any_sync(0xFFFFFFFFu, mx > thr)) {
-                    if (mx > thr) {
-                        const uint32_t r0 = row_base + (uint32_t)ch * 32u;
+                for (int j = 4; j < 32; j += 4) {
+                    t0 = fmaxf(t0, __uint_as_float(v[j]));
+                    t1 = fmaxf(t1, __uint_as_float(v[j + 1]));
+                    t2 = fmaxf(t2, __uint_as_float(v[j + 2]));
+                    t3 = fmaxf(t3, __uint_as_float(v[j + 3]));
+                }
+                const float m = fmaxf(fmaxf(t0, t1), fmaxf(t2, t3));
+                const float bound = fmaxf(m * s_hi, m * s_lo);
+                if (!__any_sync(0xFFFFFFFFu, bound > thr)) return;
+                // exact scores of the chunk (FMUL2) and the maxima of its four 8-column groups
+                float sv[32], g[4];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            if (sv[j] > thr) {
-                                my_buf[cnt] = make_uint2(__float_as_uint(sv[j]), r0 + j);
-                                ++cnt;
+                for (int q = 0; q < 4; ++q) {
+                    float m0, m1, m2, m3, m4, m5, m6, m7;
+                    ptx::lds_v4(sc_addr + (uint32_t)(ch * 32 + q * 8) * 4u, m0, m1, m2, m3);
+                    ptx::lds_v4(sc_addr + (uint32_t)(ch * 32 + q * 8 + 4) * 4u, m4, m5, m6, m7);
+                    ptx::mul2(sv[q * 8 + 0], sv[q * 8 + 1], v[q * 8 + 0], v[q * 8 + 1], m0, m1);
+                    ptx::mul2(sv[q * 8 + 2], sv[q * 8 + 3], v[q * 8 + 2], v[q * 8 + 3], m2, m3);
+                    ptx::mul2(sv[q * 8 + 4], sv[q * 8 + 5], v[q * 8 + 4], v[q * 8 + 5], m4, m5);
+                    ptx::mul2(sv[q * 8 + 6], sv[q * 8 + 7], v[q * 8 + 6], v[q * 8 + 7], m6, m7);
+                    // fmaxf ignores NaN (tombstone / padding row); an all-NaN group never passes "> thr"
+                    g[q] = fmaxf(fmaxf(fmaxf(sv[q * 8 + 0], sv[q * 8 + 1]), fmaxf(sv[q * 8 + 2], sv[q * 8 + 3])),
+                                 fmaxf(fmaxf(sv[q * 8 + 4], sv[q * 8 + 5]), fmaxf(sv[q * 8 + 6], sv[q * 8 + 7])));
+                }
+                const float mx = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
+                if (!__any_sync(0xFFFFFFFFu, mx > thr)) return;
+                if (mx > thr) {
+                    const uint32_t r0 = row_base + (uint32_t)ch * 32u;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (g[q] > thr) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                if (sv[q * 8 + e] > thr)
+                                    thr = heap_replace_root(heap, p.k, __float_as_uint(sv[q * 8 + e]), r0 + q * 8 + e);
                             }
                         }
                     }
-                    uint32_t need = __ballot_sync(0xFFFFFFFFu, cnt > p.trigger);
-                    while (need) {
-                        const int src = __ffs(need) - 1;
-                        need &= need - 1;
-                        uint2* b = reinterpret_cast<uint2*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_buf, src));
-                        const int n = __shfl_sync(0xFFFFFFFFu, cnt, src);
-                        const float t0 = __shfl_sync(0xFFFFFFFFu, thr, src);
-                        int ncnt;
-                        const float t1 = warp_compact(b, n, p.k, t0, scratch, thr_x, nullptr, &ncnt);
-                        if (lane == src) { thr = t1; cnt = ncnt; }
-                    }
                 }
             };
+            uint32_t va[32], vb[32];
+            if (p.debug & 4) {
+                release();
+            } else {
+                ptx::tmem_ld_32x32(t_addr, va);
 #pragma unroll 1
-            for (int ch = 0; ch < BLOCK_N / 32; ch += 2) {
-                ptx::tmem_ld_wait_dep(va);
-                ptx::tmem_ld_32x32(t_addr + (ch + 1) * 32, vb);
-                process(va, ch);
-                ptx::tmem_ld_wait_dep(vb);
-                if (ch + 2 < BLOCK_N / 32) ptx::tmem_ld_32x32(t_addr + (ch + 2) * 32, va);
-                process(vb, ch + 1);
-            }
-            // hand the accumulator back to the MMA issuer (leader CTA's barrier)
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                if constexpr (G == 2) ptx::mbar_arrive_cluster(&tail->tmem_empty[buf], 0);
-                else ptx::mbar_arrive(&tail->tmem_empty[buf]);
+                for (int ch = 0; ch < CHUNKS; ch += 2) {
+                    const float h0 = __shfl_sync(0xFFFFFFFFu, s_hi_l, ch * LPC);
+                    const float l0 = __shfl_sync(0xFFFFFFFFu, s_lo_l, ch * LPC);
+                    const float h1 = __shfl_sync(0xFFFFFFFFu, s_hi_l, (ch + 1) * LPC);
+                    const float l1 = __shfl_sync(0xFFFFFFFFu, s_lo_l, (ch + 1) * LPC);
+                    ptx::tmem_ld_wait_dep(va);
+                    ptx::tmem_ld_32x32(t_addr + (ch + 1) * 32, vb);
+                    process(va, ch, h0, l0);
+                    ptx::tmem_ld_wait_dep(vb);
+                    if (ch + 2 < CHUNKS) ptx::tmem_ld_32x32(t_addr + (ch + 2) * 32, va);
+                    else release();
+                    process(vb, ch + 1, h1, l1);
+                }
             }
         }
-        // final flush: sorted top-k keys of every lane's query -> partial[q][slab][k]
-        for (int src = 0; src < 32; ++src) {
-            uint2* b = reinterpret_cast<uint2*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_buf, src));
-            const int n = __shfl_sync(0xFFFFFFFFu, cnt, src);
-            const int qg = __shfl_sync(0xFFFFFFFFu, q_global, src);
-            if (qg >= p.n_queries) continue;  // warp-uniform
-            uint64_t* out = p.partial + ((size_t)qg * p.num_slabs + slab) * p.k;
-            int ncnt;
-            (void)warp_compact(b, n, p.k, 0.f, scratch, thr_x, out, &ncnt);
-        }
+        // nothing to flush: every thread's heap already is its slice of `partial`
     }
 
     // ---- teardown ------------------------------------------------------------------------
@@ -458,9 +588,9 @@ struct Plan {
     int grid;       // CTAs launched
     int num_q_tiles;
     int num_slabs;
-    int trigger;
-    size_t cand_bytes;
-    size_t partial_bytes;
+    size_t partial_bytes;   // padded to 256
+    size_t progress_bytes;  // pacing counters, zeroed together with `partial`
+    int window;             // 0 = pacing off
 };
 
 int device_sm_count(int* sms) {
@@ -482,11 +612,25 @@ int device_sm_count(int* sms) {
     return SRAG_OK;
 }
 
-int forced_cta_group() {
-    const char* e = getenv("SRAG_TOPK_CTA_GROUP");
-    if (e && (e[0] == '1' || e[0] == '2')) return e[0] - '0';
-    return 0;
+int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    if (e && ((e[0] >= '0' && e[0] <= '9') || e[0] == '-')) return atoi(e);
+    return dflt;
 }
+
+int forced_cta_group() {
+    const int g = env_int("SRAG_TOPK_CTA_GROUP", 0);
+    return (g == 1 || g == 2) ? g : 0;
+}
+
+// SRAG_TOPK_WINDOW: tiles the leader unit of a slab may run ahead of its followers (0 = no pacing)
+int pacing_window() { return env_int("SRAG_TOPK_WINDOW", 3); }
+
+// SRAG_TOPK_RQ=1 selects the resident-query operand plan (dim <= 1024); default is the streaming plan
+bool use_resident_queries(int dim) { return dim <= RQ_MAX_DIM && env_int("SRAG_TOPK_RQ", 0) != 0; }
+
+// SRAG_TOPK_EPI_WARPS: 4 or 8 epilogue warps per CTA
+int epilogue_warps() { return env_int("SRAG_TOPK_EPI_WARPS", 4) == 8 ? 8 : 4; }
 
 int make_plan(int sms, int n_queries, int k, Plan* pl) {
     int g = forced_cta_group();
@@ -502,12 +646,9 @@ int make_plan(int sms, int n_queries, int k, Plan* pl) {
     pl->grid = units * g;
     pl->num_q_tiles = tq;
     pl->num_slabs = units / tq;
-    int trig = 2 * k + 32;
-    if (trig < 64) trig = 64;
-    if (trig > CAND_CAP - 32) trig = CAND_CAP - 32;
-    pl->trigger = trig;
-    pl->cand_bytes = (size_t)pl->grid * BLOCK_M * CAND_CAP * sizeof(uint2);
-    pl->partial_bytes = (size_t)n_queries * pl->num_slabs * k * sizeof(uint64_t);
+    pl->partial_bytes = (((size_t)n_queries * pl->num_slabs * 2 * k * sizeof(uint64_t)) + 255) & ~(size_t)255;
+    pl->progress_bytes = (size_t)pl->num_slabs * 2 * PROG_SLOTS * sizeof(int);
+    pl->window = pacing_window();
     return SRAG_OK;
 }
 
@@ -521,19 +662,19 @@ struct ProfState {
     bool created = false;
 } g_prof;
 
-template <int G>
+template <int G, bool RQ, int EW>
 int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, const TopkParams& prm,
                 cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(topk_gemm_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem_bytes<G>()));
+        SRAG_CUDA(cudaFuncSetAttribute(topk_gemm_kernel<G, RQ, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem_bytes<G, RQ>()));
         attr_done = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(pl.grid);
-    cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = smem_bytes<G>();
+    cfg.blockDim = dim3(64 + 32 * EW);
+    cfg.dynamicSmemBytes = smem_bytes<G, RQ>();
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -542,7 +683,7 @@ int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, co
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    SRAG_CUDA(cudaLaunchKernelEx(&cfg, topk_gemm_kernel<G>, tq, tc, prm));
+    SRAG_CUDA(cudaLaunchKernelEx(&cfg, topk_gemm_kernel<G, RQ, EW>, tq, tc, prm));
     return SRAG_OK;
 }
 
@@ -558,7 +699,7 @@ extern "C" int srag_topk_workspace_bytes(int64_t n_rows, int n_queries, int k, s
     Plan pl;
     rc = make_plan(sms, n_queries, k, &pl);
     if (rc) return rc;
-    *bytes = pl.cand_bytes + ((pl.partial_bytes + 255) & ~(size_t)255) + 256;
+    *bytes = pl.partial_bytes + pl.progress_bytes + 256;
     return SRAG_OK;
 }
 
@@ -581,38 +722,54 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
     Plan pl;
     rc = make_plan(sms, n_queries, k, &pl);
     if (rc) return rc;
-    const size_t need = pl.cand_bytes + ((pl.partial_bytes + 255) & ~(size_t)255);
+    const size_t need = pl.partial_bytes + pl.progress_bytes;
     if (workspace_bytes < need) {
         srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
         return SRAG_E_WORKSPACE;
     }
     uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
     SRAG_CHECK_ARG(((uintptr_t)ws & 15) == 0, "workspace must be 16-byte aligned");
+    const bool rq = use_resident_queries(dim);
+    const int ew = epilogue_warps();
     TopkParams prm;
     prm.row_scale = row_scale;
+    prm.queries = reinterpret_cast<const __nv_bfloat16*>(queries_bf16);
     prm.n_rows = n_rows;
     prm.dim = dim;
     prm.n_queries = n_queries;
     prm.k = k;
     prm.num_q_tiles = pl.num_q_tiles;
     prm.num_slabs = pl.num_slabs;
-    prm.trigger = pl.trigger;
-    prm.cand = reinterpret_cast<uint2*>(ws);
-    prm.partial = reinterpret_cast<uint64_t*>(ws + pl.cand_bytes);
-    SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes, st));
+    prm.partial = reinterpret_cast<uint64_t*>(ws);
+    prm.progress = pl.window > 0 ? reinterpret_cast<int*>(ws + pl.partial_bytes) : nullptr;
+    prm.window = pl.window;
+    prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
+    SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes + pl.progress_bytes, st));
     const bool prof = g_prof.on && g_prof.n < PROF_RING;
     if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][0], st));
     if (n_rows > 0) {
         CUtensorMap tq, tc;
         rc = make_tmap(&tq, queries_bf16, n_queries, dim, BLOCK_M, false);
         if (rc) return rc;
-        rc = make_tmap(&tc, corpus_bf16, n_rows, dim, BLOCK_N / pl.cta_group, true);
+        const int block_n = rq ? 128 : 256;
+        rc = make_tmap(&tc, corpus_bf16, n_rows, dim, block_n / pl.cta_group, true);
         if (rc) return rc;
-        rc = (pl.cta_group == 2) ? launch_main<2>(pl, tq, tc, prm, st) : launch_main<1>(pl, tq, tc, prm, st);
+        const int sel = (pl.cta_group == 2 ? 4 : 0) | (rq ? 2 : 0) | (ew == 8 ? 1 : 0);
+        switch (sel) {
+            case 0: rc = launch_main<1, false, 4>(pl, tq, tc, prm, st); break;
+            case 1: rc = launch_main<1, false, 8>(pl, tq, tc, prm, st); break;
+            case 2: rc = launch_main<1, true, 4>(pl, tq, tc, prm, st); break;
+            case 3: rc = launch_main<1, true, 8>(pl, tq, tc, prm, st); break;
+            case 4: rc = launch_main<2, false, 4>(pl, tq, tc, prm, st); break;
+            case 5: rc = launch_main<2, false, 8>(pl, tq, tc, prm, st); break;
+            case 6: rc = launch_main<2, true, 4>(pl, tq, tc, prm, st); break;
+            default: rc = launch_main<2, true, 8>(pl, tq, tc, prm, st); break;
+        }
         if (rc) return rc;
     }
     if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][1], st));
-    rc = srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * k, k, q_scale, id_base, out_scores, out_ids, st);
+    rc = srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * (ew / 4) * k, k, q_scale, id_base, out_scores, out_ids,
+                              st);
     if (rc) return rc;
     if (prof) {
         SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][2], st));
