@@ -39,9 +39,11 @@ def exchange_candidates(scores: torch.Tensor, ids: torch.Tensor, group=None) -> 
     Works on NCCL (device tensors) and gloo (CPU tensors: the world_size-2 CPU tests)."""
     world = dist.get_world_size(group)
     packed = pack_candidates(scores, ids)
-    gathered = torch.empty((world,) + tuple(packed.shape), dtype=torch.int64, device=packed.device)
+    # concatenation along dim 0 is the one output layout both NCCL and gloo accept
+    gathered = torch.empty((world * packed.shape[0],) + tuple(packed.shape[1:]), dtype=torch.int64,
+                           device=packed.device)
     dist.all_gather_into_tensor(gathered, packed, group=group)
-    return unpack_candidates(gathered)
+    return unpack_candidates(gathered.view((world,) + tuple(packed.shape)))
 
 
 class ShardedVectorIndex:

@@ -258,9 +258,14 @@ class B200VectorStoreConnector:
         return self._collection().search_batch(queries, top_k)
 
 
+_REFERENCE_ADAPTOR = None  # set by nodeflow_pack.install_connector() to the class it replaces
+
+
 class VectorStoreConnectorAdaptor:
     """super_rag/vectorstore/connector.py:4-15 with the extra ``case "b200"``; any other type is
     delegated to the reference adaptor when it is importable."""
+
+    _srag_b200 = True
 
     def __init__(self, vector_store_type, ctx: Dict[str, Any], **kwargs: Any) -> None:
         self.ctx = ctx
@@ -269,8 +274,12 @@ class VectorStoreConnectorAdaptor:
             case "b200":
                 self.connector = B200VectorStoreConnector(ctx, **kwargs)
             case _:
-                try:
-                    from super_rag.vectorstore.connector import VectorStoreConnectorAdaptor as _Ref  # type: ignore
-                except Exception:
-                    raise ValueError("unsupported vector store type:", vector_store_type)
-                self.connector = _Ref(vector_store_type, ctx, **kwargs).connector
+                ref = _REFERENCE_ADAPTOR
+                if ref is None:
+                    try:
+                        from super_rag.vectorstore.connector import VectorStoreConnectorAdaptor as ref  # type: ignore
+                    except Exception:
+                        ref = None
+                if ref is None or getattr(ref, "_srag_b200", False):
+                    raise ValueError("unsupported vector store type:", vector_store_type)  # connector.py:14-15
+                self.connector = ref(vector_store_type, ctx, **kwargs).connector

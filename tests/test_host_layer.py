@@ -1,0 +1,157 @@
+"""CPU-only tests of the host layer above the C ABI: the drop-in connector / adaptor, the node pack,
+sharding helpers and the "no CPU fallback, no oracle in the product" rules. No kernel is launched."""
+import asyncio
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REFERENCE = "/root/reference"
+
+
+def _run(coro):
+    return asyncio.run(coro)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "super_rag_b200")
+    pat = re.compile(r"^\s*(from\s+oracle\b|import\s+oracle\b|from\s+\.\.?oracle\b)", re.M)
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh")):
+                src = open(os.path.join(dirpath, f), encoding="utf-8").read()
+                assert not pat.search(src), f"{f} imports the oracle"
+                assert "/root/reference" not in src, f"{f} reads the reference at run time"
+
+
+def test_no_cpu_fallback_is_loud():
+    from super_rag_b200 import SragError, ops
+    c = torch.zeros(8, 64, dtype=torch.bfloat16)
+    s = torch.ones(8)
+    with pytest.raises(SragError):
+        ops.topk_search(c, s, c[:2], s[:2], 3)
+    with pytest.raises(SragError):
+        ops.ingest_rows(torch.zeros(4, 64))
+    with pytest.raises(SragError):
+        ops.fuse(torch.zeros(2, 1, 4, dtype=torch.int64), None, ops.FUSE_RRF, 2)
+    if not torch.cuda.is_available():
+        from super_rag_b200.vectorstore import B200VectorStoreConnector
+        from super_rag_b200.models import TextNode
+        con = B200VectorStoreConnector({"collection": "t_nofallback", "vector_size": 64})
+        with pytest.raises(SragError):
+            con.add([TextNode(text="x", embedding=[0.0] * 64)])
+        con.delete_collection()
+
+
+def test_adaptor_contract():
+    from super_rag_b200.vectorstore import B200VectorStoreConnector, VectorStoreConnectorAdaptor
+    a = VectorStoreConnectorAdaptor("b200", {"collection": "t_adaptor"})
+    assert isinstance(a.connector, B200VectorStoreConnector)
+    assert a.connector.store is a.connector and a.connector.vector_size == 1024 and a.connector.distance == "cosine"
+    with pytest.raises(KeyError):                      # seekdb_connector.py:39 ctx["collection"]
+        VectorStoreConnectorAdaptor("b200", {})
+    with pytest.raises(ValueError):                    # seekdb_connector.py:95-96
+        a.connector.delete()
+    if not os.path.isdir(REFERENCE):
+        with pytest.raises(ValueError):                # connector.py:14-15
+            VectorStoreConnectorAdaptor("qdrant", {"collection": "x"})
+    a.connector.delete_collection()
+
+
+def test_doc_table_and_tombstone_bookkeeping():
+    from super_rag_b200.vectorstore import HostDocTable
+    t = HostDocTable()
+    assert list(t.append(["a", "b", "c"], ["ta", "tb", "tc"], [None, {"k": 1}, None])) == [0, 1, 2]
+    with pytest.raises(ValueError):
+        t.append(["a"], ["dup"], [None])
+    assert t.delete(["b", "zz"]) == [1] and t.delete(["b"]) == [] and t.live == 2
+    assert t.get(2) == ("c", "tc", None)
+
+
+def test_merge_union_matches_reference_golden(golden):
+    from super_rag_b200 import nodeflow_pack as n
+    from super_rag_b200.models import DocumentWithScore as D
+    n.register()
+    entry = n.NODE_RUNNER_REGISTRY["merge"]
+    runner = entry["runner"]
+    assert entry["input_model"] is n.MergeInput or not n.USING_REFERENCE_NODEFLOW
+    for c in golden["merge_union"]:
+        i = c["inputs"]
+        mk = lambda k: [D(**d) for d in i[k]]
+        ui = n.MergeInput(merge_strategy="union", deduplicate=c["deduplicate"], vector_search_docs=mk("v"),
+                          fulltext_search_docs=mk("f"), graph_search_docs=mk("g"), summary_search_docs=mk("s"),
+                          vision_search_docs=mk("vi"))
+        out, so = _run(runner.run(ui, None))
+        assert [d.model_dump() for d in out.docs] == c["docs"] and so == c["system_output"]
+    with pytest.raises(n.ValidationError, match="Unknown merge strategy: bogus"):
+        _run(runner.run(n.MergeInput(merge_strategy="bogus"), None))
+    # defaults of the reference MergeInput are preserved (merge.py:13-14)
+    assert n.MergeInput().merge_strategy == "union" and n.MergeInput().deduplicate is True
+
+
+def test_node_pack_registers_reference_shaped_nodes():
+    from super_rag_b200 import nodeflow_pack as n
+    n.register()
+    for t in ("fulltext_search", "merge", "vector_search"):
+        e = n.NODE_RUNNER_REGISTRY[t]
+        assert set(e) == {"runner", "input_model", "output_model"}
+        assert "docs" in e["output_model"].model_json_schema()["properties"]      # {{ nodes.X.output.docs }}
+    f = n.FulltextSearchInput()
+    assert f.top_k == 5 and f.keywords is None and f.collection_ids == []
+    # unknown collection / no collection ids degrade to [] like the vector node
+    si = n.SystemInput(query="q", user="u")
+    out, _ = _run(n.NODE_RUNNER_REGISTRY["fulltext_search"]["runner"].run(n.FulltextSearchInput(), si))
+    assert out.docs == []
+    out, _ = _run(n.NODE_RUNNER_REGISTRY["fulltext_search"]["runner"].run(
+        n.FulltextSearchInput(collection_ids=["nope"]), si))
+    assert out.docs == []
+
+
+def test_hash_tokenizer_and_collection_bookkeeping():
+    from super_rag_b200 import fulltext
+    enc = fulltext.hash_tokenizer(1000)
+    assert enc("Hello, hello WORLD") == [enc("hello")[0]] * 2 + enc("world") and all(0 <= t < 1000 for t in enc("a b c"))
+    col = fulltext.FulltextCollection("t_ft", tokenizer=enc, vocab=1000)
+    assert list(col.add(["alpha beta", "beta gamma gamma"], [None, {"m": 1}])) == [0, 1]
+    assert len(col) == 2 and col._tokens[1].tolist() == enc("beta gamma gamma")
+    assert col.query_terms("alpha", ["beta", "gamma"]) == enc("beta gamma")     # keywords replace the query
+    assert col.search("alpha", 0) == []
+
+
+def test_shard_range_and_packing():
+    from super_rag_b200.sharded import pack_candidates, shard_range, unpack_candidates
+    for n, g in [(10_000_000, 8), (7, 3), (0, 2), (5, 8)]:
+        edges = [shard_range(n, g, r) for r in range(g)]
+        assert edges[0][0] == 0 and edges[-1][1] == n
+        assert all(edges[r][1] == edges[r + 1][0] for r in range(g - 1))
+    s = torch.tensor([[1.5, -0.0, float("-inf")]], dtype=torch.float32)
+    i = torch.tensor([[7, 1 << 40, -1]], dtype=torch.int64)
+    s2, i2 = unpack_candidates(pack_candidates(s, i)[None])
+    assert torch.equal(s2[0].view(torch.int32), s.view(torch.int32)) and torch.equal(i2[0], i)
+
+
+@pytest.mark.skipif(not os.path.isdir(REFERENCE), reason="reference checkout not present on this machine")
+def test_install_connector_into_unmodified_reference():
+    """VECTOR_DB_TYPE=b200 resolves inside the reference's own ContextManager (context/context.py:8-12)."""
+    sys.path.insert(0, REFERENCE)
+    try:
+        import super_rag.vectorstore.connector as ref_conn
+        from super_rag.context.context import ContextManager
+        from super_rag_b200 import nodeflow_pack as n, vectorstore
+        original = ref_conn.VectorStoreConnectorAdaptor
+        try:
+            assert n.install_connector() and n.install_connector()           # idempotent
+            cm = ContextManager("t_ctx", None, "b200", {"collection": "t_ctx", "vector_size": 64})
+            assert isinstance(cm.adaptor.connector, vectorstore.B200VectorStoreConnector)
+            with pytest.raises(ValueError):                                   # other types reach the reference adaptor
+                ContextManager("t_ctx", None, "no-such-store", {"collection": "t_ctx"})
+        finally:
+            ref_conn.VectorStoreConnectorAdaptor = original
+            sys.modules["super_rag.context.context"].VectorStoreConnectorAdaptor = original
+            vectorstore._REFERENCE_ADAPTOR = None
+    finally:
+        sys.path.remove(REFERENCE)
