@@ -83,6 +83,8 @@ struct TopkParams {
     int num_q_tiles;  // T_q
     int num_slabs;    // S
     uint64_t* partial;  // [n_queries][S * EW/4][k] per-thread min-heaps of sortable keys, pre-zeroed (= empty)
+    uint32_t* gthr;   // [S * EW/4][n_queries] j-th best score of every list (orderable bits), pre-zeroed
+    int share_j;      // j = ceil(k / lists), 1..8; 0 = threshold sharing off
     int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
     int window;       // tiles the leader may run ahead of the slowest follower
     int debug;        // SRAG_TOPK_DEBUG perf-dissection bits (results are WRONG when set): 2 no MMA, 4 no epilogue work
@@ -343,7 +345,21 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         float* sc = tail->scale + ew * CPW;
         const float nanf_ = __uint_as_float(0x7FC00000u);
         const int col0 = half * CPW;
-        float thr = q_global < p.n_queries ? -INFINITY : INFINITY;
+        // Threshold sharing. The query is scanned by L = S * H lists (one per unit and column slice). Each
+        // list publishes its j-th best score, j = ceil(k / L). Every list then holds >= j rows scoring
+        // >= T = min over lists of those, i.e. >= k rows overall score >= T, so a row of the global
+        // top-k scores >= T and is never dropped by "> thr" with thr = max(own k-th best, T - 2 ulp).
+        // Cuts heap pushes per thread from ~k ln(n/k) to ~j ln(n/j).
+        const bool valid_q = q_global < p.n_queries;
+        const int qx = min(q_global, p.n_queries - 1);
+        const int num_lists = p.num_slabs * H;
+        const int my_list = slab * H + half;
+        float topj[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) topj[i] = -INFINITY;
+        float thr_own = -INFINITY, thr_shared = -INFINITY;
+        uint32_t published = 0;
+        float thr = valid_q ? -INFINITY : INFINITY;
 
         auto load_scales = [&](int c, float (&r)[SPL]) {
             const int64_t row0 = (int64_t)c * BLOCK_N + col0 + lane * SPL;
@@ -391,6 +407,16 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             __syncwarp();
             if (c + p.num_slabs < num_c_tiles) load_scales(c + p.num_slabs, nxt);
 
+            if (p.share_j > 0 && valid_q && (it & 3) == 0) {  // refresh the shared bound every 4th tile
+                uint32_t lo = 0xFFFFFFFFu;
+                const volatile uint32_t* gp = p.gthr + qx;
+#pragma unroll 6
+                for (int l = 0; l < num_lists; ++l) lo = min(lo, gp[(size_t)l * p.n_queries]);
+                if (lo > 0x00800001u) {  // every list has published something above -inf
+                    thr_shared = __uint_as_float(srag_f32_from_orderable(lo - 2u));
+                    thr = fmaxf(thr_own, thr_shared);
+                }
+            }
             ptx::mbar_wait(&tail->tmem_full[buf], use & 1);
             ptx::tc_fence_after();
             const uint32_t t_addr = lane_addr + (uint32_t)buf * BLOCK_N + (uint32_t)col0;
@@ -447,7 +473,17 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
                                 if (sv[q * 8 + e] > thr)
-                                    thr = heap_replace_root(heap, p.k, __float_as_uint(sv[q * 8 + e]), r0 + q * 8 + e);
+                                {
+                                    float v = sv[q * 8 + e];
+                                    thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
+                                    thr = fmaxf(thr_own, thr_shared);
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i) {  // keep the 8 best scores sorted (descending)
+                                        const float hi = fmaxf(topj[i], v);
+                                        v = fminf(topj[i], v);
+                                        topj[i] = hi;
+                                    }
+                                }
                             }
                         }
                     }
@@ -471,6 +507,18 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     if (ch + 2 < CHUNKS) ptx::tmem_ld_32x32(t_addr + (ch + 2) * 32, va);
                     else release();
                     process(vb, ch + 1, h1, l1);
+                }
+            }
+            if (p.share_j > 0 && valid_q) {
+                float tj = topj[0];
+#pragma unroll
+                for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
+                if (tj > -INFINITY) {
+                    const uint32_t o = srag_f32_orderable(__float_as_uint(tj));
+                    if (o > published) {  // single writer per slot: a plain (volatile) store
+                        *reinterpret_cast<volatile uint32_t*>(p.gthr + (size_t)my_list * p.n_queries + qx) = o;
+                        published = o;
+                    }
                 }
             }
         }
@@ -589,6 +637,7 @@ struct Plan {
     int num_q_tiles;
     int num_slabs;
     size_t partial_bytes;   // padded to 256
+    size_t gthr_bytes;      // shared per-query thresholds, zeroed together with `partial`
     size_t progress_bytes;  // pacing counters, zeroed together with `partial`
     int window;             // 0 = pacing off
 };
@@ -647,6 +696,7 @@ int make_plan(int sms, int n_queries, int k, Plan* pl) {
     pl->num_q_tiles = tq;
     pl->num_slabs = units / tq;
     pl->partial_bytes = (((size_t)n_queries * pl->num_slabs * 2 * k * sizeof(uint64_t)) + 255) & ~(size_t)255;
+    pl->gthr_bytes = (((size_t)n_queries * pl->num_slabs * 2 * sizeof(uint32_t)) + 255) & ~(size_t)255;
     pl->progress_bytes = (size_t)pl->num_slabs * 2 * PROG_SLOTS * sizeof(int);
     pl->window = pacing_window();
     return SRAG_OK;
@@ -699,7 +749,7 @@ extern "C" int srag_topk_workspace_bytes(int64_t n_rows, int n_queries, int k, s
     Plan pl;
     rc = make_plan(sms, n_queries, k, &pl);
     if (rc) return rc;
-    *bytes = pl.partial_bytes + pl.progress_bytes + 256;
+    *bytes = pl.partial_bytes + pl.gthr_bytes + pl.progress_bytes + 256;
     return SRAG_OK;
 }
 
@@ -722,7 +772,7 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
     Plan pl;
     rc = make_plan(sms, n_queries, k, &pl);
     if (rc) return rc;
-    const size_t need = pl.partial_bytes + pl.progress_bytes;
+    const size_t need = pl.partial_bytes + pl.gthr_bytes + pl.progress_bytes;
     if (workspace_bytes < need) {
         srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
         return SRAG_E_WORKSPACE;
@@ -741,10 +791,17 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
     prm.num_q_tiles = pl.num_q_tiles;
     prm.num_slabs = pl.num_slabs;
     prm.partial = reinterpret_cast<uint64_t*>(ws);
-    prm.progress = pl.window > 0 ? reinterpret_cast<int*>(ws + pl.partial_bytes) : nullptr;
+    prm.progress = pl.window > 0 ? reinterpret_cast<int*>(ws + pl.partial_bytes + pl.gthr_bytes) : nullptr;
+    prm.gthr = reinterpret_cast<uint32_t*>(ws + pl.partial_bytes);
+    {
+        // sharing needs j = ceil(k / lists) <= 8 tracked scores and a short list of slots to poll
+        const int lists = pl.num_slabs * (ew / 4);
+        const int j = (k + lists - 1) / lists;
+        prm.share_j = (env_int("SRAG_TOPK_SHARE", 1) != 0 && lists >= 2 && lists <= 40 && j <= 8) ? j : 0;
+    }
     prm.window = pl.window;
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
-    SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes + pl.progress_bytes, st));
+    SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes + pl.gthr_bytes + pl.progress_bytes, st));
     const bool prof = g_prof.on && g_prof.n < PROF_RING;
     if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][0], st));
     if (n_rows > 0) {

@@ -14,8 +14,8 @@ from ._lib import SragError
 METRIC_COSINE, METRIC_IP = 0, 1
 FUSE_RRF, FUSE_WEIGHTED = 0, 1
 MAX_TOPK, MAX_BM25_K, MAX_LISTS = 128, 256, 8
-# one srag_topk_search launch handles at most (SMs/2) query tiles of 256; chunk above this
-MAX_QUERIES_PER_CALL = 2048
+# batches are scanned 1024 queries per launch: 4 query tiles x 18 slabs keeps threshold sharing (j <= 8) on for k <= 128
+MAX_QUERIES_PER_CALL = 1024
 
 
 def metric_code(metric) -> int:
