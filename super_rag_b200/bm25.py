@@ -111,11 +111,8 @@ class Bm25Index:
     # ---- search ----------------------------------------------------------------------------
     def search_terms(self, q_terms: torch.Tensor, k: int):
         """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids)."""
-        if self._ws is None:
-            self._ws = torch.empty(0, dtype=torch.uint8, device=self.device)
-        B = q_terms.shape[0]
-        need = 256 * max(1, -(-self.n_docs // ops.bm25_block_docs())) * k * 8 + 256
-        if self._ws.numel() < need:
+        need = ops.bm25_workspace_bytes(self.n_docs, q_terms.shape[0], k)
+        if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         return ops.bm25_search(self.block_ptr, self.post_doc, self.post_imp, self.n_docs, q_terms, k,
                                id_base=self.id_base, workspace=self._ws)

@@ -19,12 +19,14 @@ namespace {
 constexpr int BM25_BLOCK_DOCS = 16384;  // 64 KB of fp32 accumulators per CTA
 constexpr int BM25_THREADS = 256;
 constexpr int RADIX_BINS = 2048;
-constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots
+constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
+constexpr int BM25_TERM_BATCH = 8;   // query terms whose first posting chunks are prefetched together
 
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
     uint32_t warp_tmp[BM25_THREADS / 32];
+    int64_t t_lo[8], t_hi[8];  // posting range of the current batch of query terms inside this block
     uint32_t sel_bin;
     uint32_t sel_above;
     uint32_t out_count;
@@ -93,72 +95,14 @@ __device__ void radix_pass(Bm25Smem* sm, uint32_t prefix, uint32_t prefix_mask, 
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(BM25_THREADS)
-bm25_block_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
-                  const float* __restrict__ post_imp, int n_blocks, int64_t n_docs,
-                  const int32_t* __restrict__ q_terms, int max_terms, int k, int q_offset,
-                  uint64_t* __restrict__ partial /* [q_chunk][n_blocks][k] */) {
-    extern __shared__ uint8_t bm25_smem_raw[];
-    Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
-    const int blk = blockIdx.x;
-    const int ql = blockIdx.y;  // query index inside this chunk
-    const int q = q_offset + ql;
-    const int32_t doc_base = blk * BM25_BLOCK_DOCS;
-
-    float4* a4 = reinterpret_cast<float4*>(sm->acc);
-    for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (threadIdx.x == 0) { sm->out_count = 0; sm->nonzero = 0; }
-    __syncthreads();
-
-    // ---- term-sequential scatter-accumulate ------------------------------------------------
-    const int32_t* terms = q_terms + (size_t)q * max_terms;
-    for (int j = 0; j < max_terms; ++j) {
-        const int32_t t = terms[j];
-        if (t < 0) continue;  // padding (uniform across the CTA)
-        const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk;
-        const int64_t lo = bp[0], hi = bp[1];
-        // 128-bit body over 4-aligned groups, scalar edges
-        const int64_t g0 = lo & ~(int64_t)3;
-        for (int64_t g = g0 + 4 * (int64_t)threadIdx.x; g < hi; g += 4 * BM25_THREADS) {
-            if (g >= lo && g + 4 <= hi) {
-                const int4 d = __ldg(reinterpret_cast<const int4*>(post_doc + g));
-                const float4 w = __ldg(reinterpret_cast<const float4*>(post_imp + g));
-                float* p0 = &sm->acc[d.x - doc_base];
-                float* p1 = &sm->acc[d.y - doc_base];
-                float* p2 = &sm->acc[d.z - doc_base];
-                float* p3 = &sm->acc[d.w - doc_base];
-                *p0 = __fadd_rn(*p0, w.x);
-                *p1 = __fadd_rn(*p1, w.y);
-                *p2 = __fadd_rn(*p2, w.z);
-                *p3 = __fadd_rn(*p3, w.w);
-            } else {
-                for (int e = 0; e < 4; ++e) {
-                    const int64_t p = g + e;
-                    if (p >= lo && p < hi) {
-                        float* a = &sm->acc[__ldg(post_doc + p) - doc_base];
-                        *a = __fadd_rn(*a, __ldg(post_imp + p));
-                    }
-                }
-            }
-        }
-        __syncthreads();  // next term may touch the same documents
-    }
-
-    // ---- exact block top-k -------------------------------------------------------------------
-    // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
-    uint32_t nz = 0;
-    const int s0 = threadIdx.x * SLOTS_PER_THREAD;
-    for (int i = 0; i < SLOTS_PER_THREAD; i += 4) {
-        const float4 v = *reinterpret_cast<const float4*>(&sm->acc[s0 + i]);
-        nz += (v.x != 0.f) + (v.y != 0.f) + (v.z != 0.f) + (v.w != 0.f);
-    }
-    uint32_t total_nz;
-    (void)block_excl_scan(nz, sm->warp_tmp, &total_nz);
-    uint64_t* out = partial + ((size_t)ql * n_blocks + blk) * k;
-    if (total_nz == 0) return;  // partial is pre-zeroed (= empty keys)
-
-    uint32_t thr_bits = 0;      // k-th largest value; everything above it is taken
+// Exact top-k of the accumulator tile -> k sortable keys at `out` (unordered; finalize sorts).
+// 11/11/10-bit radix select finds the k-th largest value; a tie that straddles position k is
+// resolved towards the lowest doc ids (ordered path, rare).
+__device__ void select_exact(Bm25Smem* sm, int k, int32_t doc_base, uint32_t total_nz, uint64_t* out) {
+    const float4* a4 = reinterpret_cast<const float4*>(sm->acc);
+    uint32_t thr_bits = 0;           // k-th largest value; everything above it is taken
     uint32_t need_eq = 0xFFFFFFFFu;  // how many entries == thr_bits to take (lowest doc ids first)
+    bool ordered = false;
     if (total_nz > (uint32_t)k) {
         radix_pass(sm, 0u, 0u, 21, 0x7FFu, (uint32_t)k);
         const uint32_t b1 = sm->sel_bin, above1 = sm->sel_above;
@@ -171,10 +115,28 @@ bm25_block_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         __syncthreads();
         thr_bits = (b1 << 21) | (b2 << 10) | b3;
         need_eq = (uint32_t)k - above3;
+        // last-level bin == exact value, so its population is the number of entries == thr_bits
+        ordered = sm->hist[b3] > need_eq;
     }
-    // emit: > thr in any order (finalize sorts), == thr in ascending doc order up to need_eq
+    if (!ordered) {
+        // take every entry >= thr_bits (exactly k of them, or all matches when fewer than k): bank-conflict-free
+        const uint32_t lo = thr_bits ? thr_bits : 1u;
+        for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+            const float4 v = a4[i];
+            const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (b[j] >= lo) {
+                    const uint32_t slot = atomicAdd(&sm->out_count, 1u);
+                    if (slot < (uint32_t)k) out[slot] = srag_pack_key(b[j], (uint32_t)(doc_base + 4 * i + j));
+                }
+        }
+        return;
+    }
+    // ordered path: thread t owns 64 consecutive documents, so a prefix sum in thread order is doc order
+    const int s0 = threadIdx.x * SLOTS_PER_THREAD;
     uint32_t eq = 0;
-    for (int i = 0; i < SLOTS_PER_THREAD; ++i) eq += (__float_as_uint(sm->acc[s0 + i]) == thr_bits && thr_bits != 0);
+    for (int i = 0; i < SLOTS_PER_THREAD; ++i) eq += (__float_as_uint(sm->acc[s0 + i]) == thr_bits);
     uint32_t eq_total;
     uint32_t eq_rank = block_excl_scan(eq, sm->warp_tmp, &eq_total);
     for (int i = 0; i < SLOTS_PER_THREAD; ++i) {
@@ -185,6 +147,135 @@ bm25_block_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         if (take) {
             const uint32_t slot = atomicAdd(&sm->out_count, 1u);
             if (slot < (uint32_t)k) out[slot] = srag_pack_key(b, (uint32_t)(doc_base + s0 + i));
+        }
+    }
+}
+
+// One work item = (query, 16384-document block). Persistent CTAs walk the items of one phase:
+//   phase 0  every `stride`-th block of each query, exact block top-k (select_exact);
+//   phase 1  the remaining blocks, filtered by tau[q] = k-th best score over the phase-0 blocks of the
+//            query (a lower bound of its global k-th score): ONE scan of the tile, usually nothing to emit;
+//            a block with more than k entries >= tau falls back to select_exact.
+__global__ void __launch_bounds__(BM25_THREADS, 3)
+bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
+                  const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
+                  int max_terms, int k, int q_offset, int nq, int phase, int stride,
+                  const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
+                  uint64_t* __restrict__ partial /* [nq][n_blocks][k] */) {
+    extern __shared__ uint8_t bm25_smem_raw[];
+    Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
+    const int nb0 = (n_blocks + stride - 1) / stride;
+    const int nbx = phase == 0 ? nb0 : n_blocks - nb0;
+    const long long n_items = (long long)nq * nbx;
+    float4* a4 = reinterpret_cast<float4*>(sm->acc);
+
+    for (long long item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int ql = (int)(item / nbx);
+        const int j = (int)(item - (long long)ql * nbx);
+        const int blk = phase == 0 ? j * stride : j + j / (stride - 1) + 1;
+        const int32_t doc_base = blk * BM25_BLOCK_DOCS;
+        const int32_t* terms = q_terms + (size_t)(q_offset + ql) * max_terms;
+
+        __syncthreads();  // previous item is done with the tile and the term table
+        for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (threadIdx.x == 0) sm->out_count = 0;
+        uint64_t* out = partial + ((size_t)ql * n_blocks + blk) * k;
+
+        // ---- term-sequential scatter-accumulate, 8 terms' first chunks in flight at once ---------
+        for (int j0 = 0; j0 < max_terms; j0 += BM25_TERM_BATCH) {
+            __syncthreads();
+            if (threadIdx.x < BM25_TERM_BATCH) {
+                int64_t lo = 0, hi = 0;
+                const int jj = j0 + threadIdx.x;
+                if (jj < max_terms) {
+                    const int32_t t = terms[jj];
+                    if (t >= 0) {
+                        const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk;
+                        lo = __ldg(bp);
+                        hi = __ldg(bp + 1);
+                    }
+                }
+                sm->t_lo[threadIdx.x] = lo;
+                sm->t_hi[threadIdx.x] = hi;
+            }
+            __syncthreads();
+            int4 d[BM25_TERM_BATCH];
+            float4 w[BM25_TERM_BATCH];
+#pragma unroll
+            for (int u = 0; u < BM25_TERM_BATCH; ++u) {
+                const int64_t lo = sm->t_lo[u], hi = sm->t_hi[u];
+                const int64_t g = (lo & ~(int64_t)3) + 4 * (int64_t)threadIdx.x;
+                if (g < hi) {  // whole aligned group: the arrays are padded, elements outside [lo, hi) are masked below
+                    d[u] = __ldg(reinterpret_cast<const int4*>(post_doc + g));
+                    w[u] = __ldg(reinterpret_cast<const float4*>(post_imp + g));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < BM25_TERM_BATCH; ++u) {
+                const int64_t lo = sm->t_lo[u], hi = sm->t_hi[u];
+                if (lo == hi) continue;  // uniform: padding or a term absent from this block
+                int64_t g = (lo & ~(int64_t)3) + 4 * (int64_t)threadIdx.x;
+                int4 dd = d[u];
+                float4 ww = w[u];
+                while (g < hi) {
+                    const int32_t dv[4] = {dd.x, dd.y, dd.z, dd.w};
+                    const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int64_t pp = g + e;
+                        if (pp >= lo && pp < hi) {
+                            float* a = &sm->acc[dv[e] - doc_base];
+                            *a = __fadd_rn(*a, wv[e]);
+                        }
+                    }
+                    g += 4 * BM25_THREADS;
+                    if (g < hi) {
+                        dd = __ldg(reinterpret_cast<const int4*>(post_doc + g));
+                        ww = __ldg(reinterpret_cast<const float4*>(post_imp + g));
+                    }
+                }
+                __syncthreads();  // the next term may touch the same documents
+            }
+        }
+
+        // ---- selection ---------------------------------------------------------------------------
+        // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
+        uint32_t lo_bits = 1u;
+        if (phase == 1) {
+            const float t = tau[(size_t)ql * k + (k - 1)];
+            if (t > 0.f) lo_bits = __float_as_uint(t);  // ties with the sample's k-th best are kept
+        }
+        uint32_t cnt = 0;
+        for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+            const float4 v = a4[i];
+            cnt += (__float_as_uint(v.x) >= lo_bits) + (__float_as_uint(v.y) >= lo_bits) +
+                   (__float_as_uint(v.z) >= lo_bits) + (__float_as_uint(v.w) >= lo_bits);
+        }
+        uint32_t total;
+        (void)block_excl_scan(cnt, sm->warp_tmp, &total);
+        if (total == 0) continue;  // `partial` is pre-zeroed (= empty keys)
+        if (total <= (uint32_t)k) {
+            for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+                const float4 v = a4[i];
+                const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (b[e] >= lo_bits) {
+                        const uint32_t slot = atomicAdd(&sm->out_count, 1u);
+                        out[slot] = srag_pack_key(b[e], (uint32_t)(doc_base + 4 * i + e));
+                    }
+            }
+        } else {
+            // more than k survivors (always so in phase 0 for a dense block): exact top-k of ALL matches
+            uint32_t nz = 0;
+            if (lo_bits > 1u) {
+                for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+                    const float4 v = a4[i];
+                    nz += (v.x != 0.f) + (v.y != 0.f) + (v.z != 0.f) + (v.w != 0.f);
+                }
+                (void)block_excl_scan(nz, sm->warp_tmp, &total);
+            }
+            select_exact(sm, k, doc_base, total, out);
         }
     }
 }
@@ -268,11 +359,15 @@ extern "C" int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* pos
     return SRAG_OK;
 }
 
+// workspace = per-block lists of one query chunk + the sample top-k (scores, ids) that yields tau
+static size_t bm25_partial_bytes(int qc, int nb, int k) { return (((size_t)qc * nb * k * sizeof(uint64_t)) + 255) & ~(size_t)255; }
+static size_t bm25_tau_bytes(int qc, int k) { return (((size_t)qc * k * (sizeof(float) + sizeof(int64_t))) + 255) & ~(size_t)255; }
+
 extern "C" int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes) {
     SRAG_CHECK_ARG(bytes && n_queries >= 1 && k >= 1 && k <= SRAG_MAX_BM25_K && n_docs >= 0, "bad sizes");
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
-    *bytes = (size_t)qc * nb * k * sizeof(uint64_t) + 256;
+    *bytes = bm25_partial_bytes(qc, nb, k) + bm25_tau_bytes(qc, k) + 256;
     return SRAG_OK;
 }
 
@@ -290,25 +385,47 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
-    const size_t need = (size_t)qc * nb * k * sizeof(uint64_t);
+    const size_t need = bm25_partial_bytes(qc, nb, k) + bm25_tau_bytes(qc, k);
     if (workspace_bytes < need) {
         srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
         return SRAG_E_WORKSPACE;
     }
     static bool attr_done = false;
+    static int sm_count = 0;
     if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(bm25_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)sizeof(Bm25Smem)));
+        int dev = 0;
+        SRAG_CUDA(cudaGetDevice(&dev));
+        SRAG_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
         attr_done = true;
     }
-    uint64_t* partial = reinterpret_cast<uint64_t*>(workspace);
+    uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+    uint64_t* partial = reinterpret_cast<uint64_t*>(ws);
+    float* tau_scores = reinterpret_cast<float*>(ws + bm25_partial_bytes(qc, nb, k));
+    int64_t* tau_ids = reinterpret_cast<int64_t*>(tau_scores + (size_t)qc * k);
+    // sample every 16th block first when there are enough blocks for the sample to be worth a launch
+    const int stride = nb >= 32 ? 16 : 1;
+    const int nb0 = (nb + stride - 1) / stride;
+    const int resident = sm_count * 3;  // 74 KB of shared memory per CTA
     for (int q0 = 0; q0 < n_queries; q0 += qc) {
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
         SRAG_CUDA(cudaMemsetAsync(partial, 0, (size_t)nq * nb * k * sizeof(uint64_t), st));
         if (n_docs > 0) {
-            bm25_block_kernel<<<dim3(nb, nq), BM25_THREADS, sizeof(Bm25Smem), st>>>(
-                block_ptr, post_doc, post_imp, nb, n_docs, q_terms, max_terms, k, q0, partial);
+            const long long items0 = (long long)nq * nb0;
+            const int grid0 = (int)(items0 < resident ? items0 : resident);
+            bm25_items_kernel<<<grid0, BM25_THREADS, sizeof(Bm25Smem), st>>>(
+                block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr, partial);
             SRAG_CUDA(cudaGetLastError());
+            if (stride > 1) {
+                int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, 0, tau_scores, tau_ids, st);
+                if (rc) return rc;
+                const long long items1 = (long long)nq * (nb - nb0);
+                const int grid1 = (int)(items1 < resident ? items1 : resident);
+                bm25_items_kernel<<<grid1, BM25_THREADS, sizeof(Bm25Smem), st>>>(
+                    block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 1, stride, tau_scores, partial);
+                SRAG_CUDA(cudaGetLastError());
+            }
         }
         int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, id_base, out_scores + (size_t)q0 * k,
                                       out_ids + (size_t)q0 * k, st);

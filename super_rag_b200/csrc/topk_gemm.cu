@@ -563,17 +563,46 @@ topk_finalize_kernel(const uint64_t* __restrict__ partial, int total /* lists * 
                      const float* __restrict__ q_scale, int64_t id_base, float* __restrict__ out_scores,
                      int64_t* __restrict__ out_ids) {
     extern __shared__ uint64_t fin_keys[];
+    __shared__ int fin_count;
     const int q = blockIdx.x;
     const uint64_t* src = partial + (size_t)q * total;
     const int chunk = P - kcap;
-    for (int i = threadIdx.x; i < kcap; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
-    for (int off = 0; off < total; off += chunk) {
-        for (int i = threadIdx.x; i < chunk; i += blockDim.x)
-            fin_keys[kcap + i] = (off + i < total) ? src[off + i] : SRAG_KEY_EMPTY;
+    // sparse lists (K2 with a shared threshold leaves most block lists empty): count first; when every
+    // non-empty key fits, compact them and sort ONE small power of two instead of total/chunk passes
+    if (threadIdx.x == 0) fin_count = 0;
+    __syncthreads();
+    int mine = 0;
+    if (total > chunk) {
+        for (int i = threadIdx.x; i < total; i += blockDim.x) mine += (src[i] != SRAG_KEY_EMPTY) ? 1 : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, o);
+        if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&fin_count, mine);
+    }
+    __syncthreads();
+    const int live = fin_count;
+    __syncthreads();
+    if (total > chunk && live <= chunk) {
+        int P2 = 2 * kcap;
+        while (P2 < live + kcap) P2 <<= 1;
+        for (int i = threadIdx.x; i < P2; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
+        if (threadIdx.x == 0) fin_count = 0;
         __syncthreads();
-        block_bitonic_desc(fin_keys, P);
-        for (int i = k + threadIdx.x; i < kcap; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const uint64_t key = src[i];
+            if (key != SRAG_KEY_EMPTY) fin_keys[atomicAdd(&fin_count, 1)] = key;  // order is irrelevant: sorted next
+        }
         __syncthreads();
+        block_bitonic_desc(fin_keys, P2);
+    } else {
+        for (int i = threadIdx.x; i < kcap; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
+        for (int off = 0; off < total; off += chunk) {
+            for (int i = threadIdx.x; i < chunk; i += blockDim.x)
+                fin_keys[kcap + i] = (off + i < total) ? src[off + i] : SRAG_KEY_EMPTY;
+            __syncthreads();
+            block_bitonic_desc(fin_keys, P);
+            for (int i = k + threadIdx.x; i < kcap; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
+            __syncthreads();
+        }
     }
     const float qs = q_scale ? q_scale[q] : 1.0f;
     for (int j = threadIdx.x; j < k; j += blockDim.x) {

@@ -125,6 +125,12 @@ def bm25_block_docs() -> int:
     return _lib.load().srag_bm25_block_docs()
 
 
+def bm25_workspace_bytes(n_docs: int, n_queries: int, k: int) -> int:
+    out = C.c_size_t()
+    _lib.check(_lib.load().srag_bm25_workspace_bytes(n_docs, n_queries, k, C.byref(out)), "srag_bm25_workspace_bytes")
+    return out.value
+
+
 def bm25_impacts(term_ptr, post_doc, post_tf, idf, dl, avgdl: float) -> torch.Tensor:
     _need_cuda(term_ptr, post_doc, post_tf, idf, dl)
     lib = _lib.load()
