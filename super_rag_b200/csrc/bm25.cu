@@ -20,13 +20,14 @@ constexpr int BM25_BLOCK_DOCS = 16384;  // 64 KB of fp32 accumulators per CTA
 constexpr int BM25_THREADS = 256;
 constexpr int RADIX_BINS = 2048;
 constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
-constexpr int BM25_TERM_BATCH = 8;   // query terms whose first posting chunks are prefetched together
+constexpr int BM25_TERM_BATCH = 8;   // query terms handled per prefetch batch
+constexpr int BM25_PF = 8;           // 16-byte posting groups each thread keeps in flight (x2 arrays)
 
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
     uint32_t warp_tmp[BM25_THREADS / 32];
-    int64_t t_lo[8], t_hi[8];  // posting range of the current batch of query terms inside this block
+    int64_t t_lo[2][8], t_hi[2][8];  // posting ranges of a batch of query terms inside the block (double-buffered)
     uint32_t sel_bin;
     uint32_t sel_above;
     uint32_t out_count;
@@ -156,7 +157,7 @@ __device__ void select_exact(Bm25Smem* sm, int k, int32_t doc_base, uint32_t tot
 //   phase 1  the remaining blocks, filtered by tau[q] = k-th best score over the phase-0 blocks of the
 //            query (a lower bound of its global k-th score): ONE scan of the tile, usually nothing to emit;
 //            a block with more than k entries >= tau falls back to select_exact.
-__global__ void __launch_bounds__(BM25_THREADS, 3)
+__global__ void __launch_bounds__(BM25_THREADS, 2)
 bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
                   const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
@@ -169,82 +170,126 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
     const long long n_items = (long long)nq * nbx;
     float4* a4 = reinterpret_cast<float4*>(sm->acc);
 
-    for (long long item = blockIdx.x; item < n_items; item += gridDim.x) {
+    // posting range [lo, hi) inside block `blk` of term slot `threadIdx.x` (< BM25_TERM_BATCH) of batch j0
+    auto fetch_ptrs = [&](long long it, int j0, int64_t& lo, int64_t& hi) {
+        lo = 0;
+        hi = 0;
+        const int jj = j0 + (int)threadIdx.x;
+        if (it < n_items && threadIdx.x < BM25_TERM_BATCH && jj < max_terms) {
+            const int ql_ = (int)(it / nbx);
+            const int j_ = (int)(it - (long long)ql_ * nbx);
+            const int blk_ = phase == 0 ? j_ * stride : j_ + j_ / (stride - 1) + 1;
+            const int32_t t = __ldg(q_terms + (size_t)(q_offset + ql_) * max_terms + jj);
+            if (t >= 0) {
+                const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk_;
+                lo = __ldg(bp);
+                hi = __ldg(bp + 1);
+            }
+        }
+    };
+    // Prefetch: the first 1024-posting chunk of every term of the batch (one aligned group of 4 per thread;
+    // the arrays are padded, elements outside [lo, hi) are masked when applied).
+    int4 d[BM25_TERM_BATCH];
+    float4 w[BM25_TERM_BATCH];
+    auto issue = [&](int buf) {
+#pragma unroll
+        for (int u = 0; u < BM25_TERM_BATCH; ++u) {
+            const int64_t lo = sm->t_lo[buf][u], hi = sm->t_hi[buf][u];
+            const int64_t g = (lo & ~(int64_t)3) + 4 * (int64_t)threadIdx.x;
+            if (g < hi) {
+                d[u] = __ldg(reinterpret_cast<const int4*>(post_doc + g));
+                w[u] = __ldg(reinterpret_cast<const float4*>(post_imp + g));
+            }
+        }
+    };
+    // read-add-write of one aligned group. Inside a term every posting is a distinct document, so the four
+    // shared-memory reads are issued together, then the adds, then the writes (one latency, not four).
+    auto add4 = [&](int rel, int lo_rel, int hi_rel, const int4& dd, const float4& ww, int32_t doc_base) {
+        const bool m0 = rel >= lo_rel && rel < hi_rel, m1 = rel + 1 >= lo_rel && rel + 1 < hi_rel;
+        const bool m2 = rel + 2 >= lo_rel && rel + 2 < hi_rel, m3 = rel + 3 >= lo_rel && rel + 3 < hi_rel;
+        float* p0 = &sm->acc[m0 ? dd.x - doc_base : 0];
+        float* p1 = &sm->acc[m1 ? dd.y - doc_base : 0];
+        float* p2 = &sm->acc[m2 ? dd.z - doc_base : 0];
+        float* p3 = &sm->acc[m3 ? dd.w - doc_base : 0];
+        const float a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
+        if (m0) *p0 = __fadd_rn(a0, ww.x);
+        if (m1) *p1 = __fadd_rn(a1, ww.y);
+        if (m2) *p2 = __fadd_rn(a2, ww.z);
+        if (m3) *p3 = __fadd_rn(a3, ww.w);
+    };
+    // term-sequential accumulate of one batch; a barrier after every term (the next one may touch the same
+    // documents) keeps the per-document summation order = ascending term id
+    auto apply = [&](int buf, int32_t doc_base) {
+#pragma unroll
+        for (int u = 0; u < BM25_TERM_BATCH; ++u) {
+            const int64_t lo = sm->t_lo[buf][u], hi = sm->t_hi[buf][u];
+            if (lo == hi) continue;  // uniform: padding or a term absent from this block
+            const int64_t a = lo & ~(int64_t)3;
+            const int lo_rel = (int)(lo - a), hi_rel = (int)(hi - a);  // a block slice holds < 2^31 postings
+            int rel = 4 * (int)threadIdx.x;
+            if (rel < hi_rel) add4(rel, lo_rel, hi_rel, d[u], w[u], doc_base);
+            // longer slices: two more chunks per trip, both loads in flight together
+            for (rel += 4 * BM25_THREADS; rel < hi_rel; rel += 8 * BM25_THREADS) {
+                const int rel2 = rel + 4 * BM25_THREADS;
+                const int4 d1 = __ldg(reinterpret_cast<const int4*>(post_doc + a + rel));
+                const float4 w1 = __ldg(reinterpret_cast<const float4*>(post_imp + a + rel));
+                int4 d2 = make_int4(0, 0, 0, 0);
+                float4 w2 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (rel2 < hi_rel) {
+                    d2 = __ldg(reinterpret_cast<const int4*>(post_doc + a + rel2));
+                    w2 = __ldg(reinterpret_cast<const float4*>(post_imp + a + rel2));
+                }
+                add4(rel, lo_rel, hi_rel, d1, w1, doc_base);
+                if (rel2 < hi_rel) add4(rel2, lo_rel, hi_rel, d2, w2, doc_base);
+            }
+            __syncthreads();
+        }
+    };
+
+    long long item = blockIdx.x;
+    if (item >= n_items) return;
+    {
+        int64_t lo, hi;
+        fetch_ptrs(item, 0, lo, hi);
+        if (threadIdx.x < BM25_TERM_BATCH) { sm->t_lo[0][threadIdx.x] = lo; sm->t_hi[0][threadIdx.x] = hi; }
+    }
+    __syncthreads();
+    issue(0);
+    int cur = 0;
+    // Software pipeline: while item i is selected, the postings of item i+1 (first batch of terms) are
+    // already in flight, so HBM stays busy through the shared-memory phases.
+    for (; item < n_items; item += gridDim.x, cur ^= 1) {
         const int ql = (int)(item / nbx);
         const int j = (int)(item - (long long)ql * nbx);
         const int blk = phase == 0 ? j * stride : j + j / (stride - 1) + 1;
         const int32_t doc_base = blk * BM25_BLOCK_DOCS;
-        const int32_t* terms = q_terms + (size_t)(q_offset + ql) * max_terms;
-
-        __syncthreads();  // previous item is done with the tile and the term table
-        for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (threadIdx.x == 0) sm->out_count = 0;
         uint64_t* out = partial + ((size_t)ql * n_blocks + blk) * k;
 
-        // ---- term-sequential scatter-accumulate, 8 terms' first chunks in flight at once ---------
-        for (int j0 = 0; j0 < max_terms; j0 += BM25_TERM_BATCH) {
+        const float tau_q = phase == 1 ? __ldg(tau + (size_t)ql * k + (k - 1)) : 0.f;
+        __syncthreads();  // previous item is done with the tile
+        for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (threadIdx.x == 0) sm->out_count = 0;
+        int64_t nlo, nhi;
+        fetch_ptrs(item + gridDim.x, 0, nlo, nhi);  // in flight while this item accumulates
+        __syncthreads();
+        apply(cur, doc_base);
+        for (int j0 = BM25_TERM_BATCH; j0 < max_terms; j0 += BM25_TERM_BATCH) {  // queries with more than 8 terms
+            int64_t lo, hi;
+            fetch_ptrs(item, j0, lo, hi);
             __syncthreads();
-            if (threadIdx.x < BM25_TERM_BATCH) {
-                int64_t lo = 0, hi = 0;
-                const int jj = j0 + threadIdx.x;
-                if (jj < max_terms) {
-                    const int32_t t = terms[jj];
-                    if (t >= 0) {
-                        const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk;
-                        lo = __ldg(bp);
-                        hi = __ldg(bp + 1);
-                    }
-                }
-                sm->t_lo[threadIdx.x] = lo;
-                sm->t_hi[threadIdx.x] = hi;
-            }
+            if (threadIdx.x < BM25_TERM_BATCH) { sm->t_lo[cur][threadIdx.x] = lo; sm->t_hi[cur][threadIdx.x] = hi; }
             __syncthreads();
-            int4 d[BM25_TERM_BATCH];
-            float4 w[BM25_TERM_BATCH];
-#pragma unroll
-            for (int u = 0; u < BM25_TERM_BATCH; ++u) {
-                const int64_t lo = sm->t_lo[u], hi = sm->t_hi[u];
-                const int64_t g = (lo & ~(int64_t)3) + 4 * (int64_t)threadIdx.x;
-                if (g < hi) {  // whole aligned group: the arrays are padded, elements outside [lo, hi) are masked below
-                    d[u] = __ldg(reinterpret_cast<const int4*>(post_doc + g));
-                    w[u] = __ldg(reinterpret_cast<const float4*>(post_imp + g));
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < BM25_TERM_BATCH; ++u) {
-                const int64_t lo = sm->t_lo[u], hi = sm->t_hi[u];
-                if (lo == hi) continue;  // uniform: padding or a term absent from this block
-                int64_t g = (lo & ~(int64_t)3) + 4 * (int64_t)threadIdx.x;
-                int4 dd = d[u];
-                float4 ww = w[u];
-                while (g < hi) {
-                    const int32_t dv[4] = {dd.x, dd.y, dd.z, dd.w};
-                    const float wv[4] = {ww.x, ww.y, ww.z, ww.w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const int64_t pp = g + e;
-                        if (pp >= lo && pp < hi) {
-                            float* a = &sm->acc[dv[e] - doc_base];
-                            *a = __fadd_rn(*a, wv[e]);
-                        }
-                    }
-                    g += 4 * BM25_THREADS;
-                    if (g < hi) {
-                        dd = __ldg(reinterpret_cast<const int4*>(post_doc + g));
-                        ww = __ldg(reinterpret_cast<const float4*>(post_imp + g));
-                    }
-                }
-                __syncthreads();  // the next term may touch the same documents
-            }
+            issue(cur);
+            apply(cur, doc_base);
         }
+        if (threadIdx.x < BM25_TERM_BATCH) { sm->t_lo[cur ^ 1][threadIdx.x] = nlo; sm->t_hi[cur ^ 1][threadIdx.x] = nhi; }
+        __syncthreads();
+        issue(cur ^ 1);
 
         // ---- selection ---------------------------------------------------------------------------
         // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
         uint32_t lo_bits = 1u;
-        if (phase == 1) {
-            const float t = tau[(size_t)ql * k + (k - 1)];
-            if (t > 0.f) lo_bits = __float_as_uint(t);  // ties with the sample's k-th best are kept
-        }
+        if (tau_q > 0.f) lo_bits = __float_as_uint(tau_q);  // ties with the sample's k-th best are kept
         uint32_t cnt = 0;
         for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
             const float4 v = a4[i];
@@ -253,8 +298,9 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         }
         uint32_t total;
         (void)block_excl_scan(cnt, sm->warp_tmp, &total);
-        if (total == 0) continue;  // `partial` is pre-zeroed (= empty keys)
-        if (total <= (uint32_t)k) {
+        if (total == 0) {
+            // nothing to emit: `partial` is pre-zeroed (= empty keys)
+        } else if (total <= (uint32_t)k) {
             for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
                 const float4 v = a4[i];
                 const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
@@ -323,7 +369,7 @@ __global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, co
 }
 
 int bm25_blocks(int64_t n_docs) { return (int)((n_docs + BM25_BLOCK_DOCS - 1) / BM25_BLOCK_DOCS); }
-constexpr int BM25_Q_CHUNK = 256;  // queries whose per-block lists are resident at once
+constexpr int BM25_Q_CHUNK = 1024;  // queries whose per-block lists are resident at once (0.5 GB at 10 M docs, k = 100)
 
 }  // namespace
 
@@ -407,7 +453,7 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     // sample every 16th block first when there are enough blocks for the sample to be worth a launch
     const int stride = nb >= 32 ? 16 : 1;
     const int nb0 = (nb + stride - 1) / stride;
-    const int resident = sm_count * 3;  // 74 KB of shared memory per CTA
+    const int resident = sm_count * 2;  // 128 registers x 256 threads per CTA (posting prefetch lives in registers)
     for (int q0 = 0; q0 < n_queries; q0 += qc) {
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
         SRAG_CUDA(cudaMemsetAsync(partial, 0, (size_t)nq * nb * k * sizeof(uint64_t), st));
