@@ -52,6 +52,11 @@ class ShardedVectorIndex:
     def __init__(self, rows_bf16: torch.Tensor, row_scale: torch.Tensor, id_base: int, metric="cosine", group=None):
         from . import ops
         self.ops = ops
+        # the kernels want 16-byte aligned bases; a row slice of a larger tensor need not be
+        if rows_bf16.data_ptr() % 16 or not rows_bf16.is_contiguous():
+            rows_bf16 = rows_bf16.clone(memory_format=torch.contiguous_format)
+        if row_scale.data_ptr() % 16 or not row_scale.is_contiguous():
+            row_scale = row_scale.clone(memory_format=torch.contiguous_format)
         self.rows, self.row_scale, self.id_base = rows_bf16, row_scale, int(id_base)
         self.metric = ops.metric_code(metric)
         self.group = group

@@ -1,0 +1,80 @@
+#!/usr/bin/env python
+"""N-GPU parity check over NCCL (run under torchrun on a multi-GPU box):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29533 tools/check_sharded_nccl.py
+
+Every rank builds the same seeded corpus, keeps only its row shard, and the sharded search
+(K1 per shard -> NCCL all-gather -> K4 merge) must return, on every rank, bit-identical ids and scores
+to rank 0's single-GPU scan of the whole corpus. Also checks BM25 doc-range shards with global
+statistics against the single-GPU index.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from super_rag_b200 import ops  # noqa: E402
+from super_rag_b200.bm25 import Bm25Index, Bm25Stats  # noqa: E402
+from super_rag_b200.sharded import ShardedVectorIndex, exchange_candidates, shard_range  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    n, d, b, k = 200_003, 1024, 300, 10
+    g = torch.Generator(device=dev)
+    g.manual_seed(7)
+    C = torch.randn(n, d, generator=g, device=dev)
+    Q = torch.randn(b, d, generator=g, device=dev)
+    Q[:b // 2] = C[torch.randint(0, n, (b // 2,), generator=g, device=dev)] + 0.1 * Q[:b // 2]
+    C[150_000] = C[11]                      # a tie across shards
+    Q[0] = C[11]
+    cb, cs = ops.ingest_rows(C, "cosine")
+    lo, hi = shard_range(n, world, rank)
+    index = ShardedVectorIndex(cb[lo:hi].contiguous(), cs[lo:hi].contiguous(), id_base=lo)
+    s, i = index.search_batch(Q, k)
+    qb, qs = ops.ingest_rows(Q, "cosine")
+    fs, fi = ops.topk_search(cb, cs, qb, qs, k)
+    torch.cuda.synchronize()
+    ok_v = bool(torch.equal(i, fi)) and bool(torch.equal(s.view(torch.int32), fs.view(torch.int32)))
+    assert i[0, 0].item() == 11 and i[0, 1].item() == 150_000
+
+    # BM25: doc-range shards with GLOBAL statistics == single index
+    n_docs, vocab = 120_000, 3000
+    rng = np.random.default_rng(3)
+    dl = rng.integers(20, 80, n_docs)
+    p = 1.0 / np.arange(1, vocab + 1)
+    tokens = rng.choice(vocab, size=int(dl.sum()), p=p / p.sum()).astype(np.int64)
+    doc_ptr = np.concatenate([[0], np.cumsum(dl)]).astype(np.int64)
+    full = Bm25Index.from_tokens(torch.from_numpy(tokens).to(dev), torch.from_numpy(doc_ptr).to(dev), vocab)
+    dlo, dhi = shard_range(n_docs, world, rank)
+    t_lo, t_hi = int(doc_ptr[dlo]), int(doc_ptr[dhi])
+    stats = Bm25Stats(n_docs=n_docs, df=full.stats.df, avgdl=full.stats.avgdl)
+    shard = Bm25Index.from_tokens(torch.from_numpy(tokens[t_lo:t_hi]).to(dev),
+                                  torch.from_numpy(doc_ptr[dlo:dhi + 1] - t_lo).to(dev), vocab, stats=stats, id_base=dlo)
+    queries = [rng.integers(0, vocab, 6).tolist() for _ in range(64)]
+    ls, li = shard.search(queries, 20)
+    gs, gi = exchange_candidates(ls, li)
+    ms, mi = ops.merge_candidates(gs, gi, 20)
+    ws, wi = full.search(queries, 20)
+    torch.cuda.synchronize()
+    ok_b = bool(torch.equal(mi, wi)) and bool(torch.equal(ms.view(torch.int32), ws.view(torch.int32)))
+
+    flags = torch.tensor([int(ok_v), int(ok_b)], device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print(f"world={world} vector_sharded_equals_single={bool(flags[0].item())} "
+              f"bm25_sharded_equals_single={bool(flags[1].item())}", flush=True)
+    dist.destroy_process_group()
+    if not (flags[0].item() and flags[1].item()):
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()
