@@ -12,6 +12,8 @@
 //
 // Algorithmic bytes per query = 8 * sum_t df(t)  (int32 doc + fp32 impact per posting).
 // The reference has no BM25 arithmetic; contract: oracle/bm25.py docstring.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -23,6 +25,8 @@ constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguo
 constexpr int BM25_TERM_BATCH = 8;   // query terms handled per prefetch batch
 constexpr int BM25_PF = 8;           // 16-byte posting groups each thread keeps in flight (x2 arrays)
 
+constexpr int BM25_CAND_MAX = 1024;
+
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
@@ -32,6 +36,8 @@ struct Bm25Smem {
     uint32_t sel_above;
     uint32_t out_count;
     uint32_t nonzero;
+    uint32_t cand_count;              // documents whose accumulator crossed tau while terms were applied
+    uint16_t cand[BM25_CAND_MAX];     // their offsets inside the block
 };
 
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_tmp, uint32_t* total) {
@@ -162,7 +168,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                   const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
                   const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
-                  uint64_t* __restrict__ partial /* [nq][n_blocks][k] */) {
+                  uint64_t* __restrict__ partial /* [nq][n_blocks][k] */, int debug /* SRAG_BM25_DEBUG, timing dissection only */) {
     extern __shared__ uint8_t bm25_smem_raw[];
     Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
     const int nb0 = (n_blocks + stride - 1) / stride;
@@ -204,18 +210,34 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
     };
     // read-add-write of one aligned group. Inside a term every posting is a distinct document, so the four
     // shared-memory reads are issued together, then the adds, then the writes (one latency, not four).
+    // Impacts are > 0, so an accumulator only grows and crosses tau at most once: the add that takes it
+    // from below tau to >= tau records the document (cross_bits = 0xFFFFFFFF disables this).
+    uint32_t cross_bits = 0xFFFFFFFFu;
     auto add4 = [&](int rel, int lo_rel, int hi_rel, const int4& dd, const float4& ww, int32_t doc_base) {
         const bool m0 = rel >= lo_rel && rel < hi_rel, m1 = rel + 1 >= lo_rel && rel + 1 < hi_rel;
         const bool m2 = rel + 2 >= lo_rel && rel + 2 < hi_rel, m3 = rel + 3 >= lo_rel && rel + 3 < hi_rel;
-        float* p0 = &sm->acc[m0 ? dd.x - doc_base : 0];
-        float* p1 = &sm->acc[m1 ? dd.y - doc_base : 0];
-        float* p2 = &sm->acc[m2 ? dd.z - doc_base : 0];
-        float* p3 = &sm->acc[m3 ? dd.w - doc_base : 0];
-        const float a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
-        if (m0) *p0 = __fadd_rn(a0, ww.x);
-        if (m1) *p1 = __fadd_rn(a1, ww.y);
-        if (m2) *p2 = __fadd_rn(a2, ww.z);
-        if (m3) *p3 = __fadd_rn(a3, ww.w);
+        const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
+        const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
+        const float a0 = sm->acc[r0], a1 = sm->acc[r1], a2 = sm->acc[r2], a3 = sm->acc[r3];
+        const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y), n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
+        if (m0) sm->acc[r0] = n0;
+        if (m1) sm->acc[r1] = n1;
+        if (m2) sm->acc[r2] = n2;
+        if (m3) sm->acc[r3] = n3;
+        const bool c0 = m0 && __float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits;
+        const bool c1 = m1 && __float_as_uint(n1) >= cross_bits && __float_as_uint(a1) < cross_bits;
+        const bool c2 = m2 && __float_as_uint(n2) >= cross_bits && __float_as_uint(a2) < cross_bits;
+        const bool c3 = m3 && __float_as_uint(n3) >= cross_bits && __float_as_uint(a3) < cross_bits;
+        if (c0 | c1 | c2 | c3) {
+            const int rr[4] = {r0, r1, r2, r3};
+            const bool cc[4] = {c0, c1, c2, c3};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (cc[e]) {
+                    const uint32_t slot = atomicAdd(&sm->cand_count, 1u);
+                    if (slot < (uint32_t)BM25_CAND_MAX) sm->cand[slot] = (uint16_t)rr[e];
+                }
+        }
     };
     // term-sequential accumulate of one batch; a barrier after every term (the next one may touch the same
     // documents) keeps the per-document summation order = ascending term id
@@ -227,9 +249,9 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             const int64_t a = lo & ~(int64_t)3;
             const int lo_rel = (int)(lo - a), hi_rel = (int)(hi - a);  // a block slice holds < 2^31 postings
             int rel = 4 * (int)threadIdx.x;
-            if (rel < hi_rel) add4(rel, lo_rel, hi_rel, d[u], w[u], doc_base);
+            if (rel < hi_rel && !(debug & 1)) add4(rel, lo_rel, hi_rel, d[u], w[u], doc_base);
             // longer slices: two more chunks per trip, both loads in flight together
-            for (rel += 4 * BM25_THREADS; rel < hi_rel; rel += 8 * BM25_THREADS) {
+            for (rel += 4 * BM25_THREADS; rel < hi_rel && !(debug & 8); rel += 8 * BM25_THREADS) {
                 const int rel2 = rel + 4 * BM25_THREADS;
                 const int4 d1 = __ldg(reinterpret_cast<const int4*>(post_doc + a + rel));
                 const float4 w1 = __ldg(reinterpret_cast<const float4*>(post_imp + a + rel));
@@ -267,8 +289,12 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
 
         const float tau_q = phase == 1 ? __ldg(tau + (size_t)ql * k + (k - 1)) : 0.f;
         __syncthreads();  // previous item is done with the tile
+        if (!(debug & 4))
         for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (threadIdx.x == 0) sm->out_count = 0;
+        if (threadIdx.x == 0) { sm->out_count = 0; sm->cand_count = 0; }
+        // phase 1 with a full sample: candidates are collected while accumulating, no scan of the tile
+        const bool track = tau_q > 0.f && !(debug & 16);
+        cross_bits = track ? __float_as_uint(tau_q) : 0xFFFFFFFFu;
         int64_t nlo, nhi;
         fetch_ptrs(item + gridDim.x, 0, nlo, nhi);  // in flight while this item accumulates
         __syncthreads();
@@ -290,7 +316,18 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
         uint32_t lo_bits = 1u;
         if (tau_q > 0.f) lo_bits = __float_as_uint(tau_q);  // ties with the sample's k-th best are kept
+        if (track) {
+            const uint32_t nc = sm->cand_count;  // final: every term ended with a barrier
+            if (nc <= (uint32_t)k && nc <= (uint32_t)BM25_CAND_MAX) {
+                if (threadIdx.x < nc) {
+                    const uint32_t r = sm->cand[threadIdx.x];
+                    out[threadIdx.x] = srag_pack_key(__float_as_uint(sm->acc[r]), (uint32_t)(doc_base + r));
+                }
+                continue;
+            }
+        }
         uint32_t cnt = 0;
+        if (!(debug & 2))
         for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
             const float4 v = a4[i];
             cnt += (__float_as_uint(v.x) >= lo_bits) + (__float_as_uint(v.y) >= lo_bits) +
@@ -453,6 +490,8 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     // sample every 16th block first when there are enough blocks for the sample to be worth a launch
     const int stride = nb >= 32 ? 16 : 1;
     const int nb0 = (nb + stride - 1) / stride;
+    const char* dbg_env = getenv("SRAG_BM25_DEBUG");
+    const int dbg = dbg_env ? atoi(dbg_env) : 0;
     const int resident = sm_count * 2;  // 128 registers x 256 threads per CTA (posting prefetch lives in registers)
     for (int q0 = 0; q0 < n_queries; q0 += qc) {
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
@@ -461,7 +500,7 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
             bm25_items_kernel<<<grid0, BM25_THREADS, sizeof(Bm25Smem), st>>>(
-                block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr, partial);
+                block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr, partial, dbg);
             SRAG_CUDA(cudaGetLastError());
             if (stride > 1) {
                 int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, 0, tau_scores, tau_ids, st);
@@ -469,7 +508,7 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
                 const long long items1 = (long long)nq * (nb - nb0);
                 const int grid1 = (int)(items1 < resident ? items1 : resident);
                 bm25_items_kernel<<<grid1, BM25_THREADS, sizeof(Bm25Smem), st>>>(
-                    block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 1, stride, tau_scores, partial);
+                    block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 1, stride, tau_scores, partial, dbg);
                 SRAG_CUDA(cudaGetLastError());
             }
         }
