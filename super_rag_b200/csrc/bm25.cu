@@ -22,16 +22,34 @@ constexpr int BM25_BLOCK_DOCS = 16384;  // 64 KB of fp32 accumulators per CTA
 constexpr int BM25_THREADS = 256;
 constexpr int RADIX_BINS = 2048;
 constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
-constexpr int BM25_TERM_BATCH = 8;   // query terms handled per prefetch batch
-constexpr int BM25_PF = 8;           // 16-byte posting groups each thread keeps in flight (x2 arrays)
-
+constexpr int BM25_CTA_THREADS = BM25_THREADS + 32;  // 8 consumer warps + 1 producer warp
+constexpr int BM25_SLOT_POSTINGS = 1024;             // one ring slot: 4 KB of doc ids + 4 KB of impacts
+constexpr int BM25_SLOTS = 4;
 constexpr int BM25_CAND_MAX = 1024;
+
+// stream flags of a ring slot
+constexpr uint32_t SLOT_NEW_ITEM = 1u;  // first chunk of a (query, block) item
+constexpr uint32_t SLOT_NEW_TERM = 2u;  // first chunk of a term (not the item's first term)
+constexpr uint32_t SLOT_END = 4u;       // no data: the CTA's item list is exhausted
+
+struct SlotMeta {  // written by the producer before it issues the slot's copies
+    int32_t ql, blk;         // query (inside the chunk) and document block
+    int32_t lo_rel, hi_rel;  // valid postings of the slot: [lo_rel, hi_rel)
+    uint32_t flags;
+    float tau;               // sample k-th best score of the query (0 = none)
+    int32_t pad[2];
+};
+
+__device__ __forceinline__ void consumer_sync() { ptx::named_bar_sync(1, BM25_THREADS); }
 
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
+    alignas(128) int32_t slot_doc[BM25_SLOTS][BM25_SLOT_POSTINGS];
+    alignas(128) float slot_imp[BM25_SLOTS][BM25_SLOT_POSTINGS];
+    SlotMeta meta[BM25_SLOTS];
+    uint64_t full[BM25_SLOTS], empty[BM25_SLOTS];
     uint32_t warp_tmp[BM25_THREADS / 32];
-    int64_t t_lo[2][8], t_hi[2][8];  // posting ranges of a batch of query terms inside the block (double-buffered)
     uint32_t sel_bin;
     uint32_t sel_above;
     uint32_t out_count;
@@ -49,9 +67,9 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_t
         const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
         if (lane >= o) inc += t;
     }
-    __syncthreads();  // protect warp_tmp reuse
+    consumer_sync();  // protect warp_tmp reuse
     if (lane == 31) warp_tmp[w] = inc;
-    __syncthreads();
+    consumer_sync();
     uint32_t base = 0, tot = 0;
 #pragma unroll
     for (int i = 0; i < BM25_THREADS / 32; ++i) {
@@ -69,7 +87,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_t
 __device__ void radix_pass(Bm25Smem* sm, uint32_t prefix, uint32_t prefix_mask, int shift, uint32_t mask,
                            uint32_t want) {
     for (int i = threadIdx.x; i < RADIX_BINS; i += BM25_THREADS) sm->hist[i] = 0;
-    __syncthreads();
+    consumer_sync();
     const float4* a4 = reinterpret_cast<const float4*>(sm->acc);
     for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
         const float4 v = a4[i];
@@ -78,7 +96,7 @@ __device__ void radix_pass(Bm25Smem* sm, uint32_t prefix, uint32_t prefix_mask, 
         for (int j = 0; j < 4; ++j)
             if (b[j] != 0 && (b[j] & prefix_mask) == prefix) atomicAdd(&sm->hist[(b[j] >> shift) & mask], 1u);
     }
-    __syncthreads();
+    consumer_sync();
     // suffix scan from the top bin: thread t owns bins [2047 - 8t - 7, 2047 - 8t]
     constexpr int PER = RADIX_BINS / BM25_THREADS;
     uint32_t mine = 0;
@@ -99,7 +117,7 @@ __device__ void radix_pass(Bm25Smem* sm, uint32_t prefix, uint32_t prefix_mask, 
             run += h;
         }
     }
-    __syncthreads();
+    consumer_sync();
 }
 
 // Exact top-k of the accumulator tile -> k sortable keys at `out` (unordered; finalize sorts).
@@ -113,13 +131,13 @@ __device__ void select_exact(Bm25Smem* sm, int k, int32_t doc_base, uint32_t tot
     if (total_nz > (uint32_t)k) {
         radix_pass(sm, 0u, 0u, 21, 0x7FFu, (uint32_t)k);
         const uint32_t b1 = sm->sel_bin, above1 = sm->sel_above;
-        __syncthreads();
+        consumer_sync();
         radix_pass(sm, b1 << 21, 0xFFE00000u, 10, 0x7FFu, (uint32_t)k - above1);
         const uint32_t b2 = sm->sel_bin, above2 = above1 + sm->sel_above;
-        __syncthreads();
+        consumer_sync();
         radix_pass(sm, (b1 << 21) | (b2 << 10), 0xFFFFFC00u, 0, 0x3FFu, (uint32_t)k - above2);
         const uint32_t b3 = sm->sel_bin, above3 = above2 + sm->sel_above;
-        __syncthreads();
+        consumer_sync();
         thr_bits = (b1 << 21) | (b2 << 10) | b3;
         need_eq = (uint32_t)k - above3;
         // last-level bin == exact value, so its population is the number of entries == thr_bits
@@ -161,173 +179,161 @@ __device__ void select_exact(Bm25Smem* sm, int k, int32_t doc_base, uint32_t tot
 // One work item = (query, 16384-document block). Persistent CTAs walk the items of one phase:
 //   phase 0  every `stride`-th block of each query, exact block top-k (select_exact);
 //   phase 1  the remaining blocks, filtered by tau[q] = k-th best score over the phase-0 blocks of the
-//            query (a lower bound of its global k-th score): ONE scan of the tile, usually nothing to emit;
-//            a block with more than k entries >= tau falls back to select_exact.
-__global__ void __launch_bounds__(BM25_THREADS, 2)
+//            query (a lower bound of its global k-th score): documents crossing tau are recorded while
+//            the terms are applied, so usually there is nothing to scan and nothing to emit; a block
+//            with more than k entries >= tau falls back to select_exact.
+//
+// Warp 8 is the PRODUCER: it walks the CTA's items, looks up the posting slice of every query term inside
+// the block (block_ptr) and streams the slices, in ascending-term order and cut into chunks of at most
+// 1024 postings, through a ring of shared-memory slots with 1-D bulk copies (cp.async.bulk + mbarrier
+// complete_tx). It runs as far ahead as the ring allows, across item boundaries, so HBM requests stay
+// in flight while the consumers zero, accumulate and select.
+// Warps 0..7 are the CONSUMERS: they follow the slot stream; the slot's metadata says where an item or a
+// term starts. A barrier separates terms (two terms may hit the same document; inside a term every
+// posting is a distinct document), which keeps the per-document summation order = ascending term id.
+__global__ void __launch_bounds__(BM25_CTA_THREADS, 2)
 bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
                   const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
                   const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
-                  uint64_t* __restrict__ partial /* [nq][n_blocks][k] */, int debug /* SRAG_BM25_DEBUG, timing dissection only */) {
+                  uint64_t* __restrict__ partial /* [nq][n_blocks][k] */, int debug /* SRAG_BM25_DEBUG */) {
     extern __shared__ uint8_t bm25_smem_raw[];
     Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
     const int nb0 = (n_blocks + stride - 1) / stride;
     const int nbx = phase == 0 ? nb0 : n_blocks - nb0;
     const long long n_items = (long long)nq * nbx;
-    float4* a4 = reinterpret_cast<float4*>(sm->acc);
+    const int lane = threadIdx.x & 31;
 
-    // posting range [lo, hi) inside block `blk` of term slot `threadIdx.x` (< BM25_TERM_BATCH) of batch j0
-    auto fetch_ptrs = [&](long long it, int j0, int64_t& lo, int64_t& hi) {
-        lo = 0;
-        hi = 0;
-        const int jj = j0 + (int)threadIdx.x;
-        if (it < n_items && threadIdx.x < BM25_TERM_BATCH && jj < max_terms) {
-            const int ql_ = (int)(it / nbx);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < BM25_SLOTS; ++s) {
+            ptx::mbar_init(&sm->full[s], 1);
+            ptx::mbar_init(&sm->empty[s], BM25_THREADS / 32);
+        }
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (threadIdx.x >= BM25_THREADS) {
+        // ------------------------------ producer warp ------------------------------------------
+        auto item_blk = [&](long long it, int& ql_, int& blk_) {
+            ql_ = (int)(it / nbx);
             const int j_ = (int)(it - (long long)ql_ * nbx);
-            const int blk_ = phase == 0 ? j_ * stride : j_ + j_ / (stride - 1) + 1;
-            const int32_t t = __ldg(q_terms + (size_t)(q_offset + ql_) * max_terms + jj);
-            if (t >= 0) {
+            blk_ = phase == 0 ? j_ * stride : j_ + j_ / (stride - 1) + 1;
+        };
+        // lane l looks after term slot j0 + l of the query
+        auto term_at = [&](long long it, int j0, float& tq) -> int32_t {
+            tq = 0.f;
+            if (it >= n_items) return -1;
+            int ql_, blk_;
+            item_blk(it, ql_, blk_);
+            if (phase == 1) tq = __ldg(tau + (size_t)ql_ * k + (k - 1));
+            return j0 + lane < max_terms ? __ldg(q_terms + (size_t)(q_offset + ql_) * max_terms + j0 + lane) : -1;
+        };
+        auto ptrs_at = [&](long long it, int32_t t, int64_t& lo, int64_t& hi) {
+            lo = 0;
+            hi = 0;
+            if (it < n_items && t >= 0) {
+                int ql_, blk_;
+                item_blk(it, ql_, blk_);
                 const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk_;
                 lo = __ldg(bp);
                 hi = __ldg(bp + 1);
             }
-        }
-    };
-    // Prefetch: the first 1024-posting chunk of every term of the batch (one aligned group of 4 per thread;
-    // the arrays are padded, elements outside [lo, hi) are masked when applied).
-    int4 d[BM25_TERM_BATCH];
-    float4 w[BM25_TERM_BATCH];
-    auto issue = [&](int buf) {
-#pragma unroll
-        for (int u = 0; u < BM25_TERM_BATCH; ++u) {
-            const int64_t lo = sm->t_lo[buf][u], hi = sm->t_hi[buf][u];
-            const int64_t g = (lo & ~(int64_t)3) + 4 * (int64_t)threadIdx.x;
-            if (g < hi) {
-                d[u] = __ldg(reinterpret_cast<const int4*>(post_doc + g));
-                w[u] = __ldg(reinterpret_cast<const float4*>(post_imp + g));
-            }
-        }
-    };
-    // read-add-write of one aligned group. Inside a term every posting is a distinct document, so the four
-    // shared-memory reads are issued together, then the adds, then the writes (one latency, not four).
-    // Impacts are > 0, so an accumulator only grows and crosses tau at most once: the add that takes it
-    // from below tau to >= tau records the document (cross_bits = 0xFFFFFFFF disables this).
-    uint32_t cross_bits = 0xFFFFFFFFu;
-    auto add4 = [&](int rel, int lo_rel, int hi_rel, const int4& dd, const float4& ww, int32_t doc_base) {
-        const bool m0 = rel >= lo_rel && rel < hi_rel, m1 = rel + 1 >= lo_rel && rel + 1 < hi_rel;
-        const bool m2 = rel + 2 >= lo_rel && rel + 2 < hi_rel, m3 = rel + 3 >= lo_rel && rel + 3 < hi_rel;
-        const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
-        const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
-        const float a0 = sm->acc[r0], a1 = sm->acc[r1], a2 = sm->acc[r2], a3 = sm->acc[r3];
-        const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y), n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
-        if (m0) sm->acc[r0] = n0;
-        if (m1) sm->acc[r1] = n1;
-        if (m2) sm->acc[r2] = n2;
-        if (m3) sm->acc[r3] = n3;
-        const bool c0 = m0 && __float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits;
-        const bool c1 = m1 && __float_as_uint(n1) >= cross_bits && __float_as_uint(a1) < cross_bits;
-        const bool c2 = m2 && __float_as_uint(n2) >= cross_bits && __float_as_uint(a2) < cross_bits;
-        const bool c3 = m3 && __float_as_uint(n3) >= cross_bits && __float_as_uint(a3) < cross_bits;
-        if (c0 | c1 | c2 | c3) {
-            const int rr[4] = {r0, r1, r2, r3};
-            const bool cc[4] = {c0, c1, c2, c3};
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                if (cc[e]) {
-                    const uint32_t slot = atomicAdd(&sm->cand_count, 1u);
-                    if (slot < (uint32_t)BM25_CAND_MAX) sm->cand[slot] = (uint16_t)rr[e];
+        };
+        uint32_t slot = 0, par = 0;  // ring position and its phase parity
+        auto next_slot = [&]() {
+            if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
+        };
+        const long long G = gridDim.x;
+        long long item = blockIdx.x;
+        // two-deep lookahead so that neither dependent load (term id -> slice bounds) is waited for
+        float tau0, tau1, tau2;
+        int64_t lo, hi, nlo, nhi;
+        int32_t t0 = term_at(item, 0, tau0);
+        int32_t t1 = term_at(item + G, 0, tau1);
+        int32_t t2 = term_at(item + 2 * G, 0, tau2);
+        ptrs_at(item, t0, lo, hi);
+        ptrs_at(item + G, t1, nlo, nhi);
+        for (; item < n_items; item += G) {
+            int ql, blk;
+            item_blk(item, ql, blk);
+            bool first_of_item = true;
+            for (int j0 = 0; j0 < max_terms; j0 += 32) {
+                if (j0 > 0) {  // queries with more than 32 terms: fetched in line
+                    float unused;
+                    const int32_t t = term_at(item, j0, unused);
+                    ptrs_at(item, t, lo, hi);
                 }
-        }
-    };
-    // term-sequential accumulate of one batch; a barrier after every term (the next one may touch the same
-    // documents) keeps the per-document summation order = ascending term id
-    auto apply = [&](int buf, int32_t doc_base) {
-#pragma unroll
-        for (int u = 0; u < BM25_TERM_BATCH; ++u) {
-            const int64_t lo = sm->t_lo[buf][u], hi = sm->t_hi[buf][u];
-            if (lo == hi) continue;  // uniform: padding or a term absent from this block
-            const int64_t a = lo & ~(int64_t)3;
-            const int lo_rel = (int)(lo - a), hi_rel = (int)(hi - a);  // a block slice holds < 2^31 postings
-            int rel = 4 * (int)threadIdx.x;
-            if (rel < hi_rel && !(debug & 1)) add4(rel, lo_rel, hi_rel, d[u], w[u], doc_base);
-            // longer slices: two more chunks per trip, both loads in flight together
-            for (rel += 4 * BM25_THREADS; rel < hi_rel && !(debug & 8); rel += 8 * BM25_THREADS) {
-                const int rel2 = rel + 4 * BM25_THREADS;
-                const int4 d1 = __ldg(reinterpret_cast<const int4*>(post_doc + a + rel));
-                const float4 w1 = __ldg(reinterpret_cast<const float4*>(post_imp + a + rel));
-                int4 d2 = make_int4(0, 0, 0, 0);
-                float4 w2 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (rel2 < hi_rel) {
-                    d2 = __ldg(reinterpret_cast<const int4*>(post_doc + a + rel2));
-                    w2 = __ldg(reinterpret_cast<const float4*>(post_imp + a + rel2));
+                const int nt = max_terms - j0 < 32 ? max_terms - j0 : 32;
+                for (int u = 0; u < nt; ++u) {
+                    const int64_t l = __shfl_sync(0xFFFFFFFFu, lo, u), h = __shfl_sync(0xFFFFFFFFu, hi, u);
+                    if (l == h) continue;  // padding, or a term absent from this block
+                    const int64_t end = (h + 3) & ~(int64_t)3;  // arrays are padded to a multiple of 4 postings
+                    bool first_of_term = true;
+                    for (int64_t c = l & ~(int64_t)3; c < end; c += BM25_SLOT_POSTINGS) {
+                        const uint32_t n = (uint32_t)(end - c < BM25_SLOT_POSTINGS ? end - c : BM25_SLOT_POSTINGS);
+                        ptx::mbar_wait(&sm->empty[slot], par ^ 1);
+                        if (lane == 0) {
+                            SlotMeta& m = sm->meta[slot];
+                            m.ql = ql;
+                            m.blk = blk;
+                            m.lo_rel = l > c ? (int32_t)(l - c) : 0;
+                            m.hi_rel = h - c < BM25_SLOT_POSTINGS ? (int32_t)(h - c) : BM25_SLOT_POSTINGS;
+                            m.flags = first_of_item ? SLOT_NEW_ITEM : (first_of_term ? SLOT_NEW_TERM : 0u);
+                            m.tau = tau0;
+                            ptx::mbar_arrive_expect_tx(&sm->full[slot], n * 8u);
+                            ptx::bulk_load_1d(sm->slot_doc[slot], post_doc + c, n * 4u, &sm->full[slot]);
+                            ptx::bulk_load_1d(sm->slot_imp[slot], post_imp + c, n * 4u, &sm->full[slot]);
+                        }
+                        __syncwarp();
+                        first_of_item = false;
+                        first_of_term = false;
+                        next_slot();
+                    }
                 }
-                add4(rel, lo_rel, hi_rel, d1, w1, doc_base);
-                if (rel2 < hi_rel) add4(rel2, lo_rel, hi_rel, d2, w2, doc_base);
             }
-            __syncthreads();
+            // rotate the lookahead
+            lo = nlo;
+            hi = nhi;
+            tau0 = tau1;
+            tau1 = tau2;
+            ptrs_at(item + 2 * G, t2, nlo, nhi);
+            t2 = term_at(item + 3 * G, 0, tau2);
         }
-    };
-
-    long long item = blockIdx.x;
-    if (item >= n_items) return;
-    {
-        int64_t lo, hi;
-        fetch_ptrs(item, 0, lo, hi);
-        if (threadIdx.x < BM25_TERM_BATCH) { sm->t_lo[0][threadIdx.x] = lo; sm->t_hi[0][threadIdx.x] = hi; }
+        ptx::mbar_wait(&sm->empty[slot], par ^ 1);
+        if (lane == 0) {
+            sm->meta[slot].flags = SLOT_END;
+            ptx::mbar_arrive(&sm->full[slot]);
+        }
+        return;
     }
-    __syncthreads();
-    issue(0);
-    int cur = 0;
-    // Software pipeline: while item i is selected, the postings of item i+1 (first batch of terms) are
-    // already in flight, so HBM stays busy through the shared-memory phases.
-    for (; item < n_items; item += gridDim.x, cur ^= 1) {
-        const int ql = (int)(item / nbx);
-        const int j = (int)(item - (long long)ql * nbx);
-        const int blk = phase == 0 ? j * stride : j + j / (stride - 1) + 1;
-        const int32_t doc_base = blk * BM25_BLOCK_DOCS;
-        uint64_t* out = partial + ((size_t)ql * n_blocks + blk) * k;
 
-        const float tau_q = phase == 1 ? __ldg(tau + (size_t)ql * k + (k - 1)) : 0.f;
-        __syncthreads();  // previous item is done with the tile
-        if (!(debug & 4))
-        for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (threadIdx.x == 0) { sm->out_count = 0; sm->cand_count = 0; }
-        // phase 1 with a full sample: candidates are collected while accumulating, no scan of the tile
-        const bool track = tau_q > 0.f && !(debug & 16);
-        cross_bits = track ? __float_as_uint(tau_q) : 0xFFFFFFFFu;
-        int64_t nlo, nhi;
-        fetch_ptrs(item + gridDim.x, 0, nlo, nhi);  // in flight while this item accumulates
-        __syncthreads();
-        apply(cur, doc_base);
-        for (int j0 = BM25_TERM_BATCH; j0 < max_terms; j0 += BM25_TERM_BATCH) {  // queries with more than 8 terms
-            int64_t lo, hi;
-            fetch_ptrs(item, j0, lo, hi);
-            __syncthreads();
-            if (threadIdx.x < BM25_TERM_BATCH) { sm->t_lo[cur][threadIdx.x] = lo; sm->t_hi[cur][threadIdx.x] = hi; }
-            __syncthreads();
-            issue(cur);
-            apply(cur, doc_base);
-        }
-        if (threadIdx.x < BM25_TERM_BATCH) { sm->t_lo[cur ^ 1][threadIdx.x] = nlo; sm->t_hi[cur ^ 1][threadIdx.x] = nhi; }
-        __syncthreads();
-        issue(cur ^ 1);
+    // ---------------------------------- consumer warps -----------------------------------------
+    float4* a4 = reinterpret_cast<float4*>(sm->acc);
+    uint32_t slot = 0, par = 0;
+    bool have_item = false;
+    int cur_ql = 0, cur_blk = 0;
+    float cur_tau = 0.f;
+    uint32_t cross_bits = 0xFFFFFFFFu;  // tau as orderable bits when candidates are tracked, else never crossed
 
-        // ---- selection ---------------------------------------------------------------------------
-        // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
-        uint32_t lo_bits = 1u;
-        if (tau_q > 0.f) lo_bits = __float_as_uint(tau_q);  // ties with the sample's k-th best are kept
-        if (track) {
-            const uint32_t nc = sm->cand_count;  // final: every term ended with a barrier
+    // top-k of the finished tile -> partial[cur_ql][cur_blk][*] (all consumers; adds are complete)
+    auto select_item = [&]() {
+        const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
+        uint64_t* out = partial + ((size_t)cur_ql * n_blocks + cur_blk) * k;
+        if (cross_bits != 0xFFFFFFFFu) {
+            const uint32_t nc = sm->cand_count;
             if (nc <= (uint32_t)k && nc <= (uint32_t)BM25_CAND_MAX) {
                 if (threadIdx.x < nc) {
                     const uint32_t r = sm->cand[threadIdx.x];
                     out[threadIdx.x] = srag_pack_key(__float_as_uint(sm->acc[r]), (uint32_t)(doc_base + r));
                 }
-                continue;
+                return;
             }
         }
+        // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
+        uint32_t lo_bits = 1u;
+        if (cur_tau > 0.f) lo_bits = __float_as_uint(cur_tau);  // ties with the sample's k-th best are kept
         uint32_t cnt = 0;
-        if (!(debug & 2))
         for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
             const float4 v = a4[i];
             cnt += (__float_as_uint(v.x) >= lo_bits) + (__float_as_uint(v.y) >= lo_bits) +
@@ -335,31 +341,94 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         }
         uint32_t total;
         (void)block_excl_scan(cnt, sm->warp_tmp, &total);
-        if (total == 0) {
-            // nothing to emit: `partial` is pre-zeroed (= empty keys)
-        } else if (total <= (uint32_t)k) {
+        if (total == 0) return;  // `partial` is pre-zeroed (= empty keys)
+        if (total <= (uint32_t)k) {
             for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
                 const float4 v = a4[i];
                 const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
                     if (b[e] >= lo_bits) {
-                        const uint32_t slot = atomicAdd(&sm->out_count, 1u);
-                        out[slot] = srag_pack_key(b[e], (uint32_t)(doc_base + 4 * i + e));
+                        const uint32_t s_ = atomicAdd(&sm->out_count, 1u);
+                        out[s_] = srag_pack_key(b[e], (uint32_t)(doc_base + 4 * i + e));
                     }
             }
-        } else {
-            // more than k survivors (always so in phase 0 for a dense block): exact top-k of ALL matches
-            uint32_t nz = 0;
-            if (lo_bits > 1u) {
-                for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
-                    const float4 v = a4[i];
-                    nz += (v.x != 0.f) + (v.y != 0.f) + (v.z != 0.f) + (v.w != 0.f);
-                }
-                (void)block_excl_scan(nz, sm->warp_tmp, &total);
-            }
-            select_exact(sm, k, doc_base, total, out);
+            return;
         }
+        // more than k survivors (always so in phase 0 for a dense block): exact top-k of ALL matches
+        if (lo_bits > 1u) {
+            uint32_t nz = 0;
+            for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+                const float4 v = a4[i];
+                nz += (v.x != 0.f) + (v.y != 0.f) + (v.z != 0.f) + (v.w != 0.f);
+            }
+            (void)block_excl_scan(nz, sm->warp_tmp, &total);
+        }
+        select_exact(sm, k, doc_base, total, out);
+    };
+
+    for (;;) {
+        ptx::mbar_wait(&sm->full[slot], par);
+        const SlotMeta m = sm->meta[slot];
+        if (m.flags & (SLOT_NEW_ITEM | SLOT_END)) {
+            consumer_sync();  // every add of the previous item has landed
+            if (have_item) {
+                select_item();
+                consumer_sync();  // selection has read the tile
+            }
+            if (m.flags & SLOT_END) break;
+            for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (threadIdx.x == 0) { sm->out_count = 0; sm->cand_count = 0; }
+            have_item = true;
+            cur_ql = m.ql;
+            cur_blk = m.blk;
+            cur_tau = m.tau;
+            cross_bits = (cur_tau > 0.f && !(debug & 16)) ? __float_as_uint(cur_tau) : 0xFFFFFFFFu;
+            consumer_sync();
+        } else if (m.flags & SLOT_NEW_TERM) {
+            consumer_sync();
+        }
+        const int rel = 4 * (int)threadIdx.x;
+        int4 dd = make_int4(0, 0, 0, 0);
+        float4 ww = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool active = rel < m.hi_rel && rel + 4 > m.lo_rel;
+        if (active) {
+            dd = *reinterpret_cast<const int4*>(&sm->slot_doc[slot][rel]);
+            ww = *reinterpret_cast<const float4*>(&sm->slot_imp[slot][rel]);
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
+        if (active) {
+            const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
+            const bool m0 = rel >= m.lo_rel && rel < m.hi_rel, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
+            const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
+            const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
+            const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
+            // the four reads are issued together, then the adds, then the writes (one latency, not four)
+            const float a0 = sm->acc[r0], a1 = sm->acc[r1], a2 = sm->acc[r2], a3 = sm->acc[r3];
+            const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y), n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
+            if (m0) sm->acc[r0] = n0;
+            if (m1) sm->acc[r1] = n1;
+            if (m2) sm->acc[r2] = n2;
+            if (m3) sm->acc[r3] = n3;
+            // Impacts are > 0, so an accumulator only grows and crosses tau at most once: the add that takes
+            // it from below tau to >= tau records the document.
+            const bool c0 = m0 && __float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits;
+            const bool c1 = m1 && __float_as_uint(n1) >= cross_bits && __float_as_uint(a1) < cross_bits;
+            const bool c2 = m2 && __float_as_uint(n2) >= cross_bits && __float_as_uint(a2) < cross_bits;
+            const bool c3 = m3 && __float_as_uint(n3) >= cross_bits && __float_as_uint(a3) < cross_bits;
+            if (c0 | c1 | c2 | c3) {
+                const int rr[4] = {r0, r1, r2, r3};
+                const bool cc[4] = {c0, c1, c2, c3};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (cc[e]) {
+                        const uint32_t s_ = atomicAdd(&sm->cand_count, 1u);
+                        if (s_ < (uint32_t)BM25_CAND_MAX) sm->cand[s_] = (uint16_t)rr[e];
+                    }
+            }
+        }
+        if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
     }
 }
 
@@ -492,14 +561,14 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     const int nb0 = (nb + stride - 1) / stride;
     const char* dbg_env = getenv("SRAG_BM25_DEBUG");
     const int dbg = dbg_env ? atoi(dbg_env) : 0;
-    const int resident = sm_count * 2;  // 128 registers x 256 threads per CTA (posting prefetch lives in registers)
+    const int resident = sm_count * 2;  // ~107 KB of shared memory per CTA
     for (int q0 = 0; q0 < n_queries; q0 += qc) {
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
         SRAG_CUDA(cudaMemsetAsync(partial, 0, (size_t)nq * nb * k * sizeof(uint64_t), st));
         if (n_docs > 0) {
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
-            bm25_items_kernel<<<grid0, BM25_THREADS, sizeof(Bm25Smem), st>>>(
+            bm25_items_kernel<<<grid0, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(
                 block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr, partial, dbg);
             SRAG_CUDA(cudaGetLastError());
             if (stride > 1) {
@@ -507,7 +576,7 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
                 if (rc) return rc;
                 const long long items1 = (long long)nq * (nb - nb0);
                 const int grid1 = (int)(items1 < resident ? items1 : resident);
-                bm25_items_kernel<<<grid1, BM25_THREADS, sizeof(Bm25Smem), st>>>(
+                bm25_items_kernel<<<grid1, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(
                     block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 1, stride, tau_scores, partial, dbg);
                 SRAG_CUDA(cudaGetLastError());
             }
