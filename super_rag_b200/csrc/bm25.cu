@@ -19,12 +19,18 @@
 namespace {
 
 constexpr int BM25_BLOCK_DOCS = 16384;  // 64 KB of fp32 accumulators per CTA
-constexpr int BM25_THREADS = 256;
+#ifndef SRAG_BM25_WARPS
+#define SRAG_BM25_WARPS 8
+#endif
+constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
 constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
-constexpr int BM25_CTA_THREADS = BM25_THREADS + 32;  // 8 consumer warps + 1 producer warp
-constexpr int BM25_SLOT_POSTINGS = 1024;             // one ring slot: 4 KB of doc ids + 4 KB of impacts
-constexpr int BM25_SLOTS = 4;
+constexpr int BM25_CTA_THREADS = BM25_THREADS + 64;  // consumer warps + 2 producer warps (doc ids / impacts)
+constexpr int BM25_CHUNK = 4 * BM25_THREADS;         // postings per chunk: one aligned group of 4 per consumer thread
+constexpr int BM25_CTAS_PER_SM = SRAG_BM25_WARPS == 8 ? 2 : 1;
+// posting ring capacity (x 8 bytes: doc ids + impacts): 36 KB with two CTAs per SM, 144 KB with one
+constexpr int BM25_RING = SRAG_BM25_WARPS == 8 ? 4608 : 18 * 1024;
+constexpr int BM25_SLOTS = 32;                       // chunk descriptors in flight
 constexpr int BM25_CAND_MAX = 1024;
 
 // stream flags of a ring slot
@@ -34,10 +40,11 @@ constexpr uint32_t SLOT_END = 4u;       // no data: the CTA's item list is exhau
 
 struct SlotMeta {  // written by the producer before it issues the slot's copies
     int32_t ql, blk;         // query (inside the chunk) and document block
-    int32_t lo_rel, hi_rel;  // valid postings of the slot: [lo_rel, hi_rel)
+    int32_t lo_rel, hi_rel;  // valid postings of the chunk: [lo_rel, hi_rel)
     uint32_t flags;
     float tau;               // sample k-th best score of the query (0 = none)
-    int32_t pad[2];
+    uint32_t pos;            // ring position of the chunk's first posting (multiple of 4)
+    uint32_t n;              // postings copied (multiple of 4)
 };
 
 __device__ __forceinline__ void consumer_sync() { ptx::named_bar_sync(1, BM25_THREADS); }
@@ -45,8 +52,8 @@ __device__ __forceinline__ void consumer_sync() { ptx::named_bar_sync(1, BM25_TH
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
-    alignas(128) int32_t slot_doc[BM25_SLOTS][BM25_SLOT_POSTINGS];
-    alignas(128) float slot_imp[BM25_SLOTS][BM25_SLOT_POSTINGS];
+    alignas(128) int32_t ring_doc[BM25_RING];
+    alignas(128) float ring_imp[BM25_RING];
     SlotMeta meta[BM25_SLOTS];
     uint64_t full[BM25_SLOTS], empty[BM25_SLOTS];
     uint32_t warp_tmp[BM25_THREADS / 32];
@@ -191,12 +198,13 @@ __device__ void select_exact(Bm25Smem* sm, int k, int32_t doc_base, uint32_t tot
 // Warps 0..7 are the CONSUMERS: they follow the slot stream; the slot's metadata says where an item or a
 // term starts. A barrier separates terms (two terms may hit the same document; inside a term every
 // posting is a distinct document), which keeps the per-document summation order = ascending term id.
-__global__ void __launch_bounds__(BM25_CTA_THREADS, 2)
+__global__ void __launch_bounds__(BM25_CTA_THREADS, BM25_CTAS_PER_SM)
 bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
                   const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
                   const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
-                  uint64_t* __restrict__ partial /* [nq][n_blocks][k] */, int debug /* SRAG_BM25_DEBUG */) {
+                  uint64_t* __restrict__ partial /* phase 1: [nq][n_blocks][k]; phase 0: [nq][ceil(n_blocks/stride)][k] */,
+                  int debug /* SRAG_BM25_DEBUG */) {
     extern __shared__ uint8_t bm25_smem_raw[];
     Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
     const int nb0 = (n_blocks + stride - 1) / stride;
@@ -215,94 +223,156 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
 
     if (threadIdx.x >= BM25_THREADS) {
         // ------------------------------ producer warp ------------------------------------------
-        auto item_blk = [&](long long it, int& ql_, int& blk_) {
-            ql_ = (int)(it / nbx);
-            const int j_ = (int)(it - (long long)ql_ * nbx);
-            blk_ = phase == 0 ? j_ * stride : j_ + j_ / (stride - 1) + 1;
+        // Items of this CTA: blockIdx.x, + gridDim.x, ... as (query, j-th block of the phase); stepping by
+        // gridDim.x is an add with carry, so no 64-bit division per item.
+        struct ItemPos { int ql, j; };
+        const int step_q = (int)(gridDim.x / (unsigned)nbx), step_j = (int)(gridDim.x % (unsigned)nbx);
+        auto advance = [&](ItemPos p) {
+            p.j += step_j;
+            p.ql += step_q;
+            if (p.j >= nbx) { p.j -= nbx; ++p.ql; }
+            return p;
         };
+        auto block_of = [&](int j_) { return phase == 0 ? j_ * stride : j_ + j_ / (stride - 1) + 1; };
         // lane l looks after term slot j0 + l of the query
-        auto term_at = [&](long long it, int j0, float& tq) -> int32_t {
+        auto term_at = [&](ItemPos p, int j0, float& tq) -> int32_t {
             tq = 0.f;
-            if (it >= n_items) return -1;
-            int ql_, blk_;
-            item_blk(it, ql_, blk_);
-            if (phase == 1) tq = __ldg(tau + (size_t)ql_ * k + (k - 1));
-            return j0 + lane < max_terms ? __ldg(q_terms + (size_t)(q_offset + ql_) * max_terms + j0 + lane) : -1;
+            if (p.ql >= nq) return -1;
+            if (phase == 1) tq = __ldg(tau + (size_t)p.ql * k + (k - 1));
+            return j0 + lane < max_terms ? __ldg(q_terms + (size_t)(q_offset + p.ql) * max_terms + j0 + lane) : -1;
         };
-        auto ptrs_at = [&](long long it, int32_t t, int64_t& lo, int64_t& hi) {
+        auto ptrs_at = [&](ItemPos p, int32_t t, int64_t& lo, int64_t& hi) {
             lo = 0;
             hi = 0;
-            if (it < n_items && t >= 0) {
-                int ql_, blk_;
-                item_blk(it, ql_, blk_);
-                const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + blk_;
+            if (p.ql < nq && t >= 0) {
+                const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + block_of(p.j);
                 lo = __ldg(bp);
                 hi = __ldg(bp + 1);
             }
         };
-        uint32_t slot = 0, par = 0;  // ring position and its phase parity
-        auto next_slot = [&]() {
-            if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
+        // descriptor ring (head = next to fill, tail = oldest not yet released) and posting ring space
+        uint32_t slot = 0, tail_slot = 0, tail_par = 0, inflight = 0, pos = 0, free_post = BM25_RING;
+        auto reserve = [&](uint32_t n_slots, uint32_t n_post) {  // wait for descriptors and ring space
+            while (inflight + n_slots > (uint32_t)BM25_SLOTS || free_post < n_post) {
+                ptx::mbar_wait(&sm->empty[tail_slot], tail_par);
+                free_post += sm->meta[tail_slot].n;
+                if (++tail_slot == BM25_SLOTS) { tail_slot = 0; tail_par ^= 1; }
+                --inflight;
+            }
         };
-        const long long G = gridDim.x;
-        long long item = blockIdx.x;
+        // Both producer warps run the same plan; one issues the doc-id copies (and owns the descriptors),
+        // the other the impact copies, so the per-lane copy issue is split between two warps.
+        const bool copies_doc = threadIdx.x < BM25_THREADS + 32;
+        constexpr uint32_t FULL = 0xFFFFFFFFu;
+        auto warp_incl_scan = [&](uint32_t v) {
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL, v, o);
+                if (lane >= o) v += t;
+            }
+            return v;
+        };
         // two-deep lookahead so that neither dependent load (term id -> slice bounds) is waited for
+        ItemPos p0{(int)(blockIdx.x / (unsigned)nbx), (int)(blockIdx.x % (unsigned)nbx)};
+        ItemPos p1 = advance(p0), p2 = advance(p1), p3 = advance(p2);
         float tau0, tau1, tau2;
         int64_t lo, hi, nlo, nhi;
-        int32_t t0 = term_at(item, 0, tau0);
-        int32_t t1 = term_at(item + G, 0, tau1);
-        int32_t t2 = term_at(item + 2 * G, 0, tau2);
-        ptrs_at(item, t0, lo, hi);
-        ptrs_at(item + G, t1, nlo, nhi);
-        for (; item < n_items; item += G) {
-            int ql, blk;
-            item_blk(item, ql, blk);
+        int32_t t0 = term_at(p0, 0, tau0);
+        int32_t t1 = term_at(p1, 0, tau1);
+        int32_t t2 = term_at(p2, 0, tau2);
+        ptrs_at(p0, t0, lo, hi);
+        ptrs_at(p1, t1, nlo, nhi);
+        for (; p0.ql < nq; p0 = p1, p1 = p2, p2 = p3, p3 = advance(p3)) {
+            const int ql = p0.ql, blk = block_of(p0.j);
             bool first_of_item = true;
             for (int j0 = 0; j0 < max_terms; j0 += 32) {
                 if (j0 > 0) {  // queries with more than 32 terms: fetched in line
                     float unused;
-                    const int32_t t = term_at(item, j0, unused);
-                    ptrs_at(item, t, lo, hi);
+                    const int32_t t = term_at(p0, j0, unused);
+                    ptrs_at(p0, t, lo, hi);
                 }
                 const int nt = max_terms - j0 < 32 ? max_terms - j0 : 32;
-                for (int u = 0; u < nt; ++u) {
-                    const int64_t l = __shfl_sync(0xFFFFFFFFu, lo, u), h = __shfl_sync(0xFFFFFFFFu, hi, u);
-                    if (l == h) continue;  // padding, or a term absent from this block
-                    const int64_t end = (h + 3) & ~(int64_t)3;  // arrays are padded to a multiple of 4 postings
-                    bool first_of_term = true;
-                    for (int64_t c = l & ~(int64_t)3; c < end; c += BM25_SLOT_POSTINGS) {
-                        const uint32_t n = (uint32_t)(end - c < BM25_SLOT_POSTINGS ? end - c : BM25_SLOT_POSTINGS);
-                        ptx::mbar_wait(&sm->empty[slot], par ^ 1);
-                        if (lane == 0) {
-                            SlotMeta& m = sm->meta[slot];
-                            m.ql = ql;
-                            m.blk = blk;
-                            m.lo_rel = l > c ? (int32_t)(l - c) : 0;
-                            m.hi_rel = h - c < BM25_SLOT_POSTINGS ? (int32_t)(h - c) : BM25_SLOT_POSTINGS;
-                            m.flags = first_of_item ? SLOT_NEW_ITEM : (first_of_term ? SLOT_NEW_TERM : 0u);
-                            m.tau = tau0;
-                            ptx::mbar_arrive_expect_tx(&sm->full[slot], n * 8u);
-                            ptx::bulk_load_1d(sm->slot_doc[slot], post_doc + c, n * 4u, &sm->full[slot]);
-                            ptx::bulk_load_1d(sm->slot_imp[slot], post_imp + c, n * 4u, &sm->full[slot]);
+                // Lane u plans term u: the slice rounded out to groups of 4 postings (the arrays are padded)
+                // and cut into chunks. A term has at most BM25_BLOCK_DOCS postings inside a block.
+                const int64_t a = lo & ~(int64_t)3;
+                const uint32_t hi_off = (uint32_t)(hi - a), lo_off = (uint32_t)(lo - a);
+                const uint32_t len = lo == hi ? 0u : (hi_off + 3u) & ~3u;
+                const uint32_t cnt = (len + BM25_CHUNK - 1) / BM25_CHUNK;
+                const uint32_t incl = warp_incl_scan(cnt);
+                const uint32_t total = __shfl_sync(FULL, incl, 31);
+                // Lane i then issues chunk base + i of the item's stream (term-major order)
+                for (uint32_t base = 0; base < total; base += 32) {
+                    const uint32_t i = base + lane;
+                    const bool valid = i < total;
+                    uint32_t u = 0;
+                    for (int v = 0; v < nt; ++v) u += __shfl_sync(FULL, incl, v) <= i;
+                    if (!valid) u = 0;
+                    const uint32_t j = i - __shfl_sync(FULL, incl - cnt, u);  // chunk inside its term
+                    const uint32_t off = j * BM25_CHUNK;
+                    const int64_t a_u = __shfl_sync(FULL, a, u);
+                    const uint32_t len_u = __shfl_sync(FULL, len, u), hi_u = __shfl_sync(FULL, hi_off, u);
+                    const uint32_t lo_u = __shfl_sync(FULL, lo_off, u);
+                    const uint32_t n = !valid ? 0u : (len_u - off < (uint32_t)BM25_CHUNK ? len_u - off : (uint32_t)BM25_CHUNK);
+                    const uint32_t cum = warp_incl_scan(n);
+                    const uint32_t in_round = total - base < 32u ? total - base : 32u;
+                    uint32_t done = 0, cum_base = 0;
+                    while (done < in_round) {
+                        // as many chunks as fit half the ring at once (a chunk is at most a ninth of it)
+                        const uint32_t fits = __ballot_sync(FULL, valid && lane >= done && cum - cum_base <= (uint32_t)BM25_RING / 2);
+                        const uint32_t take = __popc(fits);
+                        const uint32_t need = __shfl_sync(FULL, cum, done + take - 1) - cum_base;
+                        reserve(take, need);
+                        if (lane >= done && lane < done + take) {
+                            uint32_t my_slot = slot + (lane - done);
+                            if (my_slot >= (uint32_t)BM25_SLOTS) my_slot -= BM25_SLOTS;
+                            uint32_t my_pos = pos + (cum - n - cum_base);
+                            if (my_pos >= (uint32_t)BM25_RING) my_pos -= BM25_RING;
+                            uint64_t* bar = &sm->full[my_slot];
+                            if (copies_doc) {
+                                SlotMeta& m = sm->meta[my_slot];
+                                m.ql = ql;
+                                m.blk = blk;
+                                m.lo_rel = j == 0 ? (int32_t)lo_u : 0;
+                                m.hi_rel = hi_u - off < (uint32_t)BM25_CHUNK ? (int32_t)(hi_u - off) : BM25_CHUNK;
+                                m.flags = (first_of_item && i == 0) ? SLOT_NEW_ITEM : (j == 0 ? SLOT_NEW_TERM : 0u);
+                                m.tau = tau0;
+                                m.pos = my_pos;
+                                m.n = n;
+                                ptx::mbar_arrive_expect_tx(bar, n * 8u);  // both warps' copies
+                            }
+                            // this warp's array: 4 bytes per posting either way
+                            const char* src = (copies_doc ? reinterpret_cast<const char*>(post_doc) : reinterpret_cast<const char*>(post_imp)) +
+                                              4 * (a_u + off);
+                            char* dst = copies_doc ? reinterpret_cast<char*>(sm->ring_doc) : reinterpret_cast<char*>(sm->ring_imp);
+                            const uint32_t n1 = my_pos + n <= (uint32_t)BM25_RING ? n : BM25_RING - my_pos;  // up to the ring's end
+                            ptx::bulk_load_1d(dst + 4 * my_pos, src, n1 * 4u, bar);
+                            if (n1 < n) ptx::bulk_load_1d(dst, src + 4 * n1, (n - n1) * 4u, bar);  // wrapped remainder
                         }
                         __syncwarp();
-                        first_of_item = false;
-                        first_of_term = false;
-                        next_slot();
+                        slot += take;
+                        if (slot >= (uint32_t)BM25_SLOTS) slot -= BM25_SLOTS;
+                        pos += need;
+                        if (pos >= (uint32_t)BM25_RING) pos -= BM25_RING;
+                        free_post -= need;
+                        inflight += take;
+                        done += take;
+                        cum_base += need;
                     }
                 }
+                if (total > 0) first_of_item = false;
             }
             // rotate the lookahead
             lo = nlo;
             hi = nhi;
             tau0 = tau1;
             tau1 = tau2;
-            ptrs_at(item + 2 * G, t2, nlo, nhi);
-            t2 = term_at(item + 3 * G, 0, tau2);
+            ptrs_at(p2, t2, nlo, nhi);
+            t2 = term_at(p3, 0, tau2);
         }
-        ptx::mbar_wait(&sm->empty[slot], par ^ 1);
-        if (lane == 0) {
+        reserve(1, 0);
+        if (lane == 0 && copies_doc) {
             sm->meta[slot].flags = SLOT_END;
+            sm->meta[slot].n = 0;
             ptx::mbar_arrive(&sm->full[slot]);
         }
         return;
@@ -319,7 +389,8 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
     // top-k of the finished tile -> partial[cur_ql][cur_blk][*] (all consumers; adds are complete)
     auto select_item = [&]() {
         const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
-        uint64_t* out = partial + ((size_t)cur_ql * n_blocks + cur_blk) * k;
+        uint64_t* out = phase == 0 ? partial + ((size_t)cur_ql * nb0 + cur_blk / stride) * k
+                                   : partial + ((size_t)cur_ql * n_blocks + cur_blk) * k;
         if (cross_bits != 0xFFFFFFFFu) {
             const uint32_t nc = sm->cand_count;
             if (nc <= (uint32_t)k && nc <= (uint32_t)BM25_CAND_MAX) {
@@ -372,12 +443,13 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         const SlotMeta m = sm->meta[slot];
         if (m.flags & (SLOT_NEW_ITEM | SLOT_END)) {
             consumer_sync();  // every add of the previous item has landed
-            if (have_item) {
+            if (have_item && !(debug & 2)) {
                 select_item();
                 consumer_sync();  // selection has read the tile
             }
             if (m.flags & SLOT_END) break;
-            for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (!(debug & 4))
+                for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) a4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (threadIdx.x == 0) { sm->out_count = 0; sm->cand_count = 0; }
             have_item = true;
             cur_ql = m.ql;
@@ -385,7 +457,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             cur_tau = m.tau;
             cross_bits = (cur_tau > 0.f && !(debug & 16)) ? __float_as_uint(cur_tau) : 0xFFFFFFFFu;
             consumer_sync();
-        } else if (m.flags & SLOT_NEW_TERM) {
+        } else if ((m.flags & SLOT_NEW_TERM) && !(debug & 8)) {
             consumer_sync();
         }
         const int rel = 4 * (int)threadIdx.x;
@@ -393,12 +465,14 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         float4 ww = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool active = rel < m.hi_rel && rel + 4 > m.lo_rel;
         if (active) {
-            dd = *reinterpret_cast<const int4*>(&sm->slot_doc[slot][rel]);
-            ww = *reinterpret_cast<const float4*>(&sm->slot_imp[slot][rel]);
+            uint32_t idx = m.pos + (uint32_t)rel;
+            if (idx >= (uint32_t)BM25_RING) idx -= BM25_RING;
+            dd = *reinterpret_cast<const int4*>(&sm->ring_doc[idx]);
+            ww = *reinterpret_cast<const float4*>(&sm->ring_imp[idx]);
         }
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
-        if (active) {
+        if (active && !(debug & 1)) {
             const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
             const bool m0 = rel >= m.lo_rel && rel < m.hi_rel, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
             const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
@@ -513,13 +587,27 @@ extern "C" int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* pos
 
 // workspace = per-block lists of one query chunk + the sample top-k (scores, ids) that yields tau
 static size_t bm25_partial_bytes(int qc, int nb, int k) { return (((size_t)qc * nb * k * sizeof(uint64_t)) + 255) & ~(size_t)255; }
+// sample every stride-th block first when there are enough blocks for the sample to be worth a launch
+static int bm25_stride(int nb) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("SRAG_BM25_STRIDE");
+        forced = e ? atoi(e) : 0;
+    }
+    const int stride = forced >= 2 ? forced : 16;
+    return nb >= 2 * stride ? stride : 1;
+}
+static size_t bm25_sample_bytes(int qc, int nb, int k) {
+    const int stride = bm25_stride(nb);
+    return stride > 1 ? bm25_partial_bytes(qc, (nb + stride - 1) / stride, k) : 0;
+}
 static size_t bm25_tau_bytes(int qc, int k) { return (((size_t)qc * k * (sizeof(float) + sizeof(int64_t))) + 255) & ~(size_t)255; }
 
 extern "C" int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes) {
     SRAG_CHECK_ARG(bytes && n_queries >= 1 && k >= 1 && k <= SRAG_MAX_BM25_K && n_docs >= 0, "bad sizes");
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
-    *bytes = bm25_partial_bytes(qc, nb, k) + bm25_tau_bytes(qc, k) + 256;
+    *bytes = bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) + bm25_tau_bytes(qc, k) + 256;
     return SRAG_OK;
 }
 
@@ -537,7 +625,7 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
-    const size_t need = bm25_partial_bytes(qc, nb, k) + bm25_tau_bytes(qc, k);
+    const size_t need = bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) + bm25_tau_bytes(qc, k);
     if (workspace_bytes < need) {
         srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
         return SRAG_E_WORKSPACE;
@@ -554,25 +642,30 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     }
     uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
     uint64_t* partial = reinterpret_cast<uint64_t*>(ws);
-    float* tau_scores = reinterpret_cast<float*>(ws + bm25_partial_bytes(qc, nb, k));
+    uint64_t* sample = reinterpret_cast<uint64_t*>(ws + bm25_partial_bytes(qc, nb, k));
+    float* tau_scores = reinterpret_cast<float*>(ws + bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k));
     int64_t* tau_ids = reinterpret_cast<int64_t*>(tau_scores + (size_t)qc * k);
-    // sample every 16th block first when there are enough blocks for the sample to be worth a launch
-    const int stride = nb >= 32 ? 16 : 1;
+    const int stride = bm25_stride(nb);
     const int nb0 = (nb + stride - 1) / stride;
     const char* dbg_env = getenv("SRAG_BM25_DEBUG");
     const int dbg = dbg_env ? atoi(dbg_env) : 0;
-    const int resident = sm_count * 2;  // ~107 KB of shared memory per CTA
+    const int resident = sm_count * BM25_CTAS_PER_SM;
     for (int q0 = 0; q0 < n_queries; q0 += qc) {
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
-        SRAG_CUDA(cudaMemsetAsync(partial, 0, (size_t)nq * nb * k * sizeof(uint64_t), st));
+        // the memset covers the sample lists too (they follow `partial` in the workspace)
+        SRAG_CUDA(cudaMemsetAsync(partial, 0, bm25_partial_bytes(qc, nb, k) + (stride > 1 ? (size_t)nq * nb0 * k * sizeof(uint64_t) : 0), st));
         if (n_docs > 0) {
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
             bm25_items_kernel<<<grid0, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(
-                block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr, partial, dbg);
+                block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr,
+                stride > 1 ? sample : partial, dbg);
             SRAG_CUDA(cudaGetLastError());
             if (stride > 1) {
-                int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, 0, tau_scores, tau_ids, st);
+                // top-k of the sample: scores give tau; the keys seed the final merge in block 0's slot of
+                // `partial` (block 0 always belongs to the sample, so phase 1 never writes there)
+                int rc = srag_launch_finalize_ex(sample, (size_t)nb0 * k, nq, nb0 * k, k, nullptr, 0, tau_scores, tau_ids,
+                                                 partial, (size_t)nb * k, st);
                 if (rc) return rc;
                 const long long items1 = (long long)nq * (nb - nb0);
                 const int grid1 = (int)(items1 < resident ? items1 : resident);

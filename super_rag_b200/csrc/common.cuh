@@ -16,6 +16,11 @@ void srag_set_error(const char* fmt, ...);
 // topk_gemm.cu: per-query lists of sortable keys [n_queries][total] -> sorted top-k (k <= 256)
 int srag_launch_finalize(const uint64_t* partial, int n_queries, int total, int k, const float* q_scale,
                          int64_t id_base, float* out_scores, int64_t* out_ids, cudaStream_t st);
+// same with the lists of consecutive queries src_stride keys apart, and (optionally) the merged top-k also written
+// as sortable keys to out_keys[q * out_keys_stride + 0..k)
+int srag_launch_finalize_ex(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                            const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                            uint64_t* out_keys, size_t out_keys_stride, cudaStream_t st);
 
 #define SRAG_CHECK_ARG(cond, ...)                 \
     do {                                          \

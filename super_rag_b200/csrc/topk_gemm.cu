@@ -559,41 +559,52 @@ __device__ void block_bitonic_desc(uint64_t* a, int P) {
 }
 
 __global__ void __launch_bounds__(FIN_THREADS)
-topk_finalize_kernel(const uint64_t* __restrict__ partial, int total /* lists * k */, int k, int kcap, int P,
-                     const float* __restrict__ q_scale, int64_t id_base, float* __restrict__ out_scores,
-                     int64_t* __restrict__ out_ids) {
+topk_finalize_kernel(const uint64_t* __restrict__ partial, size_t src_stride, int total /* lists * k */, int k, int kcap,
+                     int P, const float* __restrict__ q_scale, int64_t id_base, float* __restrict__ out_scores,
+                     int64_t* __restrict__ out_ids, uint64_t* __restrict__ out_keys, size_t out_keys_stride) {
     extern __shared__ uint64_t fin_keys[];
     __shared__ int fin_count;
     const int q = blockIdx.x;
-    const uint64_t* src = partial + (size_t)q * total;
+    const uint64_t* src = partial + (size_t)q * src_stride;
     const int chunk = P - kcap;
-    // sparse lists (K2 with a shared threshold leaves most block lists empty): count first; when every
-    // non-empty key fits, compact them and sort ONE small power of two instead of total/chunk passes
-    if (threadIdx.x == 0) fin_count = 0;
-    __syncthreads();
-    int mine = 0;
+    bool sorted = false;
     if (total > chunk) {
-        for (int i = threadIdx.x; i < total; i += blockDim.x) mine += (src[i] != SRAG_KEY_EMPTY) ? 1 : 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, o);
-        if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&fin_count, mine);
-    }
-    __syncthreads();
-    const int live = fin_count;
-    __syncthreads();
-    if (total > chunk && live <= chunk) {
-        int P2 = 2 * kcap;
-        while (P2 < live + kcap) P2 <<= 1;
-        for (int i = threadIdx.x; i < P2; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
+        // Sparse lists (K2 with a sample threshold leaves most block lists empty): compact the non-empty keys
+        // in ONE pass; when they all fit, sort one small power of two instead of total/chunk passes.
+        for (int i = threadIdx.x; i < P; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
         if (threadIdx.x == 0) fin_count = 0;
         __syncthreads();
-        for (int i = threadIdx.x; i < total; i += blockDim.x) {
-            const uint64_t key = src[i];
-            if (key != SRAG_KEY_EMPTY) fin_keys[atomicAdd(&fin_count, 1)] = key;  // order is irrelevant: sorted next
+        auto keep = [&](uint64_t key) {
+            if (key != SRAG_KEY_EMPTY) {
+                const int slot = atomicAdd(&fin_count, 1);  // order is irrelevant: sorted next
+                if (slot < chunk) fin_keys[slot] = key;
+            }
+        };
+        if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+            const ulonglong2* src2 = reinterpret_cast<const ulonglong2*>(src);
+            const int pairs = total >> 1;
+#pragma unroll 8
+            for (int i = threadIdx.x; i < pairs; i += FIN_THREADS) {
+                const ulonglong2 v = __ldg(src2 + i);
+                keep(v.x);
+                keep(v.y);
+            }
+            if ((total & 1) && threadIdx.x == 0) keep(src[total - 1]);
+        } else {
+#pragma unroll 8
+            for (int i = threadIdx.x; i < total; i += FIN_THREADS) keep(__ldg(src + i));
         }
         __syncthreads();
-        block_bitonic_desc(fin_keys, P2);
-    } else {
+        const int live = fin_count;
+        __syncthreads();
+        if (live <= chunk) {
+            int P2 = 2 * kcap;
+            while (P2 < live + kcap) P2 <<= 1;
+            block_bitonic_desc(fin_keys, P2);
+            sorted = true;
+        }
+    }
+    if (!sorted) {
         for (int i = threadIdx.x; i < kcap; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
         for (int off = 0; off < total; off += chunk) {
             for (int i = threadIdx.x; i < chunk; i += blockDim.x)
@@ -604,6 +615,8 @@ topk_finalize_kernel(const uint64_t* __restrict__ partial, int total /* lists * 
             __syncthreads();
         }
     }
+    if (out_keys)  // the merged list as sortable keys (K2 seeds its second phase with the sample's top-k)
+        for (int j = threadIdx.x; j < k; j += blockDim.x) out_keys[(size_t)q * out_keys_stride + j] = fin_keys[j];
     const float qs = q_scale ? q_scale[q] : 1.0f;
     for (int j = threadIdx.x; j < k; j += blockDim.x) {
         const uint64_t key = fin_keys[j];
@@ -892,8 +905,9 @@ extern "C" int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int*
 }
 
 // Shared with K2 (bm25.cu): per-query lists of sortable keys -> sorted top-k (score, id).
-int srag_launch_finalize(const uint64_t* partial, int n_queries, int total, int k, const float* q_scale,
-                         int64_t id_base, float* out_scores, int64_t* out_ids, cudaStream_t st) {
+int srag_launch_finalize_ex(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                            const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                            uint64_t* out_keys, size_t out_keys_stride, cudaStream_t st) {
     const int kcap = (k <= 128) ? 128 : 256;
     int P = 2 * kcap;
     while (P < total + kcap && P < FIN_MAX_P) P <<= 1;
@@ -904,7 +918,13 @@ int srag_launch_finalize(const uint64_t* partial, int n_queries, int total, int 
         fin_attr = true;
     }
     topk_finalize_kernel<<<n_queries, FIN_THREADS, (size_t)P * sizeof(uint64_t), st>>>(
-        partial, total, k, kcap, P, q_scale, id_base, out_scores, out_ids);
+        partial, src_stride, total, k, kcap, P, q_scale, id_base, out_scores, out_ids, out_keys, out_keys_stride);
     SRAG_CUDA(cudaGetLastError());
     return SRAG_OK;
+}
+
+int srag_launch_finalize(const uint64_t* partial, int n_queries, int total, int k, const float* q_scale,
+                         int64_t id_base, float* out_scores, int64_t* out_ids, cudaStream_t st) {
+    return srag_launch_finalize_ex(partial, (size_t)total, n_queries, total, k, q_scale, id_base, out_scores, out_ids,
+                                   nullptr, 0, st);
 }
