@@ -78,6 +78,20 @@ int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_
                      int64_t id_base, float* out_scores, int64_t* out_ids,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same scan with the metadata pre-filter the reference BUILDS but its connector drops
+ * (ContextManager._create_combined_filter, super_rag/context/context.py:74-111;
+ * seekdb_connector.py:99-100): row r is eligible for query b iff
+ *   (row_tags  == NULL || (row_tags[r] & q_tag_mask[b]) != 0)            -- `indexer` $in / $exists:false
+ *   (row_group == NULL || q_group[b] < 0 || row_group[r] == q_group[b])  -- `chat_id` equality
+ * Ineligible rows are never returned; the result is the exact top-k of the eligible rows.
+ *   row_tags [n_rows] uint32, row_group [n_rows] int32, q_tag_mask [n_queries] uint32,
+ *   q_group [n_queries] int32 (device pointers; each row_* comes with its q_* or both are NULL) */
+int srag_topk_search_filtered(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                              const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                              int64_t id_base, const uint32_t* row_tags, const int32_t* row_group,
+                              const uint32_t* q_tag_mask, const int32_t* q_group, float* out_scores,
+                              int64_t* out_ids, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Device-side timing of K1 for roofline reporting: when enabled, srag_topk_search records CUDA
  * events around its main kernel (memset + fused GEMM/top-k) and its finalize kernel on the
  * launching stream (up to 256 calls). srag_prof_read waits for them and returns the sums.      */

@@ -40,3 +40,4 @@ from .fusion import (  # noqa: F401
     rerank_fallback,
     merge_shard_candidates,
 )
+from .filters import eval_filter, filter_rows  # noqa: F401

@@ -108,6 +108,38 @@ class Bm25Index:
         term_ptr, post_doc, post_tf, dl = cls.postings_from_tokens(tokens, doc_ptr, vocab)
         return cls.from_postings(term_ptr, post_doc, post_tf, dl, stats, id_base)
 
+    # ---- persistence (on-disk shard) ------------------------------------
+    def save(self, path: str) -> None:
+        from . import shardio
+        meta = {"n_docs": self.n_docs, "vocab": self.vocab, "id_base": self.id_base, "stats_n_docs": self.stats.n_docs,
+                "avgdl": float(self.stats.avgdl)}
+        shardio.write_shard(path, "bm25", meta, {
+            "term_ptr": self.term_ptr, "post_doc": self.post_doc, "post_imp": self.post_imp, "dl": self.dl,
+            "df": torch.from_numpy(np.ascontiguousarray(self.stats.df, dtype=np.int64))})
+
+    @classmethod
+    def load(cls, path: str, device) -> "Bm25Index":
+        """Impacts are stored, so no statistic is recomputed: scores are bit-identical to the saved index.
+        Only the per-block offsets are rebuilt (they depend on the library's block size)."""
+        from . import shardio
+        dev = torch.device(device)
+        meta, a, _ = shardio.read_shard(path, device=dev, expect_kind="bm25")
+        nnz = a["post_doc"].numel()
+        if a["post_imp"].numel() != nnz or a["term_ptr"].numel() != int(meta["vocab"]) + 1 or \
+                a["dl"].numel() != int(meta["n_docs"]):
+            raise shardio.ShardError(f"{path}: sections do not match the header")
+        # 16-byte aligned and padded by one group of 4 postings, as from_postings() lays them out
+        pd = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)
+        pi = torch.zeros(nnz + 4, dtype=torch.float32, device=dev)
+        pd[:nnz] = a["post_doc"]
+        pi[:nnz] = a["post_imp"]
+        stats = Bm25Stats(n_docs=int(meta["stats_n_docs"]), df=a["df"].cpu().numpy().astype(np.int64),
+                          avgdl=float(meta["avgdl"]))
+        term_ptr = a["term_ptr"]
+        block_ptr = ops.bm25_block_index(term_ptr, pd[:nnz], int(meta["n_docs"]))
+        return cls(term_ptr, pd[:nnz], pi[:nnz], block_ptr, int(meta["n_docs"]), int(meta["vocab"]), a["dl"], stats,
+                   int(meta["id_base"]))
+
     # ---- search ----------------------------------------------------------------------------
     def search_terms(self, q_terms: torch.Tensor, k: int):
         """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids)."""

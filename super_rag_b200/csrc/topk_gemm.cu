@@ -88,6 +88,13 @@ struct TopkParams {
     int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
     int window;       // tiles the leader may run ahead of the slowest follower
     int debug;        // SRAG_TOPK_DEBUG perf-dissection bits (results are WRONG when set): 2 no MMA, 4 no epilogue work
+    // metadata pre-filter (all null = off): a row is eligible for query q iff
+    //   (row_tags == null  || (row_tags[row] & q_tag_mask[q]) != 0) &&
+    //   (row_group == null || q_group[q] < 0 || row_group[row] == q_group[q])
+    const uint32_t* row_tags;
+    const int32_t* row_group;
+    const uint32_t* q_tag_mask;
+    const int32_t* q_group;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -360,6 +367,15 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         float thr_own = -INFINITY, thr_shared = -INFINITY;
         uint32_t published = 0;
         float thr = valid_q ? -INFINITY : INFINITY;
+        // metadata pre-filter: checked only for the few scores that beat the running threshold
+        const bool filtered = p.row_tags != nullptr || p.row_group != nullptr;
+        const uint32_t f_mask = p.row_tags ? __ldg(p.q_tag_mask + qx) : 0xFFFFFFFFu;
+        const int32_t f_group = p.row_group ? __ldg(p.q_group + qx) : -1;
+        auto eligible = [&](uint32_t row) -> bool {
+            if (p.row_tags && (__ldg(p.row_tags + row) & f_mask) == 0) return false;
+            if (f_group >= 0 && __ldg(p.row_group + row) != f_group) return false;
+            return true;
+        };
 
         auto load_scales = [&](int c, float (&r)[SPL]) {
             const int64_t row0 = (int64_t)c * BLOCK_N + col0 + lane * SPL;
@@ -472,7 +488,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                         if (g[q] > thr) {
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
-                                if (sv[q * 8 + e] > thr)
+                                if (sv[q * 8 + e] > thr && (!filtered || eligible(r0 + q * 8 + e)))
                                 {
                                     float v = sv[q * 8 + e];
                                     thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
@@ -795,11 +811,14 @@ extern "C" int srag_topk_workspace_bytes(int64_t n_rows, int n_queries, int k, s
     return SRAG_OK;
 }
 
-extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
-                                const void* queries_bf16, const float* q_scale, int n_queries, int k,
-                                int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
-                                size_t workspace_bytes, void* stream) {
+static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                            const void* queries_bf16, const float* q_scale, int n_queries, int k, int64_t id_base,
+                            const uint32_t* row_tags, const int32_t* row_group, const uint32_t* q_tag_mask,
+                            const int32_t* q_group, float* out_scores, int64_t* out_ids, void* workspace,
+                            size_t workspace_bytes, void* stream) {
     SRAG_CHECK_ARG(queries_bf16 && out_scores && out_ids && workspace, "null pointer argument");
+    SRAG_CHECK_ARG((row_tags == nullptr) == (q_tag_mask == nullptr) && (row_group == nullptr) == (q_group == nullptr),
+                   "row_tags / q_tag_mask and row_group / q_group come in pairs");
     SRAG_CHECK_ARG(n_rows == 0 || (corpus_bf16 && row_scale), "null corpus / row_scale");
     SRAG_CHECK_ARG(n_queries >= 1 && k >= 1 && k <= SRAG_MAX_TOPK, "bad sizes n_queries=%d k=%d", n_queries, k);
     SRAG_CHECK_ARG(dim >= 8 && dim % 8 == 0, "dim=%d must be a positive multiple of 8", dim);
@@ -843,6 +862,10 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
     }
     prm.window = pl.window;
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
+    prm.row_tags = n_rows > 0 ? row_tags : nullptr;
+    prm.row_group = n_rows > 0 ? row_group : nullptr;
+    prm.q_tag_mask = q_tag_mask;
+    prm.q_group = q_group;
     SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes + pl.gthr_bytes + pl.progress_bytes, st));
     const bool prof = g_prof.on && g_prof.n < PROF_RING;
     if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][0], st));
@@ -875,6 +898,23 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
         ++g_prof.n;
     }
     return SRAG_OK;
+}
+
+extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                                const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                                int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+    return topk_search_impl(corpus_bf16, row_scale, n_rows, dim, queries_bf16, q_scale, n_queries, k, id_base, nullptr,
+                            nullptr, nullptr, nullptr, out_scores, out_ids, workspace, workspace_bytes, stream);
+}
+
+extern "C" int srag_topk_search_filtered(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                                         const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                                         int64_t id_base, const uint32_t* row_tags, const int32_t* row_group,
+                                         const uint32_t* q_tag_mask, const int32_t* q_group, float* out_scores,
+                                         int64_t* out_ids, void* workspace, size_t workspace_bytes, void* stream) {
+    return topk_search_impl(corpus_bf16, row_scale, n_rows, dim, queries_bf16, q_scale, n_queries, k, id_base, row_tags,
+                            row_group, q_tag_mask, q_group, out_scores, out_ids, workspace, workspace_bytes, stream);
 }
 
 extern "C" int srag_prof_enable(int on) {

@@ -99,6 +99,35 @@ class FulltextCollection:
                                                     self.vocab)
             return self._index
 
+    # -- persistence: token ids, texts and metadata (the tokenizer itself is code, passed again on load) --
+    def save(self, path: str) -> None:
+        from . import shardio
+        with self.lock:
+            lens = np.fromiter((len(t) for t in self._tokens), dtype=np.int64, count=len(self._tokens))
+            doc_ptr = np.zeros(len(lens) + 1, dtype=np.int64)
+            np.cumsum(lens, out=doc_ptr[1:])
+            flat = np.concatenate(self._tokens) if len(self._tokens) else np.zeros(0, dtype=np.int64)
+            shardio.write_shard(path, "fulltext", {"name": self.name, "vocab": self.vocab, "n_docs": len(self.texts)},
+                                {"tokens": torch.from_numpy(flat), "doc_ptr": torch.from_numpy(doc_ptr)},
+                                {"docs": {"texts": self.texts, "metas": self.metas}})
+
+    @classmethod
+    def load(cls, path: str, tokenizer: Optional[Callable[[str], List[int]]] = None, vocab: Optional[int] = None,
+             name: Optional[str] = None, device: Optional[str] = None) -> "FulltextCollection":
+        from . import shardio
+        meta, a, blobs = shardio.read_shard(path, expect_kind="fulltext")
+        if tokenizer is not None and vocab is None:
+            vocab = int(meta["vocab"])
+        col = cls(name or meta["name"], tokenizer, vocab, device)
+        if col.vocab != int(meta["vocab"]):
+            raise shardio.ShardError(f"{path}: vocabulary size {meta['vocab']} != tokenizer's {col.vocab}")
+        tokens, doc_ptr = a["tokens"].numpy(), a["doc_ptr"].numpy()
+        col.texts, col.metas = list(blobs["docs"]["texts"]), list(blobs["docs"]["metas"])
+        if len(doc_ptr) != len(col.texts) + 1 or (len(doc_ptr) and int(doc_ptr[-1]) != len(tokens)):
+            raise shardio.ShardError(f"{path}: token table does not match the doc table")
+        col._tokens = [tokens[doc_ptr[i]:doc_ptr[i + 1]].copy() for i in range(len(col.texts))]
+        return col
+
     def query_terms(self, query: Optional[str], keywords: Optional[Iterable[str]]) -> List[int]:
         """Custom keywords replace the query text (FulltextSearchParams.keywords, view_models.py:1045-1047)."""
         text = " ".join(keywords) if keywords else (query or "")

@@ -83,9 +83,23 @@ def topk_workspace_bytes(n_rows: int, n_queries: int, k: int) -> int:
 
 def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Tensor, q_scale: torch.Tensor,
                 k: int, id_base: int = 0, workspace: Optional[torch.Tensor] = None,
-                out_scores: Optional[torch.Tensor] = None, out_ids: Optional[torch.Tensor] = None):
-    """Exact top-k of bf16 queries [B,D] against a bf16 corpus [N,D]; returns (scores fp32 [B,k], ids int64 [B,k])."""
+                out_scores: Optional[torch.Tensor] = None, out_ids: Optional[torch.Tensor] = None,
+                row_tags: Optional[torch.Tensor] = None, q_tag_mask: Optional[torch.Tensor] = None,
+                row_group: Optional[torch.Tensor] = None, q_group: Optional[torch.Tensor] = None):
+    """Exact top-k of bf16 queries [B,D] against a bf16 corpus [N,D]; returns (scores fp32 [B,k], ids int64 [B,k]).
+
+    Optional metadata pre-filter (int32 tensors holding 32-bit patterns): row r is eligible for query b iff
+    ``row_tags[r] & q_tag_mask[b] != 0`` (when given) and ``q_group[b] < 0 or row_group[r] == q_group[b]`` (when given)."""
     _need_cuda(corpus, row_scale, queries, q_scale)
+    if (row_tags is None) != (q_tag_mask is None) or (row_group is None) != (q_group is None):
+        raise SragError("row_tags / q_tag_mask and row_group / q_group come in pairs")
+    for t, n_expect, what in ((row_tags, corpus.shape[0], "row_tags"), (row_group, corpus.shape[0], "row_group"),
+                              (q_tag_mask, queries.shape[0], "q_tag_mask"), (q_group, queries.shape[0], "q_group")):
+        if t is not None:
+            _need_cuda(t)
+            if t.dtype != torch.int32 or t.numel() != n_expect or not t.is_contiguous():
+                raise SragError(f"{what} must be a contiguous int32 tensor of {n_expect} elements")
+    filtered = row_tags is not None or row_group is not None
     if corpus.dtype != torch.bfloat16 or queries.dtype != torch.bfloat16:
         raise SragError("corpus and queries must be bfloat16 (use ingest_rows)")
     lib = _lib.load()
@@ -103,6 +117,13 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
             if workspace is None or workspace.numel() < need:
                 workspace = torch.empty(need, dtype=torch.uint8, device=dev)
             q = queries[b0:b0 + nb]
+            if filtered:
+                _lib.check(lib.srag_topk_search_filtered(
+                    _ptr(corpus), _ptr(row_scale), N, D, _ptr(q), _ptr(q_scale[b0:b0 + nb]), nb, k, id_base,
+                    _ptr(row_tags), _ptr(row_group), _ptr(q_tag_mask[b0:b0 + nb] if q_tag_mask is not None else None),
+                    _ptr(q_group[b0:b0 + nb] if q_group is not None else None), _ptr(scores[b0:b0 + nb]),
+                    _ptr(ids[b0:b0 + nb]), _ptr(workspace), workspace.numel(), _stream(dev)), "srag_topk_search_filtered")
+                continue
             _lib.check(lib.srag_topk_search(_ptr(corpus), _ptr(row_scale), N, D, _ptr(q), _ptr(q_scale[b0:b0 + nb]),
                                             nb, k, id_base, _ptr(scores[b0:b0 + nb]), _ptr(ids[b0:b0 + nb]),
                                             _ptr(workspace), workspace.numel(), _stream(dev)), "srag_topk_search")

@@ -10,7 +10,9 @@ name, not in the connector instance.
 
 Scores are similarities (higher is better): cosine or inner product, order (score desc, chunk
 row asc). ``score_threshold`` / ``filter`` kwargs are accepted and ignored exactly as the
-reference does (seekdb_connector.py:99-100) unless ctx["apply_score_threshold"] is set.
+reference does (seekdb_connector.py:99-100) unless ctx["apply_score_threshold"] / ctx["apply_filter"]
+is set; with ``apply_filter`` the metadata filter built by ``ContextManager._create_combined_filter``
+(context/context.py:74-111) is folded into the scan.
 """
 from __future__ import annotations
 
@@ -21,7 +23,7 @@ from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
-from . import ops
+from . import ops, shardio
 from ._lib import SragError
 from .models import DocumentWithScore, QueryResult, QueryWithEmbedding
 
@@ -69,6 +71,89 @@ class HostDocTable:
         return self.ids[row], self.texts[row], self.metas[row]
 
 
+MISSING_BIT = 1 << 31      # row has no `indexer` field ({"indexer": {"$exists": False}})
+NO_SUCH_GROUP = 0x7FFFFFFF  # chat_id never seen in this collection: matches no row
+
+
+def _i32(pattern: int) -> int:
+    """32-bit pattern as the signed value an int32 tensor stores."""
+    pattern &= 0xFFFFFFFF
+    return pattern - (1 << 32) if pattern & 0x80000000 else pattern
+
+
+class RowTagger:
+    """Interns the two metadata fields the reference filters on (context/context.py:74-111): `indexer`
+    -> one bit of a 32-bit tag word (bit 31 = field absent), `chat_id` -> a small integer (0 = absent)."""
+
+    def __init__(self):
+        self.indexer_bit: Dict[str, int] = {}
+        self.chat_group: Dict[str, int] = {}
+
+    def encode(self, meta: Optional[dict]) -> Tuple[int, int]:
+        meta = meta or {}
+        tag = MISSING_BIT
+        if meta.get("indexer") is not None:
+            name = str(meta["indexer"])
+            if name not in self.indexer_bit:
+                if len(self.indexer_bit) >= 31:
+                    raise ValueError("more than 31 distinct `indexer` values in one collection")
+                self.indexer_bit[name] = len(self.indexer_bit)
+            tag = 1 << self.indexer_bit[name]
+        group = 0
+        if meta.get("chat_id") is not None:
+            group = self.chat_group.setdefault(str(meta["chat_id"]), len(self.chat_group) + 1)
+        return tag, group
+
+    # -- filter dict -> (tag mask, group) ------------------------------------------------------
+    def _tag_clause(self, cond) -> int:
+        if isinstance(cond, dict):
+            if set(cond) == {"$in"}:
+                m = 0
+                for v in cond["$in"]:
+                    b = self.indexer_bit.get(str(v))
+                    m |= 0 if b is None else 1 << b
+                return m
+            if set(cond) == {"$exists"}:
+                return MISSING_BIT if not cond["$exists"] else (0xFFFFFFFF & ~MISSING_BIT)
+            raise ValueError(f"unsupported filter operator {cond!r}")
+        b = self.indexer_bit.get(str(cond))
+        return 0 if b is None else 1 << b
+
+    def compile(self, flt) -> Tuple[int, int]:
+        """-> (tag mask, group); mask 0xFFFFFFFF / group -1 mean "no constraint". Grammar = what
+        `_create_combined_filter` emits, plus bare `indexer` clauses: {"or": [tag clauses]}, {"chat_id": x},
+        {"indexer": v | {"$in": [...]} | {"$exists": bool}}, {"and": [clauses]}."""
+        if not flt:
+            return 0xFFFFFFFF, -1
+        if not isinstance(flt, dict) or len(flt) != 1:
+            raise ValueError(f"unsupported filter {flt!r}")
+        (key, val), = flt.items()
+        if key == "and":
+            mask, group = 0xFFFFFFFF, -1
+            for c in val:
+                m, g = self.compile(c)
+                mask &= m
+                if g >= 0:
+                    if group >= 0 and g != group:
+                        group = NO_SUCH_GROUP
+                    else:
+                        group = g
+            return mask, group
+        if key == "or":
+            mask = 0
+            for c in val:
+                m, g = self.compile(c)
+                if g >= 0:
+                    raise ValueError("`chat_id` inside an `or` is not supported")
+                mask |= m
+            return mask, -1
+        if key == "indexer":
+            return self._tag_clause(val), -1
+        if key == "chat_id":
+            return 0xFFFFFFFF, self.chat_group.get(str(val), NO_SUCH_GROUP)
+        raise ValueError(f"unsupported filter field {key!r}")
+
+
 class DeviceCollection:
     """bf16 corpus matrix + fp32 row multipliers resident in HBM, growable, with tombstones."""
 
@@ -83,6 +168,9 @@ class DeviceCollection:
         self._rows: Optional[torch.Tensor] = None
         self._scale: Optional[torch.Tensor] = None
         self._ws: Optional[torch.Tensor] = None
+        self._tags: Optional[torch.Tensor] = None      # int32 [cap] tag words, int32 [cap] chat groups
+        self._group: Optional[torch.Tensor] = None
+        self.tagger = RowTagger()
         self._reserve = capacity
         self.lock = threading.Lock()
 
@@ -102,10 +190,14 @@ class DeviceCollection:
         dev = self._dev()
         rows = torch.empty(new_cap, self.dim, dtype=torch.bfloat16, device=dev)
         scale = torch.empty(new_cap, dtype=torch.float32, device=dev)
+        tags = torch.empty(new_cap, dtype=torch.int32, device=dev)
+        group = torch.empty(new_cap, dtype=torch.int32, device=dev)
         if self.n:
             rows[:self.n].copy_(self._rows[:self.n])
             scale[:self.n].copy_(self._scale[:self.n])
-        self._rows, self._scale = rows, scale
+            tags[:self.n].copy_(self._tags[:self.n])
+            group[:self.n].copy_(self._group[:self.n])
+        self._rows, self._scale, self._tags, self._group = rows, scale, tags, group
 
     @property
     def rows(self) -> torch.Tensor:
@@ -134,6 +226,9 @@ class DeviceCollection:
             emb = emb.to(dev, non_blocking=True).contiguous()
             ops.ingest_rows(emb, self.metric, out_bf16=self._rows[self.n:self.n + m],
                             out_scale=self._scale[self.n:self.n + m])
+            enc = [self.tagger.encode(mt) for mt in metas]
+            self._tags[self.n:self.n + m] = torch.tensor([_i32(t) for t, _ in enc], dtype=torch.int32).to(dev)
+            self._group[self.n:self.n + m] = torch.tensor([g for _, g in enc], dtype=torch.int32).to(dev)
             self.docs.append(ids, texts, metas)
             self.n += m
         return ids
@@ -146,9 +241,44 @@ class DeviceCollection:
                 self._scale[idx] = float("nan")  # tombstone: K1 never returns a NaN-scaled row
         return len(rows)
 
+    # -- persistence (on-disk shard) ---------------------------------------
+    def save(self, path: str) -> None:
+        """Write rows, multipliers (NaN tombstones included) and the doc table as one shard file."""
+        with self.lock:
+            meta = {"name": self.name, "dim": self.dim, "metric": self.metric, "n": self.n, "id_base": self.id_base}
+            docs = {"ids": self.docs.ids, "texts": self.docs.texts, "metas": self.docs.metas,
+                    "deleted": sorted(self.docs.deleted)}
+            shardio.write_shard(path, "vector", meta, {"rows": self.rows, "row_scale": self.row_scale}, {"docs": docs})
+
+    @classmethod
+    def load(cls, path: str, name: Optional[str] = None, device: Optional[str] = None) -> "DeviceCollection":
+        """Rebuild a collection from a shard written by save(); searches return bit-identical results."""
+        footer = shardio.read_footer(path)
+        meta = footer["meta"]
+        col = cls(name or meta["name"], int(meta["dim"]), int(meta["metric"]), device)
+        dev = col._dev()
+        meta, arrays, blobs = shardio.read_shard(path, device=dev, expect_kind="vector")
+        n = int(meta["n"])
+        rows, scale = arrays["rows"], arrays["row_scale"]
+        if tuple(rows.shape) != (n, col.dim) or rows.dtype != torch.bfloat16 or tuple(scale.shape) != (n,):
+            raise shardio.ShardError(f"{path}: rows / row_scale do not match the header")
+        col._rows, col._scale, col.n, col.id_base = rows, scale, n, int(meta["id_base"])
+        d = blobs["docs"]
+        if not (len(d["ids"]) == len(d["texts"]) == len(d["metas"]) == n):
+            raise shardio.ShardError(f"{path}: doc table does not match the header")
+        col.docs.ids, col.docs.texts, col.docs.metas = list(d["ids"]), list(d["texts"]), list(d["metas"])
+        col.docs.deleted = set(int(r) for r in d["deleted"])
+        col.docs.row_of = {i: r for r, i in enumerate(col.docs.ids) if r not in col.docs.deleted}
+        enc = [col.tagger.encode(mt) for mt in col.docs.metas]      # same interning order as the original appends
+        col._tags = torch.tensor([_i32(t) for t, _ in enc], dtype=torch.int32).to(dev)
+        col._group = torch.tensor([g for _, g in enc], dtype=torch.int32).to(dev)
+        return col
+
     # -- search -------------------------------------------------------------------------------
-    def search_batch(self, queries: torch.Tensor, top_k: int):
-        """queries [B, dim] (host or device, fp32 or bf16) -> (scores fp32 [B,k], ids int64 [B,k]) on device."""
+    def search_batch(self, queries: torch.Tensor, top_k: int, filters=None):
+        """queries [B, dim] (host or device, fp32 or bf16) -> (scores fp32 [B,k], ids int64 [B,k]) on device.
+        `filters`: None, one filter dict for the whole batch, or a list of B dicts (context.py:74-111 grammar);
+        the result is the exact top-k among the rows each query's filter admits."""
         dev = self._dev()
         q = queries.to(dev, non_blocking=True)
         if q.dtype not in (torch.float32, torch.bfloat16):
@@ -157,7 +287,19 @@ class DeviceCollection:
         need = ops.topk_workspace_bytes(self.n, min(q.shape[0], ops.MAX_QUERIES_PER_CALL), top_k)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
-        return ops.topk_search(self.rows, self.row_scale, qb, qs, top_k, id_base=self.id_base, workspace=self._ws)
+        kw = {}
+        if filters is not None and self.n:
+            per_q = filters if isinstance(filters, (list, tuple)) else [filters] * q.shape[0]
+            if len(per_q) != q.shape[0]:
+                raise ValueError(f"{len(per_q)} filters for {q.shape[0]} queries")
+            comp = [self.tagger.compile(f) for f in per_q]
+            if any(m != 0xFFFFFFFF for m, _ in comp):
+                kw["row_tags"] = self._tags[:self.n]
+                kw["q_tag_mask"] = torch.tensor([_i32(m) for m, _ in comp], dtype=torch.int32).to(dev)
+            if any(g >= 0 for _, g in comp):
+                kw["row_group"] = self._group[:self.n]
+                kw["q_group"] = torch.tensor([g for _, g in comp], dtype=torch.int32).to(dev)
+        return ops.topk_search(self.rows, self.row_scale, qb, qs, top_k, id_base=self.id_base, workspace=self._ws, **kw)
 
 
 _REGISTRY: Dict[str, DeviceCollection] = {}
@@ -191,6 +333,16 @@ class B200Client:
         with _REGISTRY_LOCK:
             _REGISTRY.pop(name, None)
 
+    def save_collection(self, name: str, path: str) -> None:
+        _REGISTRY[name].save(path)
+
+    def load_collection(self, path: str, name: Optional[str] = None, device=None) -> DeviceCollection:
+        """Register the collection stored at `path` (replacing one of the same name)."""
+        col = DeviceCollection.load(path, name, device)
+        with _REGISTRY_LOCK:
+            _REGISTRY[col.name] = col
+        return col
+
 
 class B200VectorStoreConnector:
     """Same constructor, attributes and methods as SeekDBVectorStoreConnector."""
@@ -202,6 +354,7 @@ class B200VectorStoreConnector:
         self.collection_name = self.ctx["collection"]        # KeyError like the reference
         self.device = ctx.get("device")
         self.apply_score_threshold = bool(ctx.get("apply_score_threshold", False))
+        self.apply_filter = bool(ctx.get("apply_filter", False))
         self.store = self                                    # seekdb_connector.py:45
         self.client = B200Client()
 
@@ -242,7 +395,7 @@ class B200VectorStoreConnector:
         if top_k > 0 and col.n > 0:
             k = min(top_k, ops.MAX_TOPK)
             q = torch.tensor([query.embedding], dtype=torch.float32)
-            scores, rows = col.search_batch(q, k)
+            scores, rows = col.search_batch(q, k, filters=kwargs.get("filter") if self.apply_filter else None)
             scores, rows = scores[0].tolist(), rows[0].tolist()
             for s, r in zip(scores, rows):
                 if r < 0:
@@ -254,8 +407,8 @@ class B200VectorStoreConnector:
         return QueryResult(query=query.query, results=results)
 
     # batched tensor API used by benchmarks and the sharded index
-    def search_batch(self, queries: torch.Tensor, top_k: int):
-        return self._collection().search_batch(queries, top_k)
+    def search_batch(self, queries: torch.Tensor, top_k: int, filters=None):
+        return self._collection().search_batch(queries, top_k, filters)
 
 
 _REFERENCE_ADAPTOR = None  # set by nodeflow_pack.install_connector() to the class it replaces
