@@ -137,6 +137,22 @@ int srag_fuse(const int64_t* ids, const float* scores, int n_lists, int n_querie
               int mode, int rank_const, double min_score, const double* weights_host,
               int k_out, int64_t* out_ids, double* out_scores, void* stream);
 
+/* ---- K5: maximal-marginal-relevance rerank ---------------------------------------------
+ * Replaces `maximal_marginal_relevance(query_vector, candidates, mmr_lambda, min_score)`
+ * (graphiti_core/search/search_utils.py:1884-1922) for candidates that are rows of the device
+ * corpus (ids as returned by srag_topk_search / srag_fuse):
+ *   c_i = row_i * row_scale[row_i]   (row_scale from srag_rows_ingest_f32 with the cosine metric)
+ *   mmr_i = lambda * (q . c_i) * q_scale + (lambda - 1) * max(0, max_{j != i} c_i . c_j)
+ * out_ids / out_scores [n_queries, m]: candidates with mmr_i >= min_score by score descending,
+ * ties in candidate order (the reference's stable sort); the rest of each row is -1 / -inf.
+ * Ids that are negative, out of range or tombstoned are skipped. q_scale = 1 keeps the
+ * reference's un-normalised query. 1 <= m <= SRAG_MAX_MMR.                                   */
+#define SRAG_MAX_MMR 256
+int srag_mmr_rerank(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                    const void* queries_bf16, const float* q_scale, int n_queries,
+                    const int64_t* cand_ids, int m, int64_t id_base, float mmr_lambda, float min_score,
+                    int64_t* out_ids, float* out_scores, void* stream);
+
 /* ---- K4: cross-shard candidate merge -------------------------------------------------
  * Final step after the all-gather of per-shard candidates.
  *   scores fp32 [n_shards, n_queries, kk], ids int64 same shape (id < 0 = padding)

@@ -41,3 +41,4 @@ from .fusion import (  # noqa: F401
     merge_shard_candidates,
 )
 from .filters import eval_filter, filter_rows  # noqa: F401
+from .mmr import mmr_rerank, mmr_scores  # noqa: F401

@@ -29,6 +29,7 @@ SIGNATURES = {
     "srag_topk_search": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _sz, _vp],
     "srag_topk_search_filtered": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                   _sz, _vp],
+    "srag_mmr_rerank": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp, _i32, _i64, _f32, _f32, _vp, _vp, _vp],
     "srag_prof_enable": [_i32],
     "srag_prof_read": [C.POINTER(_f64), C.POINTER(_f64), C.POINTER(_i32)],
     "srag_bm25_impacts": [_vp, _i32, _vp, _vp, _i64, _vp, _vp, _f32, _vp, _vp],

@@ -200,6 +200,31 @@ def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tenso
     return scores, ids
 
 
+# ---- K5 -----------------------------------------------------------------------------------
+MAX_MMR = 256
+
+
+def mmr_rerank(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Tensor, q_scale: torch.Tensor,
+               cand_ids: torch.Tensor, mmr_lambda: float = 0.5, min_score: float = -2.0, id_base: int = 0):
+    """Reference MMR (search_utils.py:1884-1922) over candidate rows of the device corpus.
+    cand_ids int64 [B, m] (-1 = none) -> (ids int64 [B, m], scores fp32 [B, m]) by score desc, -1 / -inf padded."""
+    _need_cuda(corpus, row_scale, queries, q_scale, cand_ids)
+    if corpus.dtype != torch.bfloat16 or queries.dtype != torch.bfloat16 or cand_ids.dtype != torch.int64:
+        raise SragError("corpus / queries must be bfloat16 and cand_ids int64")
+    B, m = cand_ids.shape
+    if queries.shape[0] != B or q_scale.numel() != B:
+        raise SragError("one query (and q_scale) per candidate list")
+    dev = queries.device
+    with torch.cuda.device(dev):
+        out_ids = torch.empty(B, m, dtype=torch.int64, device=dev)
+        out_scores = torch.empty(B, m, dtype=torch.float32, device=dev)
+        _lib.check(_lib.load().srag_mmr_rerank(_ptr(corpus), _ptr(row_scale), corpus.shape[0], queries.shape[1],
+                                               _ptr(queries.contiguous()), _ptr(q_scale), B, _ptr(cand_ids.contiguous()), m,
+                                               id_base, float(mmr_lambda), float(min_score), _ptr(out_ids),
+                                               _ptr(out_scores), _stream(dev)), "srag_mmr_rerank")
+    return out_ids, out_scores
+
+
 # ---- K3 / K4 ----------------------------------------------------------------------------
 def fuse(ids: torch.Tensor, scores: Optional[torch.Tensor], mode: int, k_out: int, rank_const: int = 1,
          min_score: float = 0.0, weights: Optional[Sequence[float]] = None):

@@ -34,3 +34,10 @@ def golden():
     import json
     with open(os.path.join(ROOT, "tests", "golden", "fusion_golden.json"), encoding="utf-8") as f:
         return json.load(f)["cases"]
+
+
+@pytest.fixture(scope="session")
+def mmr_golden():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "mmr_golden.json"), encoding="utf-8") as f:
+        return json.load(f)["cases"]

@@ -18,6 +18,7 @@ Pinned here:
   _apply_fallback_strategy   super_rag/nodeflow/runners/rerank.py:173-202
   SeekDBVectorStoreConnector.search / _convert_scored_point_to_document_with_score
                              super_rag/vectorstore/seekdb_connector.py:98-156
+  maximal_marginal_relevance graphiti_core/search/search_utils.py:1884-1922  (-> mmr_golden.json)
 """
 from __future__ import annotations
 
@@ -148,7 +149,47 @@ def _doc_to_json(d):
     return {"text": d.text, "score": d.score, "metadata": d.metadata}
 
 
+def _load_mmr():
+    import logging
+    from time import time
+    from numpy.typing import NDArray
+    su = os.path.join(REF, "super_rag/graphiti/graphiti_core/search/search_utils.py")
+    he = os.path.join(REF, "super_rag/graphiti/graphiti_core/helpers.py")
+    ns = {"np": np, "NDArray": NDArray, "time": time, "logger": logging.getLogger("ref"), "DEFAULT_MMR_LAMBDA": 0.5}
+    for name, code in _extract_functions(he, ["normalize_l2"]).items():
+        exec(compile(code, he, "exec"), ns)
+    for name, code in _extract_functions(su, ["maximal_marginal_relevance"]).items():
+        exec(compile(code, su, "exec"), ns)
+    return ns["maximal_marginal_relevance"]
+
+
+def make_mmr_golden():
+    """Inputs are multiples of 1/64 in [-4, 4] (exact in bf16), so the GPU path sees the same numbers."""
+    mmr = _load_mmr()
+    rng = np.random.default_rng(77)
+    cases = []
+    for m, d, lam, ms in [(1, 8, 0.5, -2.0), (2, 8, 0.5, -2.0), (5, 16, 0.5, -2.0), (12, 32, 0.7, -2.0),
+                          (33, 64, 0.3, 0.0), (64, 128, 0.5, 0.1), (100, 128, 0.5, -2.0), (200, 64, 0.9, -2.0),
+                          (7, 16, 1.0, -2.0), (7, 16, 0.0, -2.0)]:
+        q = (rng.integers(-256, 257, d) / 64.0).tolist()
+        C = rng.integers(-256, 257, (m, d)) / 64.0
+        if m >= 5:
+            C[3] = C[1]                      # duplicate embedding: similarity 1, tie in the score
+            C[4] = 0.0                       # zero vector: normalize_l2 leaves it unchanged
+        cand = {f"u{i}": C[i].tolist() for i in range(m)}
+        ids, sc = mmr(q, cand, lam, ms)
+        cases.append({"query": q, "candidates": [C[i].tolist() for i in range(m)], "mmr_lambda": lam, "min_score": ms,
+                      "order": [int(u[1:]) for u in ids], "scores": [float(x) for x in sc]})
+    path = os.path.join(OUT, "mmr_golden.json")
+    with open(path, "w", encoding="utf-8") as f:
+        json.dump({"reference_commit": "49de377", "cases": cases}, f)
+    print("wrote", path, len(cases))
+
+
 def main():
+    if "--mmr-only" in sys.argv:
+        return make_mmr_golden()
+    make_mmr_golden()
     rng = np.random.default_rng(20261104)
     rrf, cos, norm_l2 = _load_graphiti_functions()
     golden = {"reference_commit": "49de377", "cases": {}}

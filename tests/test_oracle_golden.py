@@ -117,3 +117,12 @@ def test_merge_shard_candidates():
     ms, mi = oracle.merge_shard_candidates(s, i, 4)
     assert mi[0].tolist() == [2, 4, 9, 1]
     assert ms[0].tolist() == [np.float32(0.9), np.float32(0.9), np.float32(0.6), np.float32(0.5)]
+
+
+def test_mmr_matches_reference(mmr_golden):
+    """oracle.mmr_rerank == maximal_marginal_relevance (search_utils.py:1884-1922) on the reference's own outputs."""
+    assert len(mmr_golden) >= 10
+    for c in mmr_golden:
+        order, scores = oracle.mmr_rerank(np.array(c["query"]), np.array(c["candidates"]), c["mmr_lambda"], c["min_score"])
+        assert order.tolist() == c["order"]
+        np.testing.assert_allclose(scores, np.array(c["scores"]), rtol=0, atol=1e-12)
