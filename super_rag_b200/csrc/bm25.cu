@@ -35,7 +35,7 @@ constexpr int BM25_CAND_MAX = 1024;
 
 // stream flags of a ring slot
 constexpr uint32_t SLOT_NEW_ITEM = 1u;  // first chunk of a (query, block) item
-constexpr uint32_t SLOT_NEW_TERM = 2u;  // first chunk of a term (not the item's first term)
+constexpr uint32_t SLOT_NEW_TERM = 2u;  // first chunk of a term that needs a barrier before it (see the producer)
 constexpr uint32_t SLOT_END = 4u;       // no data: the CTA's item list is exhausted
 
 struct SlotMeta {  // written by the producer before it issues the slot's copies
@@ -183,6 +183,98 @@ __device__ void select_exact(Bm25Smem* sm, int k, int32_t doc_base, uint32_t tot
     }
 }
 
+// Fast exact top-k for a tile whose matches are dense (phase 0, and phase-1 fallbacks): BM25 scores of one
+// block sit in a few binades, so a radix pass over the top bits funnels every match into a handful of
+// histogram bins (serialised shared-memory atomics). Here the histogram is taken over the DISTANCE to the
+// tile maximum in units of 2^13 ulps: the k best are spread over many bins near 0, everything further than
+// two binades below the maximum is only counted. One scan for the maximum, one for the histogram, one to
+// emit; the bin holding the k-th value is resolved exactly by ranking its few members (ties -> lowest doc id).
+// Returns false, with nothing emitted, when the k-th value is not within reach (caller falls back to the
+// radix select). Precondition: more than k matches in the tile, out_count == 0.
+constexpr int NEAR_SHIFT = 13;
+__device__ bool select_near_max(Bm25Smem* sm, int k, int32_t doc_base, uint64_t* out) {
+    const float4* a4 = reinterpret_cast<const float4*>(sm->acc);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t mx = 0;
+    for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+        const float4 v = a4[i];
+        mx = max(max(mx, __float_as_uint(v.x)), max(__float_as_uint(v.y), max(__float_as_uint(v.z), __float_as_uint(v.w))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    for (int i = threadIdx.x; i < RADIX_BINS; i += BM25_THREADS) sm->hist[i] = 0;
+    consumer_sync();  // also protects warp_tmp reuse
+    if (lane == 0) sm->warp_tmp[w] = mx;
+    consumer_sync();
+#pragma unroll
+    for (int i = 0; i < BM25_THREADS / 32; ++i) mx = max(mx, sm->warp_tmp[i]);
+    for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+        const float4 v = a4[i];
+        const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t bin = (mx - b[j]) >> NEAR_SHIFT;
+            if (b[j] != 0 && bin < (uint32_t)RADIX_BINS) atomicAdd(&sm->hist[bin], 1u);
+        }
+    }
+    consumer_sync();
+    // prefix scan from bin 0 (nearest the maximum): thread t owns bins [PER t, PER t + PER)
+    constexpr int PER = RADIX_BINS / BM25_THREADS;
+    uint32_t mine = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) mine += sm->hist[threadIdx.x * PER + i];
+    uint32_t total;
+    const uint32_t above = block_excl_scan(mine, sm->warp_tmp, &total);
+    if (total < (uint32_t)k) return false;  // uniform: the k-th value lies beyond the histogram's reach
+    if (above < (uint32_t)k && above + mine >= (uint32_t)k) {
+        uint32_t run = above;
+        for (int i = 0; i < PER; ++i) {
+            const uint32_t h = sm->hist[threadIdx.x * PER + i];
+            if (run + h >= (uint32_t)k) {
+                sm->sel_bin = (uint32_t)(threadIdx.x * PER + i);
+                sm->sel_above = run;
+                break;
+            }
+            run += h;
+        }
+        sm->cand_count = 0;
+    }
+    consumer_sync();
+    const uint32_t sel_bin = sm->sel_bin, need = (uint32_t)k - sm->sel_above;
+    const uint32_t pop = sm->hist[sel_bin];
+    if (pop > (uint32_t)BM25_CAND_MAX) return false;  // uniform
+    for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+        const float4 v = a4[i];
+        const uint32_t b[4] = {__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (b[j] == 0) continue;
+            const uint32_t bin = (mx - b[j]) >> NEAR_SHIFT;
+            if (bin < sel_bin) {
+                const uint32_t slot = atomicAdd(&sm->out_count, 1u);
+                out[slot] = srag_pack_key(b[j], (uint32_t)(doc_base + 4 * i + j));
+            } else if (bin == sel_bin) {
+                sm->cand[atomicAdd(&sm->cand_count, 1u)] = (uint16_t)(4 * i + j);
+            }
+        }
+    }
+    consumer_sync();
+    // the bin of the k-th value: take its `need` best members, equal scores by ascending doc id
+    for (uint32_t e = threadIdx.x; e < pop; e += BM25_THREADS) {
+        const uint32_t de = sm->cand[e], be = __float_as_uint(sm->acc[de]);
+        uint32_t rank = 0;
+        for (uint32_t f = 0; f < pop; ++f) {
+            const uint32_t df = sm->cand[f], bf = __float_as_uint(sm->acc[df]);
+            rank += (bf > be) || (bf == be && df < de);
+        }
+        if (rank < need) {
+            const uint32_t slot = atomicAdd(&sm->out_count, 1u);
+            out[slot] = srag_pack_key(be, (uint32_t)(doc_base + de));
+        }
+    }
+    return true;
+}
+
 // One work item = (query, 16384-document block). Persistent CTAs walk the items of one phase:
 //   phase 0  every `stride`-th block of each query, exact block top-k (select_exact);
 //   phase 1  the remaining blocks, filtered by tau[q] = k-th best score over the phase-0 blocks of the
@@ -285,6 +377,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         for (; p0.ql < nq; p0 = p1, p1 = p2, p2 = p3, p3 = advance(p3)) {
             const int ql = p0.ql, blk = block_of(p0.j);
             bool first_of_item = true;
+            uint32_t last_hr = 0;  // valid postings of the previous chunk of this item
             for (int j0 = 0; j0 < max_terms; j0 += 32) {
                 if (j0 > 0) {  // queries with more than 32 terms: fetched in line
                     float unused;
@@ -315,6 +408,14 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                     const uint32_t n = !valid ? 0u : (len_u - off < (uint32_t)BM25_CHUNK ? len_u - off : (uint32_t)BM25_CHUNK);
                     const uint32_t cum = warp_incl_scan(n);
                     const uint32_t in_round = total - base < 32u ? total - base : 32u;
+                    // A term boundary needs a CTA barrier only if either side of it involves more than the first
+                    // consumer warp (threads 0..31 own postings 0..127 of a chunk): a run of short slices is
+                    // applied by that one warp in program order.
+                    const uint32_t hr = !valid ? 0u : (hi_u - off < (uint32_t)BM25_CHUNK ? hi_u - off : (uint32_t)BM25_CHUNK);
+                    uint32_t prev_hr = __shfl_up_sync(FULL, hr, 1);
+                    if (lane == 0) prev_hr = last_hr;
+                    last_hr = __shfl_sync(FULL, hr, in_round - 1);
+                    const bool term_barrier = j == 0 && (hr > 128u || prev_hr > 128u);
                     uint32_t done = 0, cum_base = 0;
                     while (done < in_round) {
                         // as many chunks as fit half the ring at once (a chunk is at most a ninth of it)
@@ -333,8 +434,8 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                                 m.ql = ql;
                                 m.blk = blk;
                                 m.lo_rel = j == 0 ? (int32_t)lo_u : 0;
-                                m.hi_rel = hi_u - off < (uint32_t)BM25_CHUNK ? (int32_t)(hi_u - off) : BM25_CHUNK;
-                                m.flags = (first_of_item && i == 0) ? SLOT_NEW_ITEM : (j == 0 ? SLOT_NEW_TERM : 0u);
+                                m.hi_rel = (int32_t)hr;
+                                m.flags = (first_of_item && i == 0) ? SLOT_NEW_ITEM : (term_barrier ? SLOT_NEW_TERM : 0u);
                                 m.tau = tau0;
                                 m.pos = my_pos;
                                 m.n = n;
@@ -435,7 +536,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             }
             (void)block_excl_scan(nz, sm->warp_tmp, &total);
         }
-        select_exact(sm, k, doc_base, total, out);
+        if ((debug & 64) || !select_near_max(sm, k, doc_base, out)) select_exact(sm, k, doc_base, total, out);
     };
 
     for (;;) {
