@@ -56,7 +56,10 @@ def load():
         if _lib is not None:
             return _lib
         path = _build.LIB_PATH
-        if not _build.is_fresh():
+        override = os.environ.get("SRAG_B200_LIB")  # A/B experiments: load exactly this build
+        if override:
+            path = override
+        elif not _build.is_fresh():
             try:
                 path = _build.build()
             except Exception as e:  # no nvcc on this machine: use the shipped .so if there is one

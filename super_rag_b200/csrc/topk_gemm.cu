@@ -130,7 +130,7 @@ __device__ __noinline__ float heap_replace_root(uint64_t* heap, int k, uint32_t 
 // ---------------------------------------------------------------------------------------
 // main kernel
 // ---------------------------------------------------------------------------------------
-template <int G, bool RQ, int EW>
+template <int G, bool RQ, int EW, bool FILT = false>  // FILT: metadata pre-filter compiled into the push path
 __global__ void __launch_bounds__(64 + 32 * EW, 1)
 topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                  const TopkParams p) {
@@ -368,7 +368,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         uint32_t published = 0;
         float thr = valid_q ? -INFINITY : INFINITY;
         // metadata pre-filter: checked only for the few scores that beat the running threshold
-        const bool filtered = p.row_tags != nullptr || p.row_group != nullptr;
+        constexpr bool filtered = FILT;  // a template parameter: the unfiltered kernel carries none of this
         const uint32_t f_mask = p.row_tags ? __ldg(p.q_tag_mask + qx) : 0xFFFFFFFFu;
         const int32_t f_group = p.row_group ? __ldg(p.q_group + qx) : -1;
         auto eligible = [&](uint32_t row) -> bool {
@@ -770,12 +770,12 @@ struct ProfState {
     bool created = false;
 } g_prof;
 
-template <int G, bool RQ, int EW>
+template <int G, bool RQ, int EW, bool FILT = false>
 int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, const TopkParams& prm,
                 cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(topk_gemm_kernel<G, RQ, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        SRAG_CUDA(cudaFuncSetAttribute(topk_gemm_kernel<G, RQ, EW, FILT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem_bytes<G, RQ>()));
         attr_done = true;
     }
@@ -791,7 +791,7 @@ int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, co
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    SRAG_CUDA(cudaLaunchKernelEx(&cfg, topk_gemm_kernel<G, RQ, EW>, tq, tc, prm));
+    SRAG_CUDA(cudaLaunchKernelEx(&cfg, topk_gemm_kernel<G, RQ, EW, FILT>, tq, tc, prm));
     return SRAG_OK;
 }
 
@@ -877,6 +877,15 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
         rc = make_tmap(&tc, corpus_bf16, n_rows, dim, block_n / pl.cta_group, true);
         if (rc) return rc;
         const int sel = (pl.cta_group == 2 ? 4 : 0) | (rq ? 2 : 0) | (ew == 8 ? 1 : 0);
+        if (prm.row_tags || prm.row_group) {
+            // the filtered kernel exists for the default plans only (streaming queries, 4 epilogue warps)
+            if (rq || ew != 4) {
+                srag_set_error("the metadata filter is not available with SRAG_TOPK_RQ / SRAG_TOPK_EPI_WARPS overrides");
+                return SRAG_E_INVALID;
+            }
+            rc = pl.cta_group == 2 ? launch_main<2, false, 4, true>(pl, tq, tc, prm, st)
+                                   : launch_main<1, false, 4, true>(pl, tq, tc, prm, st);
+        } else
         switch (sel) {
             case 0: rc = launch_main<1, false, 4>(pl, tq, tc, prm, st); break;
             case 1: rc = launch_main<1, false, 8>(pl, tq, tc, prm, st); break;
