@@ -14,6 +14,36 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
+def test_c1_connector_full_size_vs_oracle():
+    """C1: 100k x 1024 fp32 embeddings, top-5, through the connector API (single-query calls and the batch
+    call), against the fp64 oracle on the bf16-rounded inputs the device stores."""
+    import torch
+    import oracle
+    from parity import TOL, check_topk_against_full_scores
+    from super_rag_b200.models import QueryWithEmbedding
+    from super_rag_b200.vectorstore import B200Client, VectorStoreConnectorAdaptor
+    n, d, nq, k = 100_000, 1024, 256, 5
+    rng = np.random.default_rng(1234)
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    Q = rng.standard_normal((nq, d)).astype(np.float32)
+    src = rng.integers(0, n, nq // 2)
+    Q[nq // 2:] = C[src] + 0.1 * rng.standard_normal((nq // 2, d)).astype(np.float32)
+    B200Client().delete_collection("t_c1")
+    col = B200Client().create_collection("t_c1", d)
+    col.append(torch.from_numpy(C), metas=[{"row": r} for r in range(n)])
+    con = VectorStoreConnectorAdaptor("b200", {"collection": "t_c1", "vector_size": d}).connector
+    s, i = con.search_batch(torch.from_numpy(Q), k)
+    s, i = s.cpu().numpy(), i.cpu().numpy()
+    full = oracle.exact_topk_scores_f64(oracle.bf16_round(C), oracle.bf16_round(Q), "cosine")
+    check_topk_against_full_scores(s, i, full, k, TOL)
+    assert (i[nq // 2:, 0] == src).all()
+    for b in (0, 1, nq // 2, nq - 1):       # the single-query API returns the batch call's row
+        res = con.search(QueryWithEmbedding(query="q", top_k=k, embedding=Q[b].tolist()))
+        assert [r.metadata["row"] for r in res.results] == i[b].tolist()
+        assert np.allclose([r.score for r in res.results], s[b], atol=1e-6)
+    B200Client().delete_collection("t_c1")
+
+
 def _corpus(torch, n, d, dev):
     g = torch.Generator(device=dev)
     g.manual_seed(1)
