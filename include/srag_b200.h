@@ -73,6 +73,10 @@ int srag_rows_scale_bf16(const void* rows_bf16, int64_t n, int dim, float* scale
  *   out_scores [n_queries, k] fp32, out_ids [n_queries, k] int64 = id_base + row
  *   1 <= k <= SRAG_MAX_TOPK                                                           */
 int srag_topk_workspace_bytes(int64_t n_rows, int n_queries, int k, size_t* bytes);
+/* Same plus room for a zero-padded copy of the queries (whole 128 / 256-row query tiles). Give the
+ * search a workspace of this size and small or ragged batches avoid mostly-out-of-bounds TMA boxes
+ * (1.6 x faster at B = 1); with the smaller size above the search still works, unpadded.          */
+int srag_topk_workspace_bytes_ex(int64_t n_rows, int dim, int n_queries, int k, size_t* bytes);
 int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
                      const void* queries_bf16, const float* q_scale, int n_queries, int k,
                      int64_t id_base, float* out_scores, int64_t* out_ids,

@@ -26,6 +26,7 @@ SIGNATURES = {
     "srag_rows_ingest_f32": [_vp, _i64, _i32, _vp, _vp, _i32, _vp],
     "srag_rows_scale_bf16": [_vp, _i64, _i32, _vp, _i32, _vp],
     "srag_topk_workspace_bytes": [_i64, _i32, _i32, C.POINTER(_sz)],
+    "srag_topk_workspace_bytes_ex": [_i64, _i32, _i32, _i32, C.POINTER(_sz)],
     "srag_topk_search": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _sz, _vp],
     "srag_topk_search_filtered": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                   _sz, _vp],

@@ -811,6 +811,28 @@ extern "C" int srag_topk_workspace_bytes(int64_t n_rows, int n_queries, int k, s
     return SRAG_OK;
 }
 
+// Queries padded with zero rows to whole q-tiles: a TMA box that is mostly out of bounds (B = 1..32 of a
+// 128-row tile) loads far slower than one over real zero rows (4.8 ms vs 2.9 ms per 10 M x 1024 scan at B = 1).
+static size_t padded_query_rows(const Plan& pl, int n_queries) {
+    const size_t tile = (size_t)BLOCK_M * pl.cta_group;
+    return ((size_t)n_queries + tile - 1) / tile * tile;
+}
+
+extern "C" int srag_topk_workspace_bytes_ex(int64_t n_rows, int dim, int n_queries, int k, size_t* bytes) {
+    int rc = srag_topk_workspace_bytes(n_rows, n_queries, k, bytes);
+    if (rc) return rc;
+    SRAG_CHECK_ARG(dim >= 8 && dim % 8 == 0, "dim=%d must be a positive multiple of 8", dim);
+    int sms = 0;
+    rc = device_sm_count(&sms);
+    if (rc) return rc;
+    Plan pl;
+    rc = make_plan(sms, n_queries, k, &pl);
+    if (rc) return rc;
+    const size_t rows = padded_query_rows(pl, n_queries);
+    if (rows != (size_t)n_queries) *bytes += rows * dim * sizeof(__nv_bfloat16) + 256;
+    return SRAG_OK;
+}
+
 static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
                             const void* queries_bf16, const float* q_scale, int n_queries, int k, int64_t id_base,
                             const uint32_t* row_tags, const int32_t* row_group, const uint32_t* q_tag_mask,
@@ -871,7 +893,20 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
     if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][0], st));
     if (n_rows > 0) {
         CUtensorMap tq, tc;
-        rc = make_tmap(&tq, queries_bf16, n_queries, dim, BLOCK_M, false);
+        // zero-padded copy of the queries when the batch is not whole q-tiles and the caller sized the
+        // workspace with srag_topk_workspace_bytes_ex (otherwise the out-of-bounds box path is used)
+        const size_t q_rows = padded_query_rows(pl, n_queries);
+        const size_t q_off = (need + 255) & ~(size_t)255;
+        const size_t row_bytes = (size_t)dim * sizeof(__nv_bfloat16);
+        if (q_rows != (size_t)n_queries && workspace_bytes >= q_off + q_rows * row_bytes) {
+            uint8_t* qpad = ws + q_off;
+            SRAG_CUDA(cudaMemcpyAsync(qpad, queries_bf16, n_queries * row_bytes, cudaMemcpyDeviceToDevice, st));
+            SRAG_CUDA(cudaMemsetAsync(qpad + n_queries * row_bytes, 0, (q_rows - n_queries) * row_bytes, st));
+            prm.queries = reinterpret_cast<const __nv_bfloat16*>(qpad);
+            rc = make_tmap(&tq, qpad, (int64_t)q_rows, dim, BLOCK_M, false);
+        } else {
+            rc = make_tmap(&tq, queries_bf16, n_queries, dim, BLOCK_M, false);
+        }
         if (rc) return rc;
         const int block_n = rq ? 128 : 256;
         rc = make_tmap(&tc, corpus_bf16, n_rows, dim, block_n / pl.cta_group, true);

@@ -74,10 +74,14 @@ def ingest_rows(rows: torch.Tensor, metric=METRIC_COSINE, out_bf16: Optional[tor
 
 
 # ---- K1 ---------------------------------------------------------------------------------
-def topk_workspace_bytes(n_rows: int, n_queries: int, k: int) -> int:
+def topk_workspace_bytes(n_rows: int, n_queries: int, k: int, dim: int = 0) -> int:
+    """With `dim` the size includes room for the zero-padded query copy that small / ragged batches use."""
     lib = _lib.load()
     out = C.c_size_t()
-    _lib.check(lib.srag_topk_workspace_bytes(n_rows, n_queries, k, C.byref(out)), "srag_topk_workspace_bytes")
+    if dim:
+        _lib.check(lib.srag_topk_workspace_bytes_ex(n_rows, dim, n_queries, k, C.byref(out)), "srag_topk_workspace_bytes_ex")
+    else:
+        _lib.check(lib.srag_topk_workspace_bytes(n_rows, n_queries, k, C.byref(out)), "srag_topk_workspace_bytes")
     return out.value
 
 
@@ -113,7 +117,7 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
         ids = out_ids if out_ids is not None else torch.empty(B, k, dtype=torch.int64, device=dev)
         for b0 in range(0, B, MAX_QUERIES_PER_CALL):
             nb = min(MAX_QUERIES_PER_CALL, B - b0)
-            need = topk_workspace_bytes(N, nb, k)
+            need = topk_workspace_bytes(N, nb, k, D)
             if workspace is None or workspace.numel() < need:
                 workspace = torch.empty(need, dtype=torch.uint8, device=dev)
             q = queries[b0:b0 + nb]

@@ -64,7 +64,7 @@ class ShardedVectorIndex:
         self._ws: Optional[torch.Tensor] = None
 
     def local_topk(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
-        need = self.ops.topk_workspace_bytes(self.rows.shape[0], min(q_bf16.shape[0], self.ops.MAX_QUERIES_PER_CALL), k)
+        need = self.ops.topk_workspace_bytes(self.rows.shape[0], min(q_bf16.shape[0], self.ops.MAX_QUERIES_PER_CALL), k, self.rows.shape[1])
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.rows.device)
         return self.ops.topk_search(self.rows, self.row_scale, q_bf16, q_scale, k, id_base=self.id_base,

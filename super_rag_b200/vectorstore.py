@@ -284,7 +284,7 @@ class DeviceCollection:
         if q.dtype not in (torch.float32, torch.bfloat16):
             q = q.to(torch.float32)
         qb, qs = ops.ingest_rows(q.contiguous(), self.metric)
-        need = ops.topk_workspace_bytes(self.n, min(q.shape[0], ops.MAX_QUERIES_PER_CALL), top_k)
+        need = ops.topk_workspace_bytes(self.n, min(q.shape[0], ops.MAX_QUERIES_PER_CALL), top_k, self.dim)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
         kw = {}

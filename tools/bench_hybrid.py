@@ -175,7 +175,7 @@ def main():
     h = args.queries // 2
     src = torch.randint(0, args.docs, (h,), generator=g, device=dev)
     q32[:h] = corpus[src].float() + 0.1 * q32[:h]
-    ws = torch.empty(ops.topk_workspace_bytes(args.docs, args.queries, 100), dtype=torch.uint8, device=dev)
+    ws = torch.empty(ops.topk_workspace_bytes(args.docs, args.queries, 100, args.dim), dtype=torch.uint8, device=dev)
 
     def hybrid():
         qb, qs = ops.ingest_rows(q32, "cosine")

@@ -46,7 +46,7 @@ def main():
     for B in [int(x) for x in args.batches.split(",")]:
         q = make_corpus(B, args.dim, 2, dev)
         _, qs = ops.ingest_rows(q, "cosine")
-        ws = torch.empty(ops.topk_workspace_bytes(args.rows, min(B, ops.MAX_QUERIES_PER_CALL), args.k),
+        ws = torch.empty(ops.topk_workspace_bytes(args.rows, min(B, ops.MAX_QUERIES_PER_CALL), args.k, args.dim),
                          dtype=torch.uint8, device=dev)
         for _ in range(2):
             s, i = ops.topk_search(corpus, cs, q, qs, args.k, workspace=ws)
