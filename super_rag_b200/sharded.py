@@ -85,3 +85,44 @@ class ShardedVectorIndex:
             q = q.to(torch.float32)
         qb, qs = self.ops.ingest_rows(q.contiguous(), self.metric)
         return self.search_device(qb, qs, k)
+
+
+class ShardedBm25Index:
+    """This rank's document range of a BM25 index built with GLOBAL statistics (df, N, avgdl -> idf), so a
+    shard's scores equal the single-index scores bit for bit; search = per-shard K2, one
+    all-gather of the (score, id) candidates, K4 merge."""
+
+    def __init__(self, shard_index, group=None):
+        from . import ops
+        self.ops = ops
+        self.index = shard_index                      # bm25.Bm25Index with id_base = first document of the range
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+    @classmethod
+    def from_tokens(cls, tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int, n_docs_total: int, stats, rank: int,
+                    world: int, group=None) -> "ShardedBm25Index":
+        """`tokens` / `doc_ptr` describe the WHOLE collection on every rank (host or device); this rank keeps
+        documents shard_range(n_docs_total, world, rank). `stats` = bm25.Bm25Stats of the whole collection."""
+        from .bm25 import Bm25Index
+        lo, hi = shard_range(n_docs_total, world, rank)
+        t_lo, t_hi = int(doc_ptr[lo].item()), int(doc_ptr[hi].item())
+        return cls(Bm25Index.from_tokens(tokens[t_lo:t_hi], doc_ptr[lo:hi + 1] - t_lo, vocab, stats=stats, id_base=lo),
+                   group)
+
+    def search_terms(self, q_terms: torch.Tensor, k: int):
+        s, i = self.index.search_terms(q_terms, k)
+        if self.world == 1:
+            return s, i
+        gs, gi = exchange_candidates(s, i, self.group)
+        return self.ops.merge_candidates(gs, gi, k)
+
+
+def hybrid_search(vec: ShardedVectorIndex, bm25: ShardedBm25Index, queries: torch.Tensor, q_terms: torch.Tensor,
+                  k_recall: int, k_out: int, rank_const: int = 60):
+    """C4 on shards: GLOBAL vector top-k_recall and GLOBAL BM25 top-k_recall (each: local scan, all-gather,
+    merge), then RRF on every rank — the ranks RRF sums are positions in the global lists, so the fusion must
+    come after both merges. Returns (ids int64 [B, k_out], scores float64 [B, k_out])."""
+    vs, vi = vec.search_batch(queries, k_recall)
+    bs, bi = bm25.search_terms(q_terms, k_recall)
+    return vec.ops.fuse(torch.stack([vi, bi]), None, vec.ops.FUSE_RRF, k_out, rank_const=rank_const)

@@ -19,7 +19,8 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from super_rag_b200 import ops  # noqa: E402
 from super_rag_b200.bm25 import Bm25Index, Bm25Stats  # noqa: E402
-from super_rag_b200.sharded import ShardedVectorIndex, exchange_candidates, shard_range  # noqa: E402
+from super_rag_b200.sharded import (ShardedBm25Index, ShardedVectorIndex, exchange_candidates, hybrid_search,  # noqa: E402
+                                    shard_range)
 
 
 def main():
@@ -66,11 +67,26 @@ def main():
     torch.cuda.synchronize()
     ok_b = bool(torch.equal(mi, wi)) and bool(torch.equal(ms.view(torch.int32), ws.view(torch.int32)))
 
+    # the ShardedBm25Index wrapper and the hybrid (vector + BM25 -> RRF) path == the single-GPU pipeline
+    sb = ShardedBm25Index.from_tokens(torch.from_numpy(tokens).to(dev), torch.from_numpy(doc_ptr).to(dev), vocab, n_docs,
+                                      stats, rank, world)
+    from super_rag_b200.bm25 import prepare_query_terms
+    qt = torch.from_numpy(prepare_query_terms(queries, vocab)).to(dev)
+    nvec = min(n, n_docs)
+    vidx = ShardedVectorIndex(*[t[slice(*shard_range(nvec, world, rank))].contiguous() for t in (cb[:nvec], cs[:nvec])],
+                              id_base=shard_range(nvec, world, rank)[0])
+    hi_ids, hi_sc = hybrid_search(vidx, sb, Q[:64], qt, 20, 10)
+    fvs, fvi = ops.topk_search(cb[:nvec], cs[:nvec], *ops.ingest_rows(Q[:64], "cosine"), 20)
+    fbs, fbi = full.search_terms(qt, 20)
+    w_ids, w_sc = ops.fuse(torch.stack([fvi, fbi]), None, ops.FUSE_RRF, 10, rank_const=60)
+    torch.cuda.synchronize()
+    ok_b = ok_b and bool(torch.equal(hi_ids, w_ids)) and bool(torch.equal(hi_sc, w_sc))
+
     flags = torch.tensor([int(ok_v), int(ok_b)], device=dev)
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(f"world={world} vector_sharded_equals_single={bool(flags[0].item())} "
-              f"bm25_sharded_equals_single={bool(flags[1].item())}", flush=True)
+              f"bm25_and_hybrid_sharded_equals_single={bool(flags[1].item())}", flush=True)
     dist.destroy_process_group()
     if not (flags[0].item() and flags[1].item()):
         sys.exit(1)
