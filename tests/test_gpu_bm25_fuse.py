@@ -157,3 +157,36 @@ def test_merge_candidates_matches_oracle():
     ms, mi = ops.merge_candidates(torch.from_numpy(s).cuda(), torch.from_numpy(i).cuda(), 100)
     ws, wi = oracle.merge_shard_candidates(s, i, 100)
     assert (mi.cpu().numpy() == wi).all() and (ms.cpu().numpy() == ws).all()
+
+
+def test_bm25_many_terms_per_query():
+    """Queries longer than one producer batch (32 term slots) and longer than 64: summation order stays
+    ascending term id across the batches."""
+    n_docs, vocab = 60_000, 400
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, 60, seed=77)
+    idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    rng = np.random.default_rng(5)
+    queries = [rng.choice(vocab, size=n, replace=False).tolist() for n in (9, 31, 32, 33, 40, 64, 65, 70, 100)]
+    s, i = idx.search(queries, 50)
+    os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, 50)
+    assert (i.cpu().numpy() == oi).all()
+    assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all()
+
+
+def test_bm25_two_phase_with_ties_at_the_threshold():
+    """43 blocks -> sampled first phase + thresholded second phase. Documents are drawn from a handful of
+    shapes, so thousands of documents tie exactly at the sample's k-th best score: ties at tau are kept and
+    the globally lowest doc ids win, whichever phase their block belongs to."""
+    n_docs, vocab = 700_000, 6
+    rng = np.random.default_rng(9)
+    shapes = np.array([[0, 1, 2], [0, 0, 1], [3, 4, 5], [0, 3, 3], [1, 1, 1], [2, 4, 4]], dtype=np.int64)
+    pick = rng.integers(0, len(shapes), n_docs)
+    tokens = shapes[pick].reshape(-1)
+    doc_ptr = np.arange(0, 3 * n_docs + 1, 3, dtype=np.int64)
+    idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    queries = [[0], [0, 1], [3, 4, 5], [1, 2, 4], [0, 1, 2, 3, 4, 5], [5]]
+    for k in (10, 100, 256):
+        s, i = idx.search(queries, k)
+        os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, k)
+        assert (i.cpu().numpy() == oi).all(), k
+        assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all(), k
