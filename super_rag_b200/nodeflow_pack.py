@@ -280,7 +280,34 @@ def install_connector() -> bool:
     ctx_mod = sys.modules.get("super_rag.context.context")
     if ctx_mod is not None:  # `from ... import VectorStoreConnectorAdaptor` bound the old class (context.py:4)
         ctx_mod.VectorStoreConnectorAdaptor = vectorstore.VectorStoreConnectorAdaptor
+    _enable_filter_builder()
     return True
+
+
+def _enable_filter_builder() -> None:
+    """ContextManager builds its metadata filter only ``if self.vectordb_type == "seekdb"`` (context/context.py:60,
+    92) and hands ``None`` to every other store. For type ``b200`` run the reference's OWN builder (unchanged) as if
+    the store were seekdb, so the connector receives the filter document it can honour (ctx["apply_filter"])."""
+    try:
+        from super_rag.context.context import ContextManager  # type: ignore
+    except Exception:
+        return
+    if getattr(ContextManager._create_combined_filter, "_srag_b200", False):
+        return
+    original = ContextManager._create_combined_filter
+
+    def _create_combined_filter(self, index_types=None, chat_id=None):
+        if getattr(self, "vectordb_type", None) != "b200":
+            return original(self, index_types, chat_id)
+        self.vectordb_type = "seekdb"
+        try:
+            return original(self, index_types, chat_id)
+        finally:
+            self.vectordb_type = "b200"
+
+    _create_combined_filter._srag_b200 = True
+    _create_combined_filter._original = original
+    ContextManager._create_combined_filter = _create_combined_filter
 
 
 def register() -> None:

@@ -149,7 +149,16 @@ def test_install_connector_into_unmodified_reference():
             assert isinstance(cm.adaptor.connector, vectorstore.B200VectorStoreConnector)
             with pytest.raises(ValueError):                                   # other types reach the reference adaptor
                 ContextManager("t_ctx", None, "no-such-store", {"collection": "t_ctx"})
+            # the reference's own filter builder now also runs for type b200 (it returns None for non-seekdb stores)
+            flt = cm._create_combined_filter(["vector"], "chat-9")
+            assert flt == {"and": [{"or": [{"indexer": {"$in": ["vector"]}}, {"indexer": {"$exists": False}}]},
+                                   {"chat_id": "chat-9"}]}
+            assert cm.vectordb_type == "b200" and cm._create_combined_filter(None, None) is None
+            tagger = vectorstore.RowTagger()
+            tagger.encode({"indexer": "vector", "chat_id": "chat-9"})
+            assert tagger.compile(flt) == (vectorstore.MISSING_BIT | 1, 1)
         finally:
+            ContextManager._create_combined_filter = ContextManager._create_combined_filter._original
             ref_conn.VectorStoreConnectorAdaptor = original
             sys.modules["super_rag.context.context"].VectorStoreConnectorAdaptor = original
             vectorstore._REFERENCE_ADAPTOR = None
