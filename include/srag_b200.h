@@ -126,6 +126,15 @@ int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const fl
                      int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries,
                      int max_terms, int k, int64_t id_base, float* out_scores, int64_t* out_ids,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* Same with the metadata pre-filter of srag_topk_search_filtered applied to documents: only admitted
+ * documents are scored into the result (doc_tags / doc_group are indexed by the document's position in
+ * THIS index, 0 .. n_docs-1; q_tag_mask / q_group per query).                                    */
+int srag_bm25_search_filtered(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,
+                              int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries,
+                              int max_terms, int k, int64_t id_base, const uint32_t* doc_tags,
+                              const int32_t* doc_group, const uint32_t* q_tag_mask, const int32_t* q_group,
+                              float* out_scores, int64_t* out_ids, void* workspace,
+                              size_t workspace_bytes, void* stream);
 
 /* ---- K3: fusion ---------------------------------------------------------------------
  * RRF exactly as graphiti_core/search/search_utils.py:1763-1778 (float64,

@@ -141,17 +141,18 @@ class Bm25Index:
                    int(meta["id_base"]))
 
     # ---- search ----------------------------------------------------------------------------
-    def search_terms(self, q_terms: torch.Tensor, k: int):
-        """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids)."""
+    def search_terms(self, q_terms: torch.Tensor, k: int, **filter_kw):
+        """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids).
+        filter_kw: doc_tags / q_tag_mask / doc_group / q_group (ops.bm25_search)."""
         need = ops.bm25_workspace_bytes(self.n_docs, q_terms.shape[0], k)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         return ops.bm25_search(self.block_ptr, self.post_doc, self.post_imp, self.n_docs, q_terms, k,
-                               id_base=self.id_base, workspace=self._ws)
+                               id_base=self.id_base, workspace=self._ws, **filter_kw)
 
-    def search(self, queries: Sequence[Iterable[int]], k: int):
+    def search(self, queries: Sequence[Iterable[int]], k: int, **filter_kw):
         qt = torch.from_numpy(prepare_query_terms(queries, self.vocab)).to(self.device)
-        return self.search_terms(qt, k)
+        return self.search_terms(qt, k, **filter_kw)
 
     def query_posting_bytes(self, q_terms: torch.Tensor) -> int:
         """Algorithmic bytes of a batch: 8 B per posting of every query term."""

@@ -290,13 +290,21 @@ __device__ bool select_near_max(Bm25Smem* sm, int k, int32_t doc_base, uint64_t*
 // Warps 0..7 are the CONSUMERS: they follow the slot stream; the slot's metadata says where an item or a
 // term starts. A barrier separates terms (two terms may hit the same document; inside a term every
 // posting is a distinct document), which keeps the per-document summation order = ascending term id.
+struct Bm25Filter {  // metadata pre-filter, same rule as K1 (srag_topk_search_filtered); null pointers = no constraint
+    const uint32_t* doc_tags;    // [n_docs]
+    const int32_t* doc_group;    // [n_docs]
+    const uint32_t* q_tag_mask;  // [n_queries]
+    const int32_t* q_group;      // [n_queries]
+};
+
+template <bool FILT>  // FILT: the unfiltered instantiation carries none of the filter code
 __global__ void __launch_bounds__(BM25_CTA_THREADS, BM25_CTAS_PER_SM)
 bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
                   const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
                   const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
                   uint64_t* __restrict__ partial /* phase 1: [nq][n_blocks][k]; phase 0: [nq][ceil(n_blocks/stride)][k] */,
-                  int debug /* SRAG_BM25_DEBUG */) {
+                  int debug /* SRAG_BM25_DEBUG */, Bm25Filter flt, int64_t n_docs) {
     extern __shared__ uint8_t bm25_smem_raw[];
     Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
     const int nb0 = (n_blocks + stride - 1) / stride;
@@ -486,6 +494,13 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
     int cur_ql = 0, cur_blk = 0;
     float cur_tau = 0.f;
     uint32_t cross_bits = 0xFFFFFFFFu;  // tau as orderable bits when candidates are tracked, else never crossed
+    uint32_t f_mask = 0xFFFFFFFFu;      // this item's query filter (FILT only)
+    int32_t f_group = -1;
+    auto eligible = [&](int32_t doc) -> bool {  // doc = document index inside this shard
+        if (flt.doc_tags && (__ldg(flt.doc_tags + doc) & f_mask) == 0) return false;
+        if (f_group >= 0 && __ldg(flt.doc_group + doc) != f_group) return false;
+        return true;
+    };
 
     // top-k of the finished tile -> partial[cur_ql][cur_blk][*] (all consumers; adds are complete)
     auto select_item = [&]() {
@@ -501,6 +516,20 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                 }
                 return;
             }
+        }
+        if constexpr (FILT) {
+            // scan paths select over the whole tile: drop the matches the query's filter does not admit first
+            for (int i = threadIdx.x; i < BM25_BLOCK_DOCS / 4; i += BM25_THREADS) {
+                float4 v = a4[i];
+                if (v.x == 0.f && v.y == 0.f && v.z == 0.f && v.w == 0.f) continue;
+                const int32_t d0 = doc_base + 4 * i;
+                if (v.x != 0.f && !(d0 < n_docs && eligible(d0))) v.x = 0.f;
+                if (v.y != 0.f && !(d0 + 1 < n_docs && eligible(d0 + 1))) v.y = 0.f;
+                if (v.z != 0.f && !(d0 + 2 < n_docs && eligible(d0 + 2))) v.z = 0.f;
+                if (v.w != 0.f && !(d0 + 3 < n_docs && eligible(d0 + 3))) v.w = 0.f;
+                a4[i] = v;
+            }
+            consumer_sync();
         }
         // impacts are > 0, so "matched" <=> accumulator bits != 0, and positive floats order as uints
         uint32_t lo_bits = 1u;
@@ -557,6 +586,10 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             cur_blk = m.blk;
             cur_tau = m.tau;
             cross_bits = (cur_tau > 0.f && !(debug & 16)) ? __float_as_uint(cur_tau) : 0xFFFFFFFFu;
+            if constexpr (FILT) {
+                f_mask = flt.doc_tags ? __ldg(flt.q_tag_mask + q_offset + cur_ql) : 0xFFFFFFFFu;
+                f_group = flt.doc_group ? __ldg(flt.q_group + q_offset + cur_ql) : -1;
+            }
             consumer_sync();
         } else if ((m.flags & SLOT_NEW_TERM) && !(debug & 8)) {
             consumer_sync();
@@ -597,7 +630,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                 const bool cc[4] = {c0, c1, c2, c3};
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
-                    if (cc[e]) {
+                    if (cc[e] && (!FILT || eligible(doc_base + rr[e]))) {
                         const uint32_t s_ = atomicAdd(&sm->cand_count, 1u);
                         if (s_ < (uint32_t)BM25_CAND_MAX) sm->cand[s_] = (uint16_t)rr[e];
                     }
@@ -712,10 +745,14 @@ extern "C" int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, s
     return SRAG_OK;
 }
 
-extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp, int vocab,
-                                int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms, int k,
-                                int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
-                                size_t workspace_bytes, void* stream) {
+static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp, int vocab,
+                            int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms, int k, int64_t id_base,
+                            Bm25Filter flt, float* out_scores, int64_t* out_ids, void* workspace, size_t workspace_bytes,
+                            void* stream) {
+    SRAG_CHECK_ARG((flt.doc_tags == nullptr) == (flt.q_tag_mask == nullptr) &&
+                       (flt.doc_group == nullptr) == (flt.q_group == nullptr),
+                   "doc_tags / q_tag_mask and doc_group / q_group come in pairs");
+    const bool filtered = flt.doc_tags != nullptr || flt.doc_group != nullptr;
     SRAG_CHECK_ARG(n_queries >= 1 && max_terms >= 1 && k >= 1 && k <= SRAG_MAX_BM25_K, "bad sizes n_queries=%d k=%d",
                    n_queries, k);
     SRAG_CHECK_ARG(n_docs >= 0 && n_docs < 0x7FFFFFFF && vocab >= 1, "bad index sizes");
@@ -734,7 +771,9 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
     static bool attr_done = false;
     static int sm_count = 0;
     if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(Bm25Smem)));
+        SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)sizeof(Bm25Smem)));
         int dev = 0;
         SRAG_CUDA(cudaGetDevice(&dev));
@@ -758,9 +797,10 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
         if (n_docs > 0) {
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
-            bm25_items_kernel<<<grid0, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(
-                block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 0, stride, nullptr,
-                stride > 1 ? sample : partial, dbg);
+            auto kern = filtered ? bm25_items_kernel<true> : bm25_items_kernel<false>;
+            kern<<<grid0, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k,
+                                                                    q0, nq, 0, stride, nullptr,
+                                                                    stride > 1 ? sample : partial, dbg, flt, n_docs);
             SRAG_CUDA(cudaGetLastError());
             if (stride > 1) {
                 // top-k of the sample: scores give tau; the keys seed the final merge in block 0's slot of
@@ -770,8 +810,9 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
                 if (rc) return rc;
                 const long long items1 = (long long)nq * (nb - nb0);
                 const int grid1 = (int)(items1 < resident ? items1 : resident);
-                bm25_items_kernel<<<grid1, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(
-                    block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k, q0, nq, 1, stride, tau_scores, partial, dbg);
+                kern<<<grid1, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, q_terms, max_terms,
+                                                                        k, q0, nq, 1, stride, tau_scores, partial, dbg, flt,
+                                                                        n_docs);
                 SRAG_CUDA(cudaGetLastError());
             }
         }
@@ -780,4 +821,23 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
         if (rc) return rc;
     }
     return SRAG_OK;
+}
+
+extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp, int vocab,
+                                int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms, int k,
+                                int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+    return bm25_search_impl(block_ptr, post_doc, post_imp, vocab, n_docs, q_terms, n_queries, max_terms, k, id_base,
+                            Bm25Filter{nullptr, nullptr, nullptr, nullptr}, out_scores, out_ids, workspace,
+                            workspace_bytes, stream);
+}
+
+extern "C" int srag_bm25_search_filtered(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,
+                                         int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms,
+                                         int k, int64_t id_base, const uint32_t* doc_tags, const int32_t* doc_group,
+                                         const uint32_t* q_tag_mask, const int32_t* q_group, float* out_scores,
+                                         int64_t* out_ids, void* workspace, size_t workspace_bytes, void* stream) {
+    return bm25_search_impl(block_ptr, post_doc, post_imp, vocab, n_docs, q_terms, n_queries, max_terms, k, id_base,
+                            Bm25Filter{doc_tags, doc_group, q_tag_mask, q_group}, out_scores, out_ids, workspace,
+                            workspace_bytes, stream);
 }

@@ -52,7 +52,7 @@ class FulltextCollection:
     """Chunk texts of one collection with a BM25 index in HBM. Rebuilt lazily after appends."""
 
     def __init__(self, name: str, tokenizer: Optional[Callable[[str], List[int]]] = None, vocab: Optional[int] = None,
-                 device: Optional[str] = None):
+                 device: Optional[str] = None, apply_filter: bool = False):
         if tokenizer is None:
             tokenizer, vocab = default_tokenizer()
         if vocab is None:
@@ -63,6 +63,15 @@ class FulltextCollection:
         self.metas: List[Optional[dict]] = []
         self._tokens: List[np.ndarray] = []
         self._index: Optional[Bm25Index] = None
+        # metadata pre-filter (same tag word / group encoding as the vector store); off unless asked for, like
+        # the vector connector's ctx["apply_filter"]
+        from .vectorstore import RowTagger
+        self.apply_filter = bool(apply_filter)
+        self.tagger = RowTagger()
+        self._tags: List[int] = []
+        self._groups: List[int] = []
+        self._tags_dev: Optional[torch.Tensor] = None
+        self._groups_dev: Optional[torch.Tensor] = None
         self.lock = threading.Lock()
 
     def __len__(self):
@@ -84,6 +93,9 @@ class FulltextCollection:
                 self.texts.append(t)
                 self.metas.append(m)
                 self._tokens.append(ids)
+                tag, group = self.tagger.encode(m)
+                self._tags.append(tag - (1 << 32) if tag & 0x80000000 else tag)
+                self._groups.append(group)
             self._index = None
             return range(start, len(self.texts))
 
@@ -97,6 +109,8 @@ class FulltextCollection:
                 flat = np.concatenate(self._tokens) if len(self._tokens) else np.zeros(0, dtype=np.int64)
                 self._index = Bm25Index.from_tokens(torch.from_numpy(flat).to(dev), torch.from_numpy(doc_ptr).to(dev),
                                                     self.vocab)
+                self._tags_dev = torch.tensor(self._tags, dtype=torch.int32).to(dev)
+                self._groups_dev = torch.tensor(self._groups, dtype=torch.int32).to(dev)
             return self._index
 
     # -- persistence: token ids, texts and metadata (the tokenizer itself is code, passed again on load) --
@@ -126,6 +140,10 @@ class FulltextCollection:
         if len(doc_ptr) != len(col.texts) + 1 or (len(doc_ptr) and int(doc_ptr[-1]) != len(tokens)):
             raise shardio.ShardError(f"{path}: token table does not match the doc table")
         col._tokens = [tokens[doc_ptr[i]:doc_ptr[i + 1]].copy() for i in range(len(col.texts))]
+        for m in col.metas:
+            tag, group = col.tagger.encode(m)
+            col._tags.append(tag - (1 << 32) if tag & 0x80000000 else tag)
+            col._groups.append(group)
         return col
 
     def query_terms(self, query: Optional[str], keywords: Optional[Iterable[str]]) -> List[int]:
@@ -133,11 +151,25 @@ class FulltextCollection:
         text = " ".join(keywords) if keywords else (query or "")
         return list(self.tokenizer(text))
 
-    def search(self, query: Optional[str], top_k: int, keywords: Optional[Iterable[str]] = None) -> List[DocumentWithScore]:
+    def search(self, query: Optional[str], top_k: int, keywords: Optional[Iterable[str]] = None,
+               filter: Optional[dict] = None) -> List[DocumentWithScore]:
+        """`filter`: a document in the grammar of ContextManager._create_combined_filter (context/context.py:74-111);
+        honoured when the collection was created with apply_filter=True, ignored otherwise."""
         if top_k <= 0 or not self.texts:
             return []
         terms = self.query_terms(query, keywords)
-        scores, ids = self.index().search([terms], min(int(top_k), 256))
+        index = self.index()
+        kw = {}
+        if filter and self.apply_filter:
+            mask, group = self.tagger.compile(filter)
+            dev = index.device
+            if mask != 0xFFFFFFFF:
+                kw["doc_tags"] = self._tags_dev
+                kw["q_tag_mask"] = torch.tensor([mask - (1 << 32) if mask & 0x80000000 else mask], dtype=torch.int32).to(dev)
+            if group >= 0:
+                kw["doc_group"] = self._groups_dev
+                kw["q_group"] = torch.tensor([group], dtype=torch.int32).to(dev)
+        scores, ids = index.search([terms], min(int(top_k), 256), **kw)
         out: List[DocumentWithScore] = []
         for s, r in zip(scores[0].tolist(), ids[0].tolist()):
             if r < 0:

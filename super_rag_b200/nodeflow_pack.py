@@ -86,7 +86,11 @@ class FulltextSearchNodeRunner(BaseNodeRunner):
             col = fulltext.get_collection(str(collection_ids[0]))  # generate_fulltext_index_name: str(id)
             if col is not None:
                 try:
-                    docs = col.search(getattr(si, "query", None), ui.top_k, ui.keywords)
+                    # chat documents stay inside their chat, as the vector node asks of its store
+                    # (runners/vector_search.py:79-86 -> context.py:74-111); honoured by collections created with
+                    # apply_filter=True
+                    flt = {"chat_id": ui.chat_id} if getattr(ui, "chat_id", None) else None
+                    docs = col.search(getattr(si, "query", None), ui.top_k, ui.keywords, filter=flt)
                     for item in docs:
                         if item.metadata is None:
                             item.metadata = {}

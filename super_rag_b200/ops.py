@@ -184,9 +184,20 @@ def bm25_block_index(term_ptr, post_doc, n_docs: int) -> torch.Tensor:
 
 
 def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tensor, k: int, id_base: int = 0,
-                workspace: Optional[torch.Tensor] = None):
-    """q_terms int32 [B, T]: unique ascending term ids, -1 padded."""
+                workspace: Optional[torch.Tensor] = None, doc_tags: Optional[torch.Tensor] = None,
+                q_tag_mask: Optional[torch.Tensor] = None, doc_group: Optional[torch.Tensor] = None,
+                q_group: Optional[torch.Tensor] = None):
+    """q_terms int32 [B, T]: unique ascending term ids, -1 padded. Optional metadata pre-filter as in
+    topk_search (int32 tensors: doc_tags / doc_group [n_docs], q_tag_mask / q_group [B])."""
     _need_cuda(block_ptr, post_doc, post_imp, q_terms)
+    if (doc_tags is None) != (q_tag_mask is None) or (doc_group is None) != (q_group is None):
+        raise SragError("doc_tags / q_tag_mask and doc_group / q_group come in pairs")
+    for t, n_expect, what in ((doc_tags, n_docs, "doc_tags"), (doc_group, n_docs, "doc_group"),
+                              (q_tag_mask, q_terms.shape[0], "q_tag_mask"), (q_group, q_terms.shape[0], "q_group")):
+        if t is not None:
+            _need_cuda(t)
+            if t.dtype != torch.int32 or t.numel() != n_expect or not t.is_contiguous():
+                raise SragError(f"{what} must be a contiguous int32 tensor of {n_expect} elements")
     lib = _lib.load()
     B, T = q_terms.shape
     dev = q_terms.device
@@ -198,9 +209,15 @@ def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tenso
             workspace = torch.empty(out.value, dtype=torch.uint8, device=dev)
         scores = torch.empty(B, k, dtype=torch.float32, device=dev)
         ids = torch.empty(B, k, dtype=torch.int64, device=dev)
-        _lib.check(lib.srag_bm25_search(_ptr(block_ptr), _ptr(post_doc), _ptr(post_imp), vocab, n_docs,
-                                        _ptr(q_terms.contiguous()), B, T, k, id_base, _ptr(scores), _ptr(ids),
-                                        _ptr(workspace), workspace.numel(), _stream(dev)), "srag_bm25_search")
+        if doc_tags is not None or doc_group is not None:
+            _lib.check(lib.srag_bm25_search_filtered(
+                _ptr(block_ptr), _ptr(post_doc), _ptr(post_imp), vocab, n_docs, _ptr(q_terms.contiguous()), B, T, k,
+                id_base, _ptr(doc_tags), _ptr(doc_group), _ptr(q_tag_mask), _ptr(q_group), _ptr(scores), _ptr(ids),
+                _ptr(workspace), workspace.numel(), _stream(dev)), "srag_bm25_search_filtered")
+        else:
+            _lib.check(lib.srag_bm25_search(_ptr(block_ptr), _ptr(post_doc), _ptr(post_imp), vocab, n_docs,
+                                            _ptr(q_terms.contiguous()), B, T, k, id_base, _ptr(scores), _ptr(ids),
+                                            _ptr(workspace), workspace.numel(), _stream(dev)), "srag_bm25_search")
     return scores, ids
 
 

@@ -117,3 +117,59 @@ def test_filtered_c_abi_small_k_and_groups_only():
         _check(s[q], i[q], C_r, Q_r[q:q + 1], admit, k)
     with pytest.raises(Exception):
         ops.topk_search(cb, cs, qb, qs, k, row_group=torch.from_numpy(group).to(dev))
+
+
+def test_bm25_filtered_matches_oracle_small_and_two_phase():
+    """K2 with the metadata pre-filter: exact BM25 top-k among the admitted documents only (scores bit-exact:
+    the filter removes candidates, it never changes a sum). Covers the single-phase path (few blocks) and the
+    sampled two-phase path (>= 32 blocks) with a selective and a permissive filter."""
+    import torch
+    from super_rag_b200.bm25 import Bm25Index
+    dev = torch.device("cuda:0")
+    for n_docs, vocab, k in [(40_000, 500, 20), (600_000, 300, 50)]:
+        rng = np.random.default_rng(n_docs)
+        dl = rng.integers(5, 30, n_docs)
+        p = 1.0 / np.arange(1, vocab + 1)
+        tokens = rng.choice(vocab, size=int(dl.sum()), p=p / p.sum()).astype(np.int64)
+        doc_ptr = np.concatenate([[0], np.cumsum(dl)]).astype(np.int64)
+        idx = Bm25Index.from_tokens(torch.from_numpy(tokens).to(dev), torch.from_numpy(doc_ptr).to(dev), vocab)
+        tp, pd, ptf, dl32 = oracle.build_postings(tokens, doc_ptr, vocab)
+        imp = oracle.bm25_impacts(tp, pd, ptf, dl32)
+        tags = (1 << rng.integers(0, 4, n_docs)).astype(np.int32)          # one of 4 categories per document
+        group = rng.integers(0, 200, n_docs).astype(np.int32)             # 200 groups: a selective constraint
+        queries = [rng.integers(0, vocab, 6).tolist() for _ in range(12)]
+        q_mask = np.array([0b0011, 0b1000, 0b1111, 0b0100] * 3, dtype=np.int32)
+        q_group = np.array([-1, -1, 7, 7, 150, -1] * 2, dtype=np.int32)
+        s, i = idx.search(queries, k, doc_tags=torch.from_numpy(tags).to(dev), q_tag_mask=torch.from_numpy(q_mask).to(dev),
+                          doc_group=torch.from_numpy(group).to(dev), q_group=torch.from_numpy(q_group).to(dev))
+        s, i = s.cpu().numpy(), i.cpu().numpy()
+        # oracle: every match of the query, restricted to the admitted documents, (score desc, id asc)
+        from oracle.bm25 import bm25_scores_one
+        for q in range(len(queries)):
+            acc, hit = bm25_scores_one(tp, pd, imp, n_docs, queries[q])
+            admit = hit & ((tags & q_mask[q]) != 0) & ((q_group[q] < 0) | (group == q_group[q]))
+            ids_q = np.nonzero(admit)[0]
+            order = np.lexsort((ids_q, -acc[ids_q].astype(np.float64)))[:k]
+            want_i, want_s = ids_q[order], acc[ids_q][order].astype(np.float32)
+            n = len(want_i)
+            assert i[q, :n].tolist() == want_i.tolist(), (n_docs, q)
+            assert (s[q, :n].view(np.uint32) == want_s.view(np.uint32)).all()
+            assert (i[q, n:] == -1).all()
+
+
+def test_fulltext_collection_chat_filter():
+    from super_rag_b200 import fulltext
+    enc = fulltext.hash_tokenizer(4096)
+    col = fulltext.FulltextCollection("t_ft_filter", tokenizer=enc, vocab=4096, apply_filter=True)
+    texts = [f"alpha common w{r % 30}" for r in range(2000)]
+    metas = [{"row": r, **({"chat_id": f"c{r % 4}"} if r % 2 else {})} for r in range(2000)]
+    col.add(texts, metas)
+    plain = col.search("alpha w3", 10)
+    only = col.search("alpha w3", 10, filter={"chat_id": "c1"})
+    assert len(plain) == 10 and len(only) == 10
+    assert all(d.metadata.get("chat_id") == "c1" for d in only)
+    assert any(d.metadata.get("chat_id") != "c1" for d in plain)
+    assert col.search("alpha w3", 10, filter={"chat_id": "nobody"}) == []
+    ignoring = fulltext.FulltextCollection("t_ft_nofilter", tokenizer=enc, vocab=4096)       # default: filter ignored
+    ignoring.add(texts, metas)
+    assert [d.text for d in ignoring.search("alpha w3", 10, filter={"chat_id": "c1"})] == [d.text for d in plain]
