@@ -18,18 +18,21 @@
 
 namespace {
 
-constexpr int BM25_BLOCK_DOCS = 16384;  // 64 KB of fp32 accumulators per CTA
+// Geometry (compile time): consumer warps per CTA decide the rest.
+//   8 warps: 16384-document tile (64 KB), 36 KB posting ring, 2 CTAs per SM   <- default (13.1 ms at C3)
+//   4 warps:  8192-document tile (32 KB), 24 KB posting ring, 3 CTAs per SM   (18.2 ms: per-item costs dominate)
 #ifndef SRAG_BM25_WARPS
 #define SRAG_BM25_WARPS 8
 #endif
+constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 accumulators per CTA
 constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
 constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
 constexpr int BM25_CTA_THREADS = BM25_THREADS + 64;  // consumer warps + 2 producer warps (doc ids / impacts)
 constexpr int BM25_CHUNK = 4 * BM25_THREADS;         // postings per chunk: one aligned group of 4 per consumer thread
-constexpr int BM25_CTAS_PER_SM = SRAG_BM25_WARPS == 8 ? 2 : 1;
-// posting ring capacity (x 8 bytes: doc ids + impacts): 36 KB with two CTAs per SM, 144 KB with one
-constexpr int BM25_RING = SRAG_BM25_WARPS == 8 ? 4608 : 18 * 1024;
+constexpr int BM25_CTAS_PER_SM = SRAG_BM25_WARPS == 4 ? 3 : 2;
+// posting ring capacity (x 8 bytes: doc ids + impacts)
+constexpr int BM25_RING = SRAG_BM25_WARPS == 4 ? 3072 : 4608;
 constexpr int BM25_SLOTS = 32;                       // chunk descriptors in flight
 constexpr int BM25_CAND_MAX = 1024;
 
