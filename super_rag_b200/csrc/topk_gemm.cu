@@ -82,7 +82,7 @@ struct TopkParams {
     int k;
     int num_q_tiles;  // T_q
     int num_slabs;    // S
-    uint64_t* partial;  // [n_queries][S * EW/4][k] per-thread min-heaps of sortable keys, pre-zeroed (= empty)
+    uint64_t* partial;  // [n_queries][S * EW/4][heap_stride(k)] per-thread 4-ary min-heaps of sortable keys, pre-zeroed (= empty)
     uint32_t* gthr;   // [S * EW/4][n_queries] j-th best score of every list (orderable bits), pre-zeroed
     int share_j;      // j = ceil(k / lists), 1..8; 0 = threshold sharing off
     int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
@@ -98,31 +98,39 @@ struct TopkParams {
 };
 
 // ---------------------------------------------------------------------------------------
-// Per-thread running top-k: a binary MIN-heap of k sortable keys that lives directly in this
-// thread's slice of `partial` (pre-zeroed = k EMPTY keys, which is a valid heap). A candidate
-// that beats the threshold replaces the root (the current k-th best) and sifts down: O(log k)
-// thread-private, L1-resident loads/stores, no warp cooperation, and the threshold is always
-// the exact k-th best seen so far. Precondition: key > heap[0]. Returns the new threshold.
+// Per-thread running top-k: a 4-ary MIN-heap of k sortable keys that lives directly in this
+// thread's slice of `partial` (pre-zeroed = EMPTY keys, which is a valid heap). A candidate that
+// beats the threshold replaces the root (the current k-th best) and sifts down: thread-private
+// loads/stores, no warp cooperation, and the threshold is always the exact k-th best seen so far.
+// The lists are larger than L1 at k = 100 (100 KB per CTA), so every level of the sift is an L2
+// round trip: four children per node halve the depth of a binary heap, and the list is laid out
+// so that a node's four children are ONE aligned 32-byte sector: logical node j sits in slot
+// j + 3 (slots 0..2 stay EMPTY), children 4j+1..4j+4 -> slots 4j+4..4j+7. A list is
+// heap_stride(k) slots so the last (partial) child group stays inside it.
+// Precondition: key > root. Returns the new threshold.
 // ---------------------------------------------------------------------------------------
+__host__ __device__ constexpr int heap_stride(int k) { return (k + 6 + 3) & ~3; }
+
 __device__ __noinline__ float heap_replace_root(uint64_t* heap, int k, uint32_t score_bits, uint32_t row) {
     const uint64_t key = srag_pack_key(score_bits, row);
     uint64_t root = key;
-    int i = 0;
+    int i = 0;  // logical node
     for (;;) {
-        const int l = 2 * i + 1;
-        if (l >= k) break;
-        uint64_t kc = heap[l];
-        int c = l;
-        if (l + 1 < k) {
-            const uint64_t kr = heap[l + 1];
-            if (kr < kc) { kc = kr; c = l + 1; }
-        }
+        const int c0 = 4 * i + 1;
+        if (c0 >= k) break;
+        const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(heap + c0 + 3);
+        const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(heap + c0 + 5);
+        uint64_t kc = a.x;
+        int c = c0;
+        if (c0 + 1 < k && a.y < kc) { kc = a.y; c = c0 + 1; }
+        if (c0 + 2 < k && b.x < kc) { kc = b.x; c = c0 + 2; }
+        if (c0 + 3 < k && b.y < kc) { kc = b.y; c = c0 + 3; }
         if (kc >= key) break;
-        heap[i] = kc;
+        heap[i + 3] = kc;
         if (i == 0) root = kc;
         i = c;
     }
-    heap[i] = key;
+    heap[i + 3] = key;
     return root == SRAG_KEY_EMPTY ? -INFINITY : __uint_as_float(srag_key_score_bits(root));
 }
 
@@ -347,8 +355,8 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
         }
 
-        // this thread's heap: partial[q][slab * H + half][k]; threads of padding queries never insert
-        uint64_t* heap = p.partial + ((size_t)min(q_global, p.n_queries - 1) * (p.num_slabs * H) + slab * H + half) * p.k;
+        // this thread's heap: partial[q][slab * H + half][heap_stride(k)]; threads of padding queries never insert
+        uint64_t* heap = p.partial + ((size_t)min(q_global, p.n_queries - 1) * (p.num_slabs * H) + slab * H + half) * heap_stride(p.k);
         float* sc = tail->scale + ew * CPW;
         const float nanf_ = __uint_as_float(0x7FC00000u);
         const int col0 = half * CPW;
@@ -753,7 +761,7 @@ int make_plan(int sms, int n_queries, int k, Plan* pl) {
     pl->grid = units * g;
     pl->num_q_tiles = tq;
     pl->num_slabs = units / tq;
-    pl->partial_bytes = (((size_t)n_queries * pl->num_slabs * 2 * k * sizeof(uint64_t)) + 255) & ~(size_t)255;
+    pl->partial_bytes = (((size_t)n_queries * pl->num_slabs * 2 * heap_stride(k) * sizeof(uint64_t)) + 255) & ~(size_t)255;
     pl->gthr_bytes = (((size_t)n_queries * pl->num_slabs * 2 * sizeof(uint32_t)) + 255) & ~(size_t)255;
     pl->progress_bytes = (size_t)pl->num_slabs * 2 * PROG_SLOTS * sizeof(int);
     pl->window = pacing_window();
@@ -880,7 +888,10 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
         // sharing needs j = ceil(k / lists) <= 8 tracked scores and a short list of slots to poll
         const int lists = pl.num_slabs * (ew / 4);
         const int j = (k + lists - 1) / lists;
-        prm.share_j = (env_int("SRAG_TOPK_SHARE", 1) != 0 && lists >= 2 && lists <= 40 && j <= 8) ? j : 0;
+        // polling many lists costs a little per refresh: with one q-tile (148 lists) it only pays for large k
+        // (k = 100, B = 128: 18.1 -> 5.8 ms; k = 10: 3.5 -> 3.8 ms)
+        const bool worth = lists <= 80 || (lists <= 160 && k >= 32);
+        prm.share_j = (env_int("SRAG_TOPK_SHARE", 1) != 0 && lists >= 2 && worth && j <= 8) ? j : 0;
     }
     prm.window = pl.window;
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
@@ -934,7 +945,7 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
         if (rc) return rc;
     }
     if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][1], st));
-    rc = srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * (ew / 4) * k, k, q_scale, id_base, out_scores, out_ids,
+    rc = srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * (ew / 4) * heap_stride(k), k, q_scale, id_base, out_scores, out_ids,
                               st);
     if (rc) return rc;
     if (prof) {
