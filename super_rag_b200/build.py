@@ -42,7 +42,7 @@ def _digest() -> str:
     files = sources() + sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh"))
     files.append(os.path.join(os.path.dirname(HERE), "include", "srag_b200.h"))
     for p in files:
-        h.update(p.encode())
+        h.update(os.path.basename(p).encode())  # names, not absolute paths: the tree is copied to other machines
         with open(p, "rb") as f:
             h.update(f.read())
     h.update(" ".join(NVCC_FLAGS).encode())
@@ -57,11 +57,26 @@ def is_fresh() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every .cu under csrc/ into one shared library. Returns its path."""
+    """Compile every .cu under csrc/ into one shared library. Returns its path.
+    Safe under concurrent callers (one process per GPU): an exclusive file lock serialises builders, objects and
+    the library are written under process-private names and renamed into place, so nobody ever maps a
+    half-written file."""
     if not force and is_fresh():
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
-    obj_dir = os.path.join(LIB_DIR, "obj")
+    import fcntl
+    with open(os.path.join(LIB_DIR, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_fresh():  # another process built it while we waited
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
+    obj_dir = os.path.join(LIB_DIR, f"obj.{os.getpid()}")
     os.makedirs(obj_dir, exist_ok=True)
     nvcc = _nvcc()
     objs = []
@@ -74,15 +89,19 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
         objs.append(obj)
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+    tmp_lib = LIB_PATH + f".{os.getpid()}.tmp"
+    cmd = [nvcc, "-shared", "-o", tmp_lib, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     logs.append(f"$ {' '.join(cmd)}\n{r.stdout}{r.stderr}")
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp_lib, LIB_PATH)
+    shutil.rmtree(obj_dir, ignore_errors=True)
     with open(os.path.join(LIB_DIR, "build.log"), "w") as f:
         f.write("\n".join(logs))
-    with open(STAMP, "w") as f:
+    with open(STAMP + ".tmp", "w") as f:
         f.write(_digest())
+    os.replace(STAMP + ".tmp", STAMP)
     if verbose:
         print("\n".join(logs))
     return LIB_PATH
