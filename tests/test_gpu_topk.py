@@ -140,3 +140,37 @@ def test_bad_arguments_raise():
         ops.topk_search(c.cpu(), s, c[:2], s[:2], 5)
     with pytest.raises(SragError):
         ops.topk_search(c, s, torch.zeros(2, 32, device="cuda", dtype=torch.bfloat16), s[:2], 5)
+
+
+@pytest.mark.parametrize("n,d,b,k", [
+    (3000, 8, 5, 3),            # smallest legal dimension
+    (3000, 72, 9, 4),           # dim not a multiple of the 64-wide k-block: TMA zero-fills the tail
+    (900, 4096, 4, 6),          # 64 k-blocks
+    (2000, 64, 129, 5),         # ragged batches: zero-padded query staging, one and two q-tiles
+    (2000, 64, 257, 5),
+    (50, 64, 1030, 3),          # more queries than one call takes: ops splits the batch
+])
+def test_parity_more_shapes(n, d, b, k):
+    C, Q = _data(n, d, b, 7 * n + d + b)
+    _check(C, Q, k)
+
+
+def test_single_q_tile_large_k_uses_shared_threshold():
+    """B <= 128 with k >= 32: 148 lists per query publish their best score (threshold sharing across all
+    slabs). Planted duplicates and a cluster of near neighbours make sure nothing above the shared bound is lost."""
+    C, Q = _data(300_000, 128, 100, 99)
+    Q[:50] = C[1000:1050] + 0.05 * Q[:50]
+    C[250_000:250_050] = C[1000:1050]          # exact duplicates far away: both must be returned, lower id first
+    s, i = _check(C, Q, 100)
+    for b in range(50):
+        assert i[b, 0] == 1000 + b and i[b, 1] == 250_000 + b
+
+
+def test_empty_corpus_returns_padding():
+    import torch
+    from super_rag_b200 import ops
+    dev = torch.device("cuda:0")
+    q = torch.randn(3, 64, device=dev)
+    qb, qs = ops.ingest_rows(q, "cosine")
+    s, i = ops.topk_search(torch.empty(0, 64, dtype=torch.bfloat16, device=dev), torch.empty(0, device=dev), qb, qs, 4)
+    assert (i.cpu().numpy() == -1).all() and np.isinf(s.cpu().numpy()).all()
