@@ -355,11 +355,14 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         };
         // descriptor ring (head = next to fill, tail = oldest not yet released) and posting ring space
         uint32_t slot = 0, tail_slot = 0, tail_par = 0, inflight = 0, pos = 0, free_post = BM25_RING;
+        uint32_t slot_post = 0;  // lane L: postings of the chunk that occupies descriptor slot L (BM25_SLOTS == 32)
+        static_assert(BM25_SLOTS == 32, "one descriptor slot per producer lane");
         auto reserve = [&](uint32_t n_slots, uint32_t n_post) {  // wait for descriptors and ring space
             while (inflight + n_slots > (uint32_t)BM25_SLOTS || free_post < n_post) {
-                ptx::mbar_wait(&sm->empty[tail_slot], tail_par);
-                free_post += sm->meta[tail_slot].n;
-                if (++tail_slot == BM25_SLOTS) { tail_slot = 0; tail_par ^= 1; }
+                ptx::mbar_wait_lean(&sm->empty[tail_slot], tail_par);
+                free_post += __shfl_sync(0xFFFFFFFFu, slot_post, tail_slot);
+                tail_slot = (tail_slot + 1) & (BM25_SLOTS - 1);
+                tail_par ^= tail_slot == 0;
                 --inflight;
             }
         };
@@ -461,6 +464,11 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                             if (n1 < n) ptx::bulk_load_1d(dst, src + 4 * n1, (n - n1) * 4u, bar);  // wrapped remainder
                         }
                         __syncwarp();
+                        {   // lane L remembers the size of the chunk that now sits in descriptor slot L
+                            const uint32_t rel_slot = (lane - slot) & (BM25_SLOTS - 1);  // 0 .. take-1 for the new chunks
+                            const uint32_t n_src = __shfl_sync(FULL, n, (done + rel_slot) & 31);
+                            if (rel_slot < take) slot_post = n_src;
+                        }
                         slot += take;
                         if (slot >= (uint32_t)BM25_SLOTS) slot -= BM25_SLOTS;
                         pos += need;
@@ -576,7 +584,11 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         const SlotMeta m = sm->meta[slot];
         if (m.flags & (SLOT_NEW_ITEM | SLOT_END)) {
             consumer_sync();  // every add of the previous item has landed
-            if (have_item && !(debug & 2)) {
+            // A tracked item in which nothing crossed tau (the usual case in phase 1) has nothing to select and
+            // nothing to read back from the tile: go straight to zeroing. cand_count is final after the barrier
+            // above, and the only write that can race with this read is thread 0 storing the same 0 below.
+            const bool nothing = cross_bits != 0xFFFFFFFFu && sm->cand_count == 0;
+            if (have_item && !nothing && !(debug & 2)) {
                 select_item();
                 consumer_sync();  // selection has read the tile
             }
