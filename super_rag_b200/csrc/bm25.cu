@@ -28,7 +28,7 @@ constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 ac
 constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
 constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
-constexpr int BM25_CTA_THREADS = BM25_THREADS + 64;  // consumer warps + 2 producer warps (doc ids / impacts)
+constexpr int BM25_CTA_THREADS = BM25_THREADS + 64;  // consumer warps + 2 producer warps (alternate items)
 constexpr int BM25_CHUNK = 4 * BM25_THREADS;         // postings per chunk: one aligned group of 4 per consumer thread
 constexpr int BM25_CTAS_PER_SM = SRAG_BM25_WARPS == 4 ? 3 : 2;
 // posting ring capacity (x 8 bytes: doc ids + impacts)
@@ -52,6 +52,13 @@ struct SlotMeta {  // written by the producer before it issues the slot's copies
 
 __device__ __forceinline__ void consumer_sync() { ptx::named_bar_sync(1, BM25_THREADS); }
 
+struct ProducerState {  // ring bookkeeping, handed between the two producer warps with the turn
+    uint32_t slot, pos, inflight, free_post, tail_slot, tail_par;
+    uint32_t turn;                    // sequence number (in the CTA's item list) of the item whose chunks go next
+    uint32_t pad;
+    uint32_t slot_post[BM25_SLOTS];   // postings of the chunk occupying each descriptor slot
+};
+
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
@@ -59,6 +66,7 @@ struct Bm25Smem {
     alignas(128) float ring_imp[BM25_RING];
     SlotMeta meta[BM25_SLOTS];
     uint64_t full[BM25_SLOTS], empty[BM25_SLOTS];
+    ProducerState prod;
     uint32_t warp_tmp[BM25_THREADS / 32];
     uint32_t sel_bin;
     uint32_t sel_above;
@@ -321,6 +329,8 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             ptx::mbar_init(&sm->empty[s], BM25_THREADS / 32);
         }
         ptx::fence_mbar_init();
+        sm->prod.slot = 0; sm->prod.pos = 0; sm->prod.inflight = 0; sm->prod.free_post = BM25_RING;
+        sm->prod.tail_slot = 0; sm->prod.tail_par = 0; sm->prod.turn = 0;
     }
     __syncthreads();
 
@@ -353,22 +363,43 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                 hi = __ldg(bp + 1);
             }
         };
-        // descriptor ring (head = next to fill, tail = oldest not yet released) and posting ring space
+        // The two producer warps take ALTERNATE items of the CTA's list: planning an item (slice lookup, scans,
+        // chunk table) is most of a producer's work and runs in parallel on both; the issue of its chunks into
+        // the shared rings is serialised by a turn counter so that the stream stays in item order. Ring state
+        // (head / tail of the descriptor ring, posting ring position and free space) lives in shared memory and
+        // is handed over with the turn.
+        const uint32_t pw = (threadIdx.x - BM25_THREADS) >> 5;  // 0 or 1
+        ProducerState& ps = sm->prod;
         uint32_t slot = 0, tail_slot = 0, tail_par = 0, inflight = 0, pos = 0, free_post = BM25_RING;
-        uint32_t slot_post = 0;  // lane L: postings of the chunk that occupies descriptor slot L (BM25_SLOTS == 32)
-        static_assert(BM25_SLOTS == 32, "one descriptor slot per producer lane");
+        static_assert(BM25_SLOTS == 32, "descriptor slots are addressed with 5-bit arithmetic");
+        auto acquire_turn = [&](uint32_t seq) {
+            uint32_t spins = 0;
+            while (*reinterpret_cast<volatile uint32_t*>(&ps.turn) != seq) {
+                __nanosleep(32);
+                if (++spins > (1u << 26)) __trap();
+            }
+            __threadfence_block();  // the other warp's state stores are visible
+            slot = ps.slot; pos = ps.pos; inflight = ps.inflight; free_post = ps.free_post;
+            tail_slot = ps.tail_slot; tail_par = ps.tail_par;
+        };
+        auto release_turn = [&](uint32_t seq) {
+            __syncwarp();
+            if (lane == 0) {
+                ps.slot = slot; ps.pos = pos; ps.inflight = inflight; ps.free_post = free_post;
+                ps.tail_slot = tail_slot; ps.tail_par = tail_par;
+                __threadfence_block();
+                *reinterpret_cast<volatile uint32_t*>(&ps.turn) = seq + 1;
+            }
+        };
         auto reserve = [&](uint32_t n_slots, uint32_t n_post) {  // wait for descriptors and ring space
             while (inflight + n_slots > (uint32_t)BM25_SLOTS || free_post < n_post) {
                 ptx::mbar_wait_lean(&sm->empty[tail_slot], tail_par);
-                free_post += __shfl_sync(0xFFFFFFFFu, slot_post, tail_slot);
+                free_post += ps.slot_post[tail_slot];
                 tail_slot = (tail_slot + 1) & (BM25_SLOTS - 1);
                 tail_par ^= tail_slot == 0;
                 --inflight;
             }
         };
-        // Both producer warps run the same plan; one issues the doc-id copies (and owns the descriptors),
-        // the other the impact copies, so the per-lane copy issue is split between two warps.
-        const bool copies_doc = threadIdx.x < BM25_THREADS + 32;
         constexpr uint32_t FULL = 0xFFFFFFFFu;
         auto warp_incl_scan = [&](uint32_t v) {
 #pragma unroll
@@ -378,9 +409,11 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             }
             return v;
         };
-        // two-deep lookahead so that neither dependent load (term id -> slice bounds) is waited for
+        auto advance2 = [&](ItemPos p) { return advance(advance(p)); };
+        // two-deep lookahead (in this warp's own item sequence) so that neither dependent load is waited for
         ItemPos p0{(int)(blockIdx.x / (unsigned)nbx), (int)(blockIdx.x % (unsigned)nbx)};
-        ItemPos p1 = advance(p0), p2 = advance(p1), p3 = advance(p2);
+        if (pw) p0 = advance(p0);
+        ItemPos p1 = advance2(p0), p2 = advance2(p1), p3 = advance2(p2);
         float tau0, tau1, tau2;
         int64_t lo, hi, nlo, nhi;
         int32_t t0 = term_at(p0, 0, tau0);
@@ -388,9 +421,10 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         int32_t t2 = term_at(p2, 0, tau2);
         ptrs_at(p0, t0, lo, hi);
         ptrs_at(p1, t1, nlo, nhi);
-        for (; p0.ql < nq; p0 = p1, p1 = p2, p2 = p3, p3 = advance(p3)) {
+        uint32_t seq = pw;  // position of the current item in the CTA's list
+        for (; p0.ql < nq; p0 = p1, p1 = p2, p2 = p3, p3 = advance2(p3), seq += 2) {
             const int ql = p0.ql, blk = block_of(p0.j);
-            bool first_of_item = true;
+            bool first_of_item = true, have_turn = false;
             uint32_t last_hr = 0;  // valid postings of the previous chunk of this item
             for (int j0 = 0; j0 < max_terms; j0 += 32) {
                 if (j0 > 0) {  // queries with more than 32 terms: fetched in line
@@ -430,6 +464,21 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                     if (lane == 0) prev_hr = last_hr;
                     last_hr = __shfl_sync(FULL, hr, in_round - 1);
                     const bool term_barrier = j == 0 && (hr > 128u || prev_hr > 128u);
+                    // the chunk's descriptor, complete but for its ring position
+                    SlotMeta md;
+                    md.ql = ql;
+                    md.blk = blk;
+                    md.lo_rel = j == 0 ? (int32_t)lo_u : 0;
+                    md.hi_rel = (int32_t)hr;
+                    md.flags = (first_of_item && i == 0) ? SLOT_NEW_ITEM : (term_barrier ? SLOT_NEW_TERM : 0u);
+                    md.tau = tau0;
+                    md.n = n;
+                    const int32_t* src_d = post_doc + a_u + off;
+                    const float* src_w = post_imp + a_u + off;
+                    if (!have_turn) {  // everything above ran while the other warp was issuing its item
+                        acquire_turn(seq);
+                        have_turn = true;
+                    }
                     uint32_t done = 0, cum_base = 0;
                     while (done < in_round) {
                         // as many chunks as fit half the ring at once (a chunk is at most a ninth of it)
@@ -438,39 +487,24 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                         const uint32_t need = __shfl_sync(FULL, cum, done + take - 1) - cum_base;
                         reserve(take, need);
                         if (lane >= done && lane < done + take) {
-                            uint32_t my_slot = slot + (lane - done);
-                            if (my_slot >= (uint32_t)BM25_SLOTS) my_slot -= BM25_SLOTS;
+                            const uint32_t my_slot = (slot + (lane - done)) & (BM25_SLOTS - 1);
                             uint32_t my_pos = pos + (cum - n - cum_base);
                             if (my_pos >= (uint32_t)BM25_RING) my_pos -= BM25_RING;
                             uint64_t* bar = &sm->full[my_slot];
-                            if (copies_doc) {
-                                SlotMeta& m = sm->meta[my_slot];
-                                m.ql = ql;
-                                m.blk = blk;
-                                m.lo_rel = j == 0 ? (int32_t)lo_u : 0;
-                                m.hi_rel = (int32_t)hr;
-                                m.flags = (first_of_item && i == 0) ? SLOT_NEW_ITEM : (term_barrier ? SLOT_NEW_TERM : 0u);
-                                m.tau = tau0;
-                                m.pos = my_pos;
-                                m.n = n;
-                                ptx::mbar_arrive_expect_tx(bar, n * 8u);  // both warps' copies
-                            }
-                            // this warp's array: 4 bytes per posting either way
-                            const char* src = (copies_doc ? reinterpret_cast<const char*>(post_doc) : reinterpret_cast<const char*>(post_imp)) +
-                                              4 * (a_u + off);
-                            char* dst = copies_doc ? reinterpret_cast<char*>(sm->ring_doc) : reinterpret_cast<char*>(sm->ring_imp);
+                            md.pos = my_pos;
+                            sm->meta[my_slot] = md;
+                            ps.slot_post[my_slot] = n;
+                            ptx::mbar_arrive_expect_tx(bar, n * 8u);
                             const uint32_t n1 = my_pos + n <= (uint32_t)BM25_RING ? n : BM25_RING - my_pos;  // up to the ring's end
-                            ptx::bulk_load_1d(dst + 4 * my_pos, src, n1 * 4u, bar);
-                            if (n1 < n) ptx::bulk_load_1d(dst, src + 4 * n1, (n - n1) * 4u, bar);  // wrapped remainder
+                            ptx::bulk_load_1d(&sm->ring_doc[my_pos], src_d, n1 * 4u, bar);
+                            ptx::bulk_load_1d(&sm->ring_imp[my_pos], src_w, n1 * 4u, bar);
+                            if (n1 < n) {  // wrapped remainder
+                                ptx::bulk_load_1d(&sm->ring_doc[0], src_d + n1, (n - n1) * 4u, bar);
+                                ptx::bulk_load_1d(&sm->ring_imp[0], src_w + n1, (n - n1) * 4u, bar);
+                            }
                         }
                         __syncwarp();
-                        {   // lane L remembers the size of the chunk that now sits in descriptor slot L
-                            const uint32_t rel_slot = (lane - slot) & (BM25_SLOTS - 1);  // 0 .. take-1 for the new chunks
-                            const uint32_t n_src = __shfl_sync(FULL, n, (done + rel_slot) & 31);
-                            if (rel_slot < take) slot_post = n_src;
-                        }
-                        slot += take;
-                        if (slot >= (uint32_t)BM25_SLOTS) slot -= BM25_SLOTS;
+                        slot = (slot + take) & (BM25_SLOTS - 1);
                         pos += need;
                         if (pos >= (uint32_t)BM25_RING) pos -= BM25_RING;
                         free_post -= need;
@@ -481,6 +515,8 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                 }
                 if (total > 0) first_of_item = false;
             }
+            if (!have_turn) acquire_turn(seq);  // an item without postings still passes the turn on
+            release_turn(seq);
             // rotate the lookahead
             lo = nlo;
             hi = nhi;
@@ -489,11 +525,16 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             ptrs_at(p2, t2, nlo, nhi);
             t2 = term_at(p3, 0, tau2);
         }
-        reserve(1, 0);
-        if (lane == 0 && copies_doc) {
-            sm->meta[slot].flags = SLOT_END;
-            sm->meta[slot].n = 0;
-            ptx::mbar_arrive(&sm->full[slot]);
+        // the warp whose turn follows the CTA's last item closes the stream
+        const uint32_t n_cta = (uint32_t)((n_items - (long long)blockIdx.x + gridDim.x - 1) / gridDim.x);
+        if (seq == n_cta) {
+            acquire_turn(seq);
+            reserve(1, 0);
+            if (lane == 0) {
+                sm->meta[slot].flags = SLOT_END;
+                sm->meta[slot].n = 0;
+                ptx::mbar_arrive(&sm->full[slot]);
+            }
         }
         return;
     }
