@@ -1,14 +1,17 @@
 // K2: BM25 scoring over CSR postings. HBM-bound integer/float streaming work — no tensor cores.
 //
-//   bm25_block_kernel  grid (doc blocks, queries). A CTA owns one query and one range of
-//                      BM25_BLOCK_DOCS consecutive documents whose fp32 accumulators live in
-//                      shared memory. Query terms are visited in ASCENDING term id; inside a
-//                      term every posting hits a distinct document, so plain (non-atomic)
-//                      read-add-write is race-free and the per-document sum order is fixed ->
-//                      bit-exact with oracle/bm25.py. The CTA then selects its exact top-k with
-//                      an 11/11/10-bit radix select over the accumulator tile (ties -> lowest
-//                      doc id) and writes k sortable keys.
-//   srag_launch_finalize (topk_gemm.cu) merges the per-block lists of a query.
+//   bm25_items_kernel  persistent CTAs (2 per SM) walk work items = (query, block of BM25_BLOCK_DOCS
+//                      consecutive documents). The block's fp32 accumulators live in shared memory.
+//                      Query terms are applied in ASCENDING term id; inside a term every posting hits a
+//                      distinct document, so plain (non-atomic) read-add-write is race-free and the
+//                      per-document sum order is fixed -> bit-exact with oracle/bm25.py.
+//                      Two producer warps look the posting slices up and stream them through a packed
+//                      shared-memory ring with 1-D bulk copies; eight consumer warps follow the chunk
+//                      descriptors, accumulate, and select (details at the kernel).
+//                      Selection is two-phase: a sample of the blocks gets an exact block top-k, its
+//                      k-th best score tau bounds the query's global k-th score from below, and the other
+//                      blocks only record the documents whose accumulator crosses tau.
+//   srag_launch_finalize(_ex) (topk_gemm.cu) merges the per-block lists of a query.
 //
 // Algorithmic bytes per query = 8 * sum_t df(t)  (int32 doc + fp32 impact per posting).
 // The reference has no BM25 arithmetic; contract: oracle/bm25.py docstring.
