@@ -106,7 +106,7 @@ int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int* n_calls);
  * The `fulltext_search` node the reference declares but does not implement
  * (super_rag/nodeflow/runners/merge.py:18-20, super_rag/schema/view_models.py:1043-1047).
  * Index layout (CSR by term): term_ptr int64 [vocab+1]; post_doc int32 [nnz] ascending
- * inside a term; post_imp fp32 [nnz]. Numeric contract: oracle/bm25.py docstring.
+ * inside a term (until srag_bm25_bank_order permutes the doc-block slices); post_imp fp32 [nnz]. Numeric contract: oracle/bm25.py docstring.
  *
  * srag_bm25_impacts: imp = idf[term] * tf*(k1+1) / (tf + k1*(1-b+b*dl/avgdl)), one IEEE
  * fp32 op per step; the term of posting p is found by bisection in term_ptr.
@@ -119,6 +119,14 @@ int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32_t* post_do
 int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* post_doc, int vocab,
                           int64_t n_docs, int block_docs, int64_t* block_ptr, void* stream);
 int srag_bm25_block_docs(void);   /* doc-range width one CTA accumulates in shared memory */
+/* Index-build step after srag_bm25_block_index: permutes the postings INSIDE every (term, doc-block) slice
+ * (doc_in/imp_in -> doc_out/imp_out, same offsets, not in place; arrays padded by 4 entries like the inputs)
+ * so that the 32 accumulators one warp of the scoring kernel touches per shared-memory access fall on
+ * distinct banks where the slice allows it. Every posting of a slice is a distinct document that receives
+ * one add per query, so scores are unchanged bit for bit; block_ptr stays valid. After this call post_doc is
+ * ascending per (term, block) slice only as a SET, not as a sequence.                                     */
+int srag_bm25_bank_order(const int64_t* block_ptr, int vocab, int64_t n_docs, const int32_t* doc_in,
+                         const float* imp_in, int32_t* doc_out, float* imp_out, void* stream);
 int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes);
 /* q_terms int32 [n_queries, max_terms]: unique term ids in ASCENDING order, -1 padded.
  * out_* [n_queries, k]; only documents matching >= 1 term are candidates.               */

@@ -11,6 +11,7 @@ term lists. Scoring, impacts, block index and top-k are CUDA kernels.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Iterable, List, Optional, Sequence
 
@@ -52,10 +53,26 @@ class Bm25Index:
     """CSR-by-term postings (int32 doc, fp32 impact) + per-term doc-block offsets, all on one GPU."""
 
     def __init__(self, term_ptr, post_doc, post_imp, block_ptr, n_docs: int, vocab: int, dl, stats: Bm25Stats,
-                 id_base: int = 0):
+                 id_base: int = 0, bank_ordered: bool = False):
         self.term_ptr, self.post_doc, self.post_imp, self.block_ptr = term_ptr, post_doc, post_imp, block_ptr
         self.n_docs, self.vocab, self.dl, self.stats, self.id_base = n_docs, vocab, dl, stats, id_base
+        self.bank_ordered = bank_ordered
         self._ws = None
+
+    def _bank_order(self) -> None:
+        """Permute every (term, doc-block) slice for conflict-free accumulation (ops.bm25_bank_order). Scores do not
+        depend on the order inside a slice. SRAG_BM25_BANK_ORDER=0 keeps ascending documents (A/B measurements)."""
+        if self.bank_ordered or os.environ.get("SRAG_BM25_BANK_ORDER", "1") == "0":
+            return
+        self.post_doc, self.post_imp = ops.bm25_bank_order(self.block_ptr, self.post_doc, self.post_imp, self.n_docs)
+        self.bank_ordered = True
+
+    def canonical_postings(self):
+        """(post_doc, post_imp) with ascending documents inside every term — the order the oracle builds."""
+        df = self.term_ptr[1:] - self.term_ptr[:-1]
+        term = torch.repeat_interleave(torch.arange(self.vocab, device=self.device, dtype=torch.int64), df)
+        order = torch.argsort(term * max(1, self.n_docs) + self.post_doc.to(torch.int64))
+        return self.post_doc[order], self.post_imp[order]
 
     @property
     def nnz(self) -> int:
@@ -100,7 +117,9 @@ class Bm25Index:
         post_doc = pd[:nnz]
         imp = ops.bm25_impacts(term_ptr, post_doc, post_tf, idf, dl, stats.avgdl)
         block_ptr = ops.bm25_block_index(term_ptr, post_doc, n_docs)
-        return cls(term_ptr, post_doc, imp, block_ptr, n_docs, vocab, dl, stats, id_base)
+        idx = cls(term_ptr, post_doc, imp, block_ptr, n_docs, vocab, dl, stats, id_base)
+        idx._bank_order()
+        return idx
 
     @classmethod
     def from_tokens(cls, tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int, stats: Optional[Bm25Stats] = None,
@@ -112,7 +131,7 @@ class Bm25Index:
     def save(self, path: str) -> None:
         from . import shardio
         meta = {"n_docs": self.n_docs, "vocab": self.vocab, "id_base": self.id_base, "stats_n_docs": self.stats.n_docs,
-                "avgdl": float(self.stats.avgdl)}
+                "avgdl": float(self.stats.avgdl), "bank_ordered": bool(self.bank_ordered), "block_docs": ops.bm25_block_docs()}
         shardio.write_shard(path, "bm25", meta, {
             "term_ptr": self.term_ptr, "post_doc": self.post_doc, "post_imp": self.post_imp, "dl": self.dl,
             "df": torch.from_numpy(np.ascontiguousarray(self.stats.df, dtype=np.int64))})
@@ -136,9 +155,21 @@ class Bm25Index:
         stats = Bm25Stats(n_docs=int(meta["stats_n_docs"]), df=a["df"].cpu().numpy().astype(np.int64),
                           avgdl=float(meta["avgdl"]))
         term_ptr = a["term_ptr"]
-        block_ptr = ops.bm25_block_index(term_ptr, pd[:nnz], int(meta["n_docs"]))
-        return cls(term_ptr, pd[:nnz], pi[:nnz], block_ptr, int(meta["n_docs"]), int(meta["vocab"]), a["dl"], stats,
-                   int(meta["id_base"]))
+        n_docs, vocab = int(meta["n_docs"]), int(meta["vocab"])
+        ordered = bool(meta.get("bank_ordered", False))
+        idx = cls(term_ptr, pd[:nnz], pi[:nnz], None, n_docs, vocab, a["dl"], stats, int(meta["id_base"]),
+                  bank_ordered=ordered)
+        if ordered and int(meta.get("block_docs", 0)) != ops.bm25_block_docs():
+            # written by a library with another doc-block width: back to ascending documents, then re-ordered below
+            d, w = idx.canonical_postings()
+            pd[:nnz] = d
+            pi[:nnz] = w
+            idx.bank_ordered = False
+        # The offsets are found by bisection on "doc < j * block_docs", which is monotone along a term as long as its
+        # doc-block slices follow one another — true for ascending and for bank-ordered postings of this block width.
+        idx.block_ptr = ops.bm25_block_index(term_ptr, idx.post_doc, n_docs)
+        idx._bank_order()
+        return idx
 
     # ---- search ----------------------------------------------------------------------------
     def search_terms(self, q_terms: torch.Tensor, k: int, **filter_kw):

@@ -27,6 +27,10 @@ namespace {
 #ifndef SRAG_BM25_WARPS
 #define SRAG_BM25_WARPS 8
 #endif
+// 1: consumers fetch chunk s+1 between the accumulator reads and the adds of chunk s (see the consumer loop)
+#ifndef SRAG_BM25_PIPE
+#define SRAG_BM25_PIPE 0
+#endif
 constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 accumulators per CTA
 constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
@@ -623,9 +627,48 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         if ((debug & 64) || !select_near_max(sm, k, doc_base, out)) select_exact(sm, k, doc_base, total, out);
     };
 
-    for (;;) {
+    // One chunk of the slot stream held in registers: descriptor + this thread's aligned group of 4 postings.
+    struct Chunk {
+        SlotMeta m;
+        int4 dd;
+        float4 ww;
+        bool active;
+    };
+    // Wait for the slot, take the descriptor and the postings into registers and hand the ring space back.
+    auto fetch = [&]() -> Chunk {
+        Chunk c;
         ptx::mbar_wait(&sm->full[slot], par);
-        const SlotMeta m = sm->meta[slot];
+        c.m = sm->meta[slot];
+        c.dd = make_int4(0, 0, 0, 0);
+        c.ww = make_float4(0.f, 0.f, 0.f, 0.f);
+        c.active = false;
+        if (c.m.flags & SLOT_END) return c;  // no data, nothing to hand back
+        const int rel = 4 * (int)threadIdx.x;
+        c.active = rel < c.m.hi_rel && rel + 4 > c.m.lo_rel;
+        if (c.active) {
+            uint32_t idx = c.m.pos + (uint32_t)rel;
+            if (idx >= (uint32_t)BM25_RING) idx -= BM25_RING;
+            c.dd = *reinterpret_cast<const int4*>(&sm->ring_doc[idx]);
+            c.ww = *reinterpret_cast<const float4*>(&sm->ring_imp[idx]);
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
+        if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
+        return c;
+    };
+
+#if SRAG_BM25_PIPE
+    // Software-pipelined: the next chunk's wait / descriptor / postings are fetched between the accumulator reads of
+    // the current chunk and its adds, so the three dependent shared-memory round trips of a chunk overlap the next
+    // one's. Fetching ahead cannot deadlock: the producer fills slot s+1 as soon as there is ring space, and every
+    // slot up to s has already been handed back.
+    Chunk cur = fetch();
+#endif
+    for (;;) {
+#if !SRAG_BM25_PIPE
+        const Chunk cur = fetch();
+#endif
+        const SlotMeta m = cur.m;
         if (m.flags & (SLOT_NEW_ITEM | SLOT_END)) {
             consumer_sync();  // every add of the previous item has landed
             // A tracked item in which nothing crossed tau (the usual case in phase 1) has nothing to select and
@@ -654,25 +697,23 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             consumer_sync();
         }
         const int rel = 4 * (int)threadIdx.x;
-        int4 dd = make_int4(0, 0, 0, 0);
-        float4 ww = make_float4(0.f, 0.f, 0.f, 0.f);
-        const bool active = rel < m.hi_rel && rel + 4 > m.lo_rel;
+        const int4 dd = cur.dd;
+        const float4 ww = cur.ww;
+        const bool active = cur.active && !(debug & 1);
+        const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
+        const bool m0 = active && rel >= m.lo_rel && rel < m.hi_rel, m1 = active && rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
+        const bool m2 = active && rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = active && rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
+        const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
+        const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         if (active) {
-            uint32_t idx = m.pos + (uint32_t)rel;
-            if (idx >= (uint32_t)BM25_RING) idx -= BM25_RING;
-            dd = *reinterpret_cast<const int4*>(&sm->ring_doc[idx]);
-            ww = *reinterpret_cast<const float4*>(&sm->ring_imp[idx]);
-        }
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
-        if (active && !(debug & 1)) {
-            const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
-            const bool m0 = rel >= m.lo_rel && rel < m.hi_rel, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
-            const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
-            const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
-            const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
             // the four reads are issued together, then the adds, then the writes (one latency, not four)
-            const float a0 = sm->acc[r0], a1 = sm->acc[r1], a2 = sm->acc[r2], a3 = sm->acc[r3];
+            a0 = sm->acc[r0]; a1 = sm->acc[r1]; a2 = sm->acc[r2]; a3 = sm->acc[r3];
+        }
+#if SRAG_BM25_PIPE
+        cur = fetch();
+#endif
+        if (active) {
             const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y), n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
             if (m0) sm->acc[r0] = n0;
             if (m1) sm->acc[r1] = n1;
@@ -695,7 +736,6 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                     }
             }
         }
-        if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
     }
 }
 
@@ -741,6 +781,99 @@ __global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, co
     }
 }
 
+// Bank order (index build). Inside a (term, block) slice every posting is a distinct document and receives exactly
+// one add per query, so the ORDER of a slice's postings is free: sums, and therefore scores, do not depend on it.
+// The consumers of bm25_items_kernel read-add-write acc[doc - doc_base] with lane l of a warp holding postings
+// 4l .. 4l+3 of the warp's aligned group of 128, i.e. one shared-memory access covers the 32 postings at positions
+// 128g + 4l + e (fixed g, e). With postings in ascending document order their banks (doc & 31) are as good as random:
+// 3.4 wavefronts per access. This kernel permutes each slice so that those 32 postings fall on distinct banks
+// wherever the slice allows it: the postings are laid out "round-robin over banks" (all first-of-their-bank
+// postings in bank order, then all second ones, ...; a window of 32 consecutive entries of full rounds hits every
+// bank once) and that sequence is written to the slice's positions in ACCESS order (g, e, l). The floor is
+// max_b count(b) wavefronts per slice; simulation: 3.4 -> 1.6 wavefronts per access for slices of ~800 postings,
+// -> 1.2 for ~5000. One warp per slice, deterministic (stable inside a bank).
+constexpr int BANK_ORDER_WARPS = 8;
+__global__ void __launch_bounds__(32 * BANK_ORDER_WARPS)
+bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_blocks,
+                       const int32_t* __restrict__ doc_in, const float* __restrict__ imp_in,
+                       int32_t* __restrict__ doc_out, float* __restrict__ imp_out) {
+    __shared__ uint32_t cnt_s[BANK_ORDER_WARPS][32];
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t* cnt = cnt_s[w];
+    const int64_t n_slices = (int64_t)vocab * n_blocks;
+    const int64_t n_warps = (int64_t)gridDim.x * BANK_ORDER_WARPS;
+    for (int64_t s0 = ((int64_t)blockIdx.x * BANK_ORDER_WARPS + w) * 32; s0 < n_slices; s0 += n_warps * 32) {
+        // the bounds of 32 consecutive slices, one per lane
+        int64_t lo_l = 0, hi_l = 0;
+        if (s0 + lane < n_slices) {
+            const int64_t t = (s0 + lane) / n_blocks, j = (s0 + lane) - t * n_blocks;
+            const int64_t* bp = block_ptr + t * (n_blocks + 1) + j;
+            lo_l = __ldg(bp);
+            hi_l = __ldg(bp + 1);
+        }
+        uint32_t todo = __ballot_sync(FULL, hi_l > lo_l);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t lo = __shfl_sync(FULL, lo_l, src), hi = __shfl_sync(FULL, hi_l, src);
+            const int n = (int)(hi - lo);
+            const int64_t a = lo & ~(int64_t)3;                // the consumers' groups of 4 / 128 are aligned to this
+            const int lo_off = (int)(lo - a), hi_off = lo_off + n;
+            // pass 1: postings per bank (lane b ends up holding the count of bank b)
+            cnt[lane] = 0;
+            __syncwarp();
+            for (int i = lane; i < n; i += 32) atomicAdd(&cnt[__ldg(doc_in + lo + i) & 31], 1u);
+            __syncwarp();
+            const uint32_t c = cnt[lane];
+            __syncwarp();
+            cnt[lane] = 0;  // pass 2: postings of each bank placed so far
+            __syncwarp();
+            for (int base = 0; base < n; base += 32) {
+                const int i = base + lane;
+                const bool valid = i < n;
+                const int32_t d = valid ? __ldg(doc_in + lo + i) : 0;
+                const float im = valid ? __ldg(imp_in + lo + i) : 0.f;
+                const uint32_t b = (uint32_t)d & 31u;
+                const uint32_t peers = __match_any_sync(FULL, valid ? b : 32u + (uint32_t)lane);
+                // r = how many postings of this bank come before this one (stable: slice order)
+                const uint32_t r = cnt[b] + __popc(peers & ((1u << lane) - 1u));
+                __syncwarp();
+                if (valid && (peers >> lane) == 1u) cnt[b] = r + 1;  // the highest lane of the group
+                __syncwarp();
+                // index in the round-robin sequence: every bank contributes min(count, r) entries to rounds 0..r-1,
+                // and the banks below b that still have an r-th posting come first in round r
+                uint32_t sidx = 0;
+#pragma unroll
+                for (int bb = 0; bb < 32; ++bb) {
+                    const uint32_t cb = __shfl_sync(FULL, c, bb);
+                    sidx += (cb < r ? cb : r) + (((uint32_t)bb < b && cb > r) ? 1u : 0u);
+                }
+                if (valid) {
+                    // the sidx-th position of the slice in access order (group g, element e, lane l)
+                    const int g = ((int)sidx + lo_off) >> 7;
+                    int k = (int)sidx - (g ? 128 * g - lo_off : 0);
+                    const int sg = g ? 0 : lo_off;
+                    const int tg = hi_off - 128 * g < 128 ? hi_off - 128 * g : 128;
+                    int pos = -1;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int l0 = (sg - e + 3) >> 2, l1 = (tg - e + 3) >> 2;
+                        const int ne = l1 > l0 ? l1 - l0 : 0;
+                        if (pos < 0) {
+                            if (k < ne) pos = 128 * g + 4 * (l0 + k) + e;
+                            else k -= ne;
+                        }
+                    }
+                    doc_out[a + pos] = d;
+                    imp_out[a + pos] = im;
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
 int bm25_blocks(int64_t n_docs) { return (int)((n_docs + BM25_BLOCK_DOCS - 1) / BM25_BLOCK_DOCS); }
 constexpr int BM25_Q_CHUNK = 1024;  // queries whose per-block lists are resident at once (0.5 GB at 10 M docs, k = 100)
 
@@ -774,6 +907,22 @@ extern "C" int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* pos
     if (blocks > 148 * 32) blocks = 148 * 32;
     bm25_block_index_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
         term_ptr, post_doc, vocab, nb, block_docs, block_ptr);
+    SRAG_CUDA(cudaGetLastError());
+    return SRAG_OK;
+}
+
+extern "C" int srag_bm25_bank_order(const int64_t* block_ptr, int vocab, int64_t n_docs, const int32_t* doc_in,
+                                    const float* imp_in, int32_t* doc_out, float* imp_out, void* stream) {
+    SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF, "bad sizes vocab=%d n_docs=%lld", vocab,
+                   (long long)n_docs);
+    if (n_docs == 0) return SRAG_OK;
+    SRAG_CHECK_ARG(block_ptr && doc_in && imp_in && doc_out && imp_out, "null pointer argument");
+    SRAG_CHECK_ARG(doc_in != doc_out && imp_in != imp_out, "the permutation is not in place");
+    const int nb = bm25_blocks(n_docs);
+    const int64_t rounds = ((int64_t)vocab * nb + 32 * BANK_ORDER_WARPS - 1) / (32 * BANK_ORDER_WARPS);
+    const int64_t blocks = rounds < 148 * 64 ? rounds : 148 * 64;
+    bm25_bank_order_kernel<<<(int)blocks, 32 * BANK_ORDER_WARPS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        block_ptr, vocab, nb, doc_in, imp_in, doc_out, imp_out);
     SRAG_CUDA(cudaGetLastError());
     return SRAG_OK;
 }

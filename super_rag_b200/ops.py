@@ -183,6 +183,22 @@ def bm25_block_index(term_ptr, post_doc, n_docs: int) -> torch.Tensor:
     return bp
 
 
+def bm25_bank_order(block_ptr, post_doc, post_imp, n_docs: int):
+    """Permute the postings inside every (term, doc-block) slice for conflict-free shared-memory accumulation
+    (srag_bm25_bank_order). Returns new (post_doc, post_imp), padded like the inputs; scores are unchanged."""
+    _need_cuda(block_ptr, post_doc, post_imp)
+    nnz = post_doc.numel()
+    dev = post_doc.device
+    with torch.cuda.device(dev):
+        pd = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]
+        pi = torch.zeros(nnz + 4, dtype=torch.float32, device=dev)[:nnz]
+        if nnz:
+            _lib.check(_lib.load().srag_bm25_bank_order(_ptr(block_ptr), block_ptr.shape[0], n_docs, _ptr(post_doc),
+                                                        _ptr(post_imp), _ptr(pd), _ptr(pi), _stream(dev)),
+                       "srag_bm25_bank_order")
+    return pd, pi
+
+
 def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tensor, k: int, id_base: int = 0,
                 workspace: Optional[torch.Tensor] = None, doc_tags: Optional[torch.Tensor] = None,
                 q_tag_mask: Optional[torch.Tensor] = None, doc_group: Optional[torch.Tensor] = None,

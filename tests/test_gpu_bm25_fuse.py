@@ -35,8 +35,9 @@ def test_bm25_bit_exact(n_docs, vocab, mean_len, k):
     tokens, doc_ptr = zipf_corpus(n_docs, vocab, mean_len, seed=n_docs)
     idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
     assert (idx.term_ptr.cpu().numpy() == tp).all()
-    assert (idx.post_doc.cpu().numpy() == pd).all()
-    assert (idx.post_imp.cpu().numpy().view(np.uint32) == imp.view(np.uint32)).all(), "impacts not bit-exact"
+    cd, ci = idx.canonical_postings()  # the index keeps every (term, doc-block) slice in bank order
+    assert (cd.cpu().numpy() == pd).all()
+    assert (ci.cpu().numpy().view(np.uint32) == imp.view(np.uint32)).all(), "impacts not bit-exact"
     rng = np.random.default_rng(4)
     queries = [rng.integers(0, vocab, size=int(rng.integers(1, 9))).tolist() for _ in range(40)]
     queries += [[0], [vocab - 1], [], [0, 1, 2, 3, 4, 5, 6, 7], [5, 5, 5, -3, vocab + 10]]
@@ -190,3 +191,58 @@ def test_bm25_two_phase_with_ties_at_the_threshold():
         os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, k)
         assert (i.cpu().numpy() == oi).all(), k
         assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all(), k
+
+
+def _wavefronts(docs, lo):
+    """Shared-memory wavefronts of the scoring kernel's accumulator accesses over one slice whose first posting
+    sits at absolute offset lo: one access = the postings at positions 128g + 4l + e (fixed g, e) relative to lo & ~3;
+    its cost = the largest number of them on one bank (doc & 31)."""
+    pos = np.arange(len(docs)) + (lo & 3)
+    grp = (pos >> 7) * 4 + (pos & 3)
+    tot = acc = 0
+    for gkey in np.unique(grp):
+        tot += np.bincount(docs[grp == gkey] & 31, minlength=32).max()
+        acc += 1
+    return tot, acc
+
+
+def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
+    import torch
+    from super_rag_b200 import ops
+    from super_rag_b200.bm25 import Bm25Index
+    n_docs, vocab = 70_000, 400
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, 60, seed=77)
+    monkeypatch.setenv("SRAG_BM25_BANK_ORDER", "0")
+    plain = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
+    monkeypatch.delenv("SRAG_BM25_BANK_ORDER")
+    idx = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
+    assert not plain.bank_ordered and idx.bank_ordered
+    bd = ops.bm25_block_docs()
+    d0, w0 = plain.post_doc.cpu().numpy(), plain.post_imp.cpu().numpy().view(np.uint32)
+    d1, w1 = idx.post_doc.cpu().numpy(), idx.post_imp.cpu().numpy().view(np.uint32)
+    bp = idx.block_ptr.cpu().numpy()
+    assert (bp == plain.block_ptr.cpu().numpy()).all()
+    # every slice holds the same (doc, impact) pairs as before, all inside its doc block
+    t0 = t1 = 0
+    for t in range(vocab):
+        for j in range(bp.shape[1] - 1):
+            lo, hi = int(bp[t, j]), int(bp[t, j + 1])
+            if lo == hi:
+                continue
+            a, b = d0[lo:hi], d1[lo:hi]
+            assert (b // bd == j).all()
+            o = np.argsort(b, kind="stable")
+            assert (b[o] == a).all() and (w1[lo:hi][o] == w0[lo:hi]).all()
+            if hi - lo >= 64:
+                t0 += _wavefronts(a, lo)[0]
+                t1 += _wavefronts(b, lo)[0]
+    assert t1 < 0.7 * t0, (t0, t1)
+    # same scores and ids, bit for bit, from both layouts
+    rng = np.random.default_rng(5)
+    queries = [rng.integers(0, vocab, size=int(rng.integers(1, 9))).tolist() for _ in range(64)]
+    s0, i0 = plain.search(queries, 50)
+    s1, i1 = idx.search(queries, 50)
+    assert torch.equal(i0, i1) and torch.equal(s0.view(torch.int32), s1.view(torch.int32))
+    # deterministic: a second build gives the same layout
+    again = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
+    assert torch.equal(again.post_doc, idx.post_doc) and torch.equal(again.post_imp.view(torch.int32), idx.post_imp.view(torch.int32))
