@@ -27,10 +27,6 @@ namespace {
 #ifndef SRAG_BM25_WARPS
 #define SRAG_BM25_WARPS 8
 #endif
-// 1: consumers fetch chunk s+1 between the accumulator reads and the adds of chunk s (see the consumer loop)
-#ifndef SRAG_BM25_PIPE
-#define SRAG_BM25_PIPE 0
-#endif
 constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 accumulators per CTA
 constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
@@ -627,48 +623,9 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         if ((debug & 64) || !select_near_max(sm, k, doc_base, out)) select_exact(sm, k, doc_base, total, out);
     };
 
-    // One chunk of the slot stream held in registers: descriptor + this thread's aligned group of 4 postings.
-    struct Chunk {
-        SlotMeta m;
-        int4 dd;
-        float4 ww;
-        bool active;
-    };
-    // Wait for the slot, take the descriptor and the postings into registers and hand the ring space back.
-    auto fetch = [&]() -> Chunk {
-        Chunk c;
-        ptx::mbar_wait(&sm->full[slot], par);
-        c.m = sm->meta[slot];
-        c.dd = make_int4(0, 0, 0, 0);
-        c.ww = make_float4(0.f, 0.f, 0.f, 0.f);
-        c.active = false;
-        if (c.m.flags & SLOT_END) return c;  // no data, nothing to hand back
-        const int rel = 4 * (int)threadIdx.x;
-        c.active = rel < c.m.hi_rel && rel + 4 > c.m.lo_rel;
-        if (c.active) {
-            uint32_t idx = c.m.pos + (uint32_t)rel;
-            if (idx >= (uint32_t)BM25_RING) idx -= BM25_RING;
-            c.dd = *reinterpret_cast<const int4*>(&sm->ring_doc[idx]);
-            c.ww = *reinterpret_cast<const float4*>(&sm->ring_imp[idx]);
-        }
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
-        if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
-        return c;
-    };
-
-#if SRAG_BM25_PIPE
-    // Software-pipelined: the next chunk's wait / descriptor / postings are fetched between the accumulator reads of
-    // the current chunk and its adds, so the three dependent shared-memory round trips of a chunk overlap the next
-    // one's. Fetching ahead cannot deadlock: the producer fills slot s+1 as soon as there is ring space, and every
-    // slot up to s has already been handed back.
-    Chunk cur = fetch();
-#endif
     for (;;) {
-#if !SRAG_BM25_PIPE
-        const Chunk cur = fetch();
-#endif
-        const SlotMeta m = cur.m;
+        ptx::mbar_wait(&sm->full[slot], par);
+        const SlotMeta m = sm->meta[slot];
         if (m.flags & (SLOT_NEW_ITEM | SLOT_END)) {
             consumer_sync();  // every add of the previous item has landed
             // A tracked item in which nothing crossed tau (the usual case in phase 1) has nothing to select and
@@ -697,23 +654,25 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             consumer_sync();
         }
         const int rel = 4 * (int)threadIdx.x;
-        const int4 dd = cur.dd;
-        const float4 ww = cur.ww;
-        const bool active = cur.active && !(debug & 1);
-        const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
-        const bool m0 = active && rel >= m.lo_rel && rel < m.hi_rel, m1 = active && rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
-        const bool m2 = active && rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = active && rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
-        const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
-        const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        int4 dd = make_int4(0, 0, 0, 0);
+        float4 ww = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool active = rel < m.hi_rel && rel + 4 > m.lo_rel;
         if (active) {
-            // the four reads are issued together, then the adds, then the writes (one latency, not four)
-            a0 = sm->acc[r0]; a1 = sm->acc[r1]; a2 = sm->acc[r2]; a3 = sm->acc[r3];
+            uint32_t idx = m.pos + (uint32_t)rel;
+            if (idx >= (uint32_t)BM25_RING) idx -= BM25_RING;
+            dd = *reinterpret_cast<const int4*>(&sm->ring_doc[idx]);
+            ww = *reinterpret_cast<const float4*>(&sm->ring_imp[idx]);
         }
-#if SRAG_BM25_PIPE
-        cur = fetch();
-#endif
-        if (active) {
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
+        if (active && !(debug & 1)) {
+            const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
+            const bool m0 = rel >= m.lo_rel && rel < m.hi_rel, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
+            const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
+            const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
+            const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
+            // the four reads are issued together, then the adds, then the writes (one latency, not four)
+            const float a0 = sm->acc[r0], a1 = sm->acc[r1], a2 = sm->acc[r2], a3 = sm->acc[r3];
             const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y), n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
             if (m0) sm->acc[r0] = n0;
             if (m1) sm->acc[r1] = n1;
@@ -736,6 +695,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
                     }
             }
         }
+        if (++slot == BM25_SLOTS) { slot = 0; par ^= 1; }
     }
 }
 
