@@ -28,6 +28,10 @@ namespace {
 #define SRAG_BM25_WARPS 8
 #endif
 constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 accumulators per CTA
+// Index granularity: block_ptr holds one offset per (term, BM25_SUB_DOCS documents). A tile of bm25_items_kernel is
+// BM25_SUBS consecutive sub-blocks; bm25_sub_kernel gives one sub-block to one warp.
+constexpr int BM25_SUB_DOCS = 2048;
+constexpr int BM25_SUBS = BM25_BLOCK_DOCS / BM25_SUB_DOCS;
 constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
 constexpr int SLOTS_PER_THREAD = BM25_BLOCK_DOCS / BM25_THREADS;  // 64 contiguous slots (ordered tie path only)
@@ -313,14 +317,17 @@ struct Bm25Filter {  // metadata pre-filter, same rule as K1 (srag_topk_search_f
 
 template <bool FILT>  // FILT: the unfiltered instantiation carries none of the filter code
 __global__ void __launch_bounds__(BM25_CTA_THREADS, BM25_CTAS_PER_SM)
-bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restrict__ post_doc,
-                  const float* __restrict__ post_imp, int n_blocks, const int32_t* __restrict__ q_terms,
+bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, const int32_t* __restrict__ post_doc,
+                  const float* __restrict__ post_imp, int n_blocks, int n_sub, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
                   const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
                   uint64_t* __restrict__ partial /* phase 1: [nq][n_blocks][k]; phase 0: [nq][ceil(n_blocks/stride)][k] */,
-                  int debug /* SRAG_BM25_DEBUG */, Bm25Filter flt, int64_t n_docs) {
+                  int debug /* SRAG_BM25_DEBUG */, Bm25Filter flt, int64_t n_docs,
+                  const uint32_t* __restrict__ q_flag /* non-null: only the flagged queries (fallback of bm25_sub_kernel) */,
+                  const uint32_t* __restrict__ n_flagged) {
     extern __shared__ uint8_t bm25_smem_raw[];
     Bm25Smem* sm = reinterpret_cast<Bm25Smem*>(bm25_smem_raw);
+    if (q_flag && *n_flagged == 0) return;  // nothing overflowed: the usual case
     const int nb0 = (n_blocks + stride - 1) / stride;
     const int nbx = phase == 0 ? nb0 : n_blocks - nb0;
     const long long n_items = (long long)nq * nbx;
@@ -354,6 +361,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
         auto term_at = [&](ItemPos p, int j0, float& tq) -> int32_t {
             tq = 0.f;
             if (p.ql >= nq) return -1;
+            if (q_flag && q_flag[p.ql] == 0) return -1;  // an item without terms costs nothing downstream
             if (phase == 1) tq = __ldg(tau + (size_t)p.ql * k + (k - 1));
             return j0 + lane < max_terms ? __ldg(q_terms + (size_t)(q_offset + p.ql) * max_terms + j0 + lane) : -1;
         };
@@ -361,9 +369,10 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
             lo = 0;
             hi = 0;
             if (p.ql < nq && t >= 0) {
-                const int64_t* bp = block_ptr + (size_t)t * (n_blocks + 1) + block_of(p.j);
-                lo = __ldg(bp);
-                hi = __ldg(bp + 1);
+                const int s0 = block_of(p.j) * BM25_SUBS;  // the tile = sub-blocks s0 .. s0 + BM25_SUBS - 1
+                const int64_t* bp = block_ptr + (size_t)t * (n_sub + 1);
+                lo = __ldg(bp + s0);
+                hi = __ldg(bp + (s0 + BM25_SUBS < n_sub ? s0 + BM25_SUBS : n_sub));
             }
         };
         // The two producer warps take ALTERNATE items of the CTA's list: planning an item (slice lookup, scans,
@@ -699,6 +708,297 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr, const int32_t* __restri
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// bm25_sub_kernel: phase 1 (tau known) at WARP granularity. A work item is (query, sub-block of BM25_SUB_DOCS
+// documents); the sub-block's fp32 accumulators are 8 KB of shared memory private to ONE warp, so every add to a
+// document is made by the same warp: terms are applied in ascending order with nothing but __syncwarp() between
+// rounds — no CTA barrier, no producer warps, no descriptor ring. 27 independent warps per SM walk the items
+// round-robin; neighbouring warps take neighbouring sub-blocks, i.e. neighbouring pieces of the same posting lists.
+//   * lane u holds the bounds of query term u inside the sub-block (block_ptr), fetched one item ahead (term ids two
+//     ahead), so no dependent load is waited for;
+//   * a round = 32 consecutive postings of one term (one coalesced load per array, L1 no-allocate); rounds of all
+//     terms form one stream in ascending-term order that is loaded SUB_DEPTH rounds ahead of the adds;
+//   * a document whose accumulator crosses tau is remembered (<= SUB_CAND per item); at the end of the item its
+//     final score goes into the query's candidate region — the query's slice of `partial`, filled from slot k up
+//     (slots 0..k-1 hold the sample's top-k) through one atomic counter per query. tau is the k-th best score of a
+//     1/stride sample, so a query collects about stride * k candidates over all its items;
+//   * more crossings in one sub-block than SUB_CAND, or a full region, flags the QUERY; flagged queries are redone
+//     by bm25_items_kernel (exact per-block selection) after their region is cleared. Massive ties end up there.
+// Per-document sums are formed exactly as in bm25_items_kernel: bit-exact with the oracle.
+constexpr int SUB_WARPS = 27;   // 27 x 8 KB of accumulators + candidate lists = 222 KB: one CTA per SM
+constexpr int SUB_CAND = 64;
+#ifndef SRAG_BM25_SUB_DEPTH
+#define SRAG_BM25_SUB_DEPTH 2
+#endif
+constexpr int SUB_DEPTH = SRAG_BM25_SUB_DEPTH;  // rounds (of 128 postings) in flight per warp
+
+struct SubSmem {
+    float acc[SUB_WARPS][BM25_SUB_DOCS];
+    uint16_t cand[SUB_WARPS][SUB_CAND];
+    uint32_t cand_count[SUB_WARPS];
+};
+
+__device__ __forceinline__ int4 ldg_stream_s32x4(const int32_t* p) {
+    int4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float4 ldg_stream_f32x4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+template <bool FILT>
+__global__ void __launch_bounds__(32 * SUB_WARPS, 1)
+bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, const int32_t* __restrict__ post_doc,
+                const float* __restrict__ post_imp, int n_blocks, int n_sub, const int32_t* __restrict__ q_terms,
+                int max_terms, int k, int q_offset, int nq, int stride, const float* __restrict__ tau /* [nq][k] */,
+                uint64_t* __restrict__ partial /* [nq][n_blocks * k] */, uint32_t* __restrict__ q_count /* [nq], zeroed */,
+                uint32_t* __restrict__ q_flag /* [nq], zeroed */, uint32_t* __restrict__ n_flagged, Bm25Filter flt) {
+    extern __shared__ uint8_t bm25_smem_raw[];
+    SubSmem* sm = reinterpret_cast<SubSmem*>(bm25_smem_raw);
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* acc = sm->acc[w];
+    uint16_t* cand = sm->cand[w];
+    uint32_t* cand_count = &sm->cand_count[w];
+    const int nb0 = (n_blocks + stride - 1) / stride;
+    const int per_q = (n_blocks - nb0) * BM25_SUBS;            // phase-1 sub-blocks of one query
+    const long long n_items = (long long)nq * per_q;
+    const long long step = (long long)gridDim.x * SUB_WARPS;
+    const uint32_t cap = (uint32_t)n_blocks * (uint32_t)k;     // key slots of one query in `partial`
+
+    // Items of this warp: first, first + step, ... as (query, j-th phase-1 sub-block); stepping is an add with carry.
+    struct Item { int q, j; };
+    const int step_q = (int)(step / per_q), step_j = (int)(step % per_q);
+    auto advance = [&](Item x) {
+        x.j += step_j;
+        x.q += step_q;
+        if (x.j >= per_q) { x.j -= per_q; ++x.q; }
+        return x;
+    };
+    auto sub_of = [&](Item x) -> int {  // sub-block index, -1 past the end of the queries or of the documents
+        if (x.q >= nq) return -1;
+        const int jb = x.j / BM25_SUBS;
+        const int blk = jb + jb / (stride - 1) + 1;  // the jb-th block that is not in the sample
+        const int sub = blk * BM25_SUBS + (x.j - jb * BM25_SUBS);
+        return sub < n_sub ? sub : -1;
+    };
+    auto term_of = [&](Item x, int sub, int j0) -> int32_t {
+        if (sub < 0 || j0 + lane >= max_terms) return -1;
+        return __ldg(q_terms + (size_t)(q_offset + x.q) * max_terms + j0 + lane);
+    };
+    auto bounds_of = [&](int sub, int32_t t, int64_t& lo, uint32_t& n) {  // first posting and length of the slice
+        lo = 0;
+        n = 0;
+        if (sub >= 0 && t >= 0) {
+            const int64_t* bp = block_ptr + (size_t)t * (n_sub + 1) + sub;
+            lo = __ldg(bp);
+            n = (uint32_t)(__ldg(bp + 1) - lo);
+        }
+    };
+    auto flag_query = [&](int q) {
+        if (lane == 0 && atomicExch(&q_flag[q], 1u) == 0u) atomicAdd(n_flagged, 1u);
+    };
+
+    // Lookahead: slice bounds one and two items ahead (the second so that the item after next can be pulled into L2 a
+    // whole item early), term ids three ahead, so that no dependent load is ever waited for.
+    const long long first = (long long)blockIdx.x * SUB_WARPS + w;
+    Item x0{(int)(first / per_q), (int)(first % per_q)};
+    Item x1 = advance(x0), x2 = advance(x1), x3 = advance(x2);
+    int s0 = sub_of(x0), s1 = sub_of(x1), s2 = sub_of(x2), s3 = sub_of(x3);
+    int32_t t3 = term_of(x3, s3, 0);
+    int64_t lo, lo1, lo2;
+    uint32_t n0, n1, n2;
+    bounds_of(s0, term_of(x0, s0, 0), lo, n0);
+    bounds_of(s1, term_of(x1, s1, 0), lo1, n1);
+    bounds_of(s2, term_of(x2, s2, 0), lo2, n2);
+    float tau0 = s0 >= 0 ? __ldg(tau + (size_t)x0.q * k + (k - 1)) : 0.f;
+    float tau1 = s1 >= 0 ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
+
+    for (; x0.q < nq;) {
+        if (s0 >= 0) {
+            const int q = x0.q;
+            const int32_t doc_base = s0 * BM25_SUB_DOCS;
+            // tau = 0 (the sample matched fewer than k documents): every matched document is a candidate
+            const uint32_t cross_bits = tau0 > 0.f ? __float_as_uint(tau0) : 1u;
+            uint32_t f_mask = 0xFFFFFFFFu;
+            int32_t f_group = -1;
+            if constexpr (FILT) {
+                f_mask = flt.doc_tags ? __ldg(flt.q_tag_mask + q_offset + q) : 0xFFFFFFFFu;
+                f_group = flt.doc_group ? __ldg(flt.q_group + q_offset + q) : -1;
+            }
+            if (n1 > 0) {
+                // Pull the NEXT item's slices into L2 now (lane u: term u, one 128-byte line per request): its loads then
+                // see L2 latency instead of HBM latency, and nothing has to be held in registers meanwhile.
+                const char* pd = reinterpret_cast<const char*>(post_doc + lo1);
+                const char* pi = reinterpret_cast<const char*>(post_imp + lo1);
+                const int bytes = (int)n1 * 4 + (int)(reinterpret_cast<uintptr_t>(pd) & 127);
+                pd -= reinterpret_cast<uintptr_t>(pd) & 127;
+                pi -= reinterpret_cast<uintptr_t>(pi) & 127;
+                for (int o = 0; o < bytes; o += 128) {
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pd + o));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pi + o));
+                }
+            }
+            bool zeroed = false;
+            for (int j0 = 0; j0 < max_terms; j0 += 32) {
+                if (j0 > 0) bounds_of(s0, term_of(x0, s0, j0), lo, n0);  // queries with more than 32 terms: fetched in line
+                // Lane u plans term j0 + u: its slice rounded out to aligned groups of 4 postings (the arrays are padded)
+                // and cut into rounds of 128 postings = one 16-byte load per lane and array.
+                const uint32_t n_l = n0;
+                const uint32_t cnt = n_l == 0 ? 0u : (((uint32_t)lo & 3u) + n_l + 127u) >> 7;
+                uint32_t incl = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t v = __shfl_up_sync(FULL, incl, o);
+                    if (lane >= o) incl += v;
+                }
+                const uint32_t rounds = __shfl_sync(FULL, incl, 31);
+                if (rounds == 0) continue;
+                if (!zeroed) {
+                    float4* a4 = reinterpret_cast<float4*>(acc);
+#pragma unroll
+                    for (int i = 0; i < BM25_SUB_DOCS / 128; ++i) a4[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (lane == 0) *cand_count = 0;
+                    zeroed = true;
+                    __syncwarp();
+                }
+                // round r of the stream belongs to term u = the first lane whose inclusive round count exceeds r
+                const uint32_t excl = incl - cnt;
+                int4 d[SUB_DEPTH];
+                float4 wv[SUB_DEPTH];
+                uint32_t vm[SUB_DEPTH];  // which of the lane's 4 postings belong to the slice
+                auto load_round = [&](uint32_t r, int4& dd, float4& ww, uint32_t& mask) {
+                    const int u = __popc(__ballot_sync(FULL, incl <= r));
+                    const int64_t lo_u = __shfl_sync(FULL, lo, u);
+                    const uint32_t n_u = __shfl_sync(FULL, n_l, u);
+                    const uint32_t off_u = (uint32_t)lo_u & 3u;  // the slice starts at this element of its first group
+                    const int32_t pos = (int32_t)(((r - __shfl_sync(FULL, excl, u)) << 7) + 4u * (uint32_t)lane);
+                    // elements pos .. pos+3 of the rounded-out slice; the slice proper is [off_u, off_u + n_u)
+                    const int32_t skip = (int32_t)off_u - pos;                // > 0 only in the first group
+                    const int32_t keep = (int32_t)(off_u + n_u) - pos;        // elements up to the slice's end
+                    mask = keep <= 0 ? 0u : (0xFu >> (keep >= 4 ? 0 : 4 - keep));
+                    if (skip > 0) mask &= 0xFu << skip;
+                    dd = make_int4(0, 0, 0, 0);
+                    ww = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (mask) {
+                        const int64_t p = (lo_u & ~(int64_t)3) + pos;
+                        dd = ldg_stream_s32x4(post_doc + p);
+                        ww = ldg_stream_f32x4(post_imp + p);
+                    }
+                };
+#pragma unroll
+                for (int s_ = 0; s_ < SUB_DEPTH; ++s_) {
+                    vm[s_] = 0;
+                    d[s_] = make_int4(0, 0, 0, 0);
+                    wv[s_] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if ((uint32_t)s_ < rounds) load_round((uint32_t)s_, d[s_], wv[s_], vm[s_]);
+                }
+                for (uint32_t r0 = 0; r0 < rounds; r0 += SUB_DEPTH) {
+#pragma unroll
+                    for (int s_ = 0; s_ < SUB_DEPTH; ++s_) {
+                        if (r0 + s_ < rounds) {  // warp-uniform
+                            const uint32_t mask = vm[s_];
+                            const int4 dd = d[s_];
+                            const float4 ww = wv[s_];
+                            // refill the stage first: the loads must be in flight while this round is applied
+                            if (r0 + s_ + SUB_DEPTH < rounds) load_round(r0 + s_ + SUB_DEPTH, d[s_], wv[s_], vm[s_]);
+                            if (mask) {
+                                const bool m0 = mask & 1u, m1 = mask & 2u, m2 = mask & 4u, m3 = mask & 8u;
+                                const int r0_ = m0 ? dd.x - doc_base : 0, r1_ = m1 ? dd.y - doc_base : 0;
+                                const int r2_ = m2 ? dd.z - doc_base : 0, r3_ = m3 ? dd.w - doc_base : 0;
+                                // the four reads are issued together, then the adds, then the writes
+                                const float a0 = acc[r0_], a1 = acc[r1_], a2 = acc[r2_], a3 = acc[r3_];
+                                const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y);
+                                const float n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
+                                if (m0) acc[r0_] = n0;
+                                if (m1) acc[r1_] = n1;
+                                if (m2) acc[r2_] = n2;
+                                if (m3) acc[r3_] = n3;
+                                // Impacts are > 0: an accumulator only grows and crosses tau at most once. Cheap test first
+                                // (some new value reaches tau; elements outside the slice may raise a false alarm).
+                                if (__float_as_uint(fmaxf(fmaxf(n0, n1), fmaxf(n2, n3))) >= cross_bits) {
+                                    const int rr[4] = {r0_, r1_, r2_, r3_};
+                                    const bool cc[4] = {
+                                        m0 && __float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits,
+                                        m1 && __float_as_uint(n1) >= cross_bits && __float_as_uint(a1) < cross_bits,
+                                        m2 && __float_as_uint(n2) >= cross_bits && __float_as_uint(a2) < cross_bits,
+                                        m3 && __float_as_uint(n3) >= cross_bits && __float_as_uint(a3) < cross_bits};
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        if (!cc[e]) continue;
+                                        bool ok = true;
+                                        if constexpr (FILT) {
+                                            const int32_t doc = doc_base + rr[e];
+                                            if (flt.doc_tags && (__ldg(flt.doc_tags + doc) & f_mask) == 0) ok = false;
+                                            if (f_group >= 0 && __ldg(flt.doc_group + doc) != f_group) ok = false;
+                                        }
+                                        if (ok) {
+                                            const uint32_t c = atomicAdd(cand_count, 1u);
+                                            if (c < (uint32_t)SUB_CAND) cand[c] = (uint16_t)rr[e];
+                                        }
+                                    }
+                                }
+                            }
+                            __syncwarp();  // the next round may belong to the next term and hit the same documents
+                        }
+                    }
+                }
+            }
+            if (zeroed) {
+                __syncwarp();
+                const uint32_t nc = *cand_count;
+                if (nc > (uint32_t)SUB_CAND) {
+                    flag_query(q);
+                } else if (nc > 0) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&q_count[q], nc);
+                    base = __shfl_sync(FULL, base, 0) + (uint32_t)k;  // slots 0..k-1: the sample's top-k
+                    if (base + nc > cap) {
+                        flag_query(q);
+                    } else {
+                        uint64_t* out = partial + (size_t)q * cap + base;
+                        for (uint32_t i = lane; i < nc; i += 32) {
+                            const uint32_t rel = cand[i];
+                            out[i] = srag_pack_key(__float_as_uint(acc[rel]), (uint32_t)doc_base + rel);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        // rotate the lookahead
+        x0 = x1;
+        x1 = x2;
+        x2 = x3;
+        x3 = advance(x3);
+        s0 = s1;
+        s1 = s2;
+        s2 = s3;
+        s3 = sub_of(x3);
+        lo = lo1;
+        n0 = n1;
+        lo1 = lo2;
+        n1 = n2;
+        tau0 = tau1;
+        bounds_of(s2, t3, lo2, n2);
+        tau1 = s1 >= 0 ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
+        t3 = term_of(x3, s3, 0);
+    }
+}
+
+// Flagged queries are redone by bm25_items_kernel into per-block lists: clear everything but the sample's top-k.
+__global__ void bm25_clear_flagged_kernel(uint64_t* __restrict__ partial, int k, uint32_t cap, const uint32_t* __restrict__ q_flag,
+                                          const uint32_t* __restrict__ n_flagged) {
+    if (*n_flagged == 0 || q_flag[blockIdx.x] == 0) return;
+    uint64_t* p = partial + (size_t)blockIdx.x * cap;
+    for (uint32_t i = (uint32_t)k + threadIdx.x; i < cap; i += blockDim.x) p[i] = SRAG_KEY_EMPTY;
+}
+
 // imp = idf[t] * (tf * (k1 + 1)) / (tf + k1 * ((1 - b) + b * (dl / avgdl))), one rounding per op
 __global__ void bm25_impacts_kernel(const int64_t* __restrict__ term_ptr, int vocab,
                                     const int32_t* __restrict__ post_doc, const int32_t* __restrict__ post_tf,
@@ -741,34 +1041,34 @@ __global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, co
     }
 }
 
-// Bank order (index build). Inside a (term, block) slice every posting is a distinct document and receives exactly
+// Bank order (index build). Inside a (term, sub-block) slice every posting is a distinct document and receives exactly
 // one add per query, so the ORDER of a slice's postings is free: sums, and therefore scores, do not depend on it.
-// The consumers of bm25_items_kernel read-add-write acc[doc - doc_base] with lane l of a warp holding postings
-// 4l .. 4l+3 of the warp's aligned group of 128, i.e. one shared-memory access covers the 32 postings at positions
-// 128g + 4l + e (fixed g, e). With postings in ascending document order their banks (doc & 31) are as good as random:
-// 3.4 wavefronts per access. This kernel permutes each slice so that those 32 postings fall on distinct banks
-// wherever the slice allows it: the postings are laid out "round-robin over banks" (all first-of-their-bank
-// postings in bank order, then all second ones, ...; a window of 32 consecutive entries of full rounds hits every
-// bank once) and that sequence is written to the slice's positions in ACCESS order (g, e, l). The floor is
-// max_b count(b) wavefronts per slice; simulation: 3.4 -> 1.6 wavefronts per access for slices of ~800 postings,
-// -> 1.2 for ~5000. One warp per slice, deterministic (stable inside a bank).
+// Both scoring kernels read-add-write acc[doc - doc_base] with lane l holding postings 4l .. 4l+3 of an aligned group of
+// 128 (aligned relative to lo & ~3), i.e. one shared-memory access covers the 32 postings at positions 128g + 4l + e
+// (fixed g, e). With postings in ascending document order their banks (doc & 31) are as good as random: ~3.4
+// wavefronts per access. This kernel permutes each slice so that those 32 postings fall on distinct banks wherever the
+// slice allows it: the postings are laid out "round-robin over banks" (all first-of-their-bank postings in bank order,
+// then all second ones, ...; a window of 32 consecutive entries of full rounds hits every bank once) and that sequence
+// is written to the slice's positions in ACCESS order (g, e, l). The floor is max_b count(b) wavefronts per slice;
+// simulation: 3.2 -> 2.1 wavefronts per access for slices of 100 postings, 3.4 -> 1.6 for 800.
+// One warp per slice, deterministic (stable inside a bank).
 constexpr int BANK_ORDER_WARPS = 8;
 __global__ void __launch_bounds__(32 * BANK_ORDER_WARPS)
-bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_blocks,
+bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_sub,
                        const int32_t* __restrict__ doc_in, const float* __restrict__ imp_in,
                        int32_t* __restrict__ doc_out, float* __restrict__ imp_out) {
     __shared__ uint32_t cnt_s[BANK_ORDER_WARPS][32];
     constexpr uint32_t FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     uint32_t* cnt = cnt_s[w];
-    const int64_t n_slices = (int64_t)vocab * n_blocks;
+    const int64_t n_slices = (int64_t)vocab * n_sub;
     const int64_t n_warps = (int64_t)gridDim.x * BANK_ORDER_WARPS;
     for (int64_t s0 = ((int64_t)blockIdx.x * BANK_ORDER_WARPS + w) * 32; s0 < n_slices; s0 += n_warps * 32) {
         // the bounds of 32 consecutive slices, one per lane
         int64_t lo_l = 0, hi_l = 0;
         if (s0 + lane < n_slices) {
-            const int64_t t = (s0 + lane) / n_blocks, j = (s0 + lane) - t * n_blocks;
-            const int64_t* bp = block_ptr + t * (n_blocks + 1) + j;
+            const int64_t t = (s0 + lane) / n_sub, j = (s0 + lane) - t * n_sub;
+            const int64_t* bp = block_ptr + t * (n_sub + 1) + j;
             lo_l = __ldg(bp);
             hi_l = __ldg(bp + 1);
         }
@@ -778,7 +1078,7 @@ bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_b
             todo &= todo - 1;
             const int64_t lo = __shfl_sync(FULL, lo_l, src), hi = __shfl_sync(FULL, hi_l, src);
             const int n = (int)(hi - lo);
-            const int64_t a = lo & ~(int64_t)3;                // the consumers' groups of 4 / 128 are aligned to this
+            const int64_t a = lo & ~(int64_t)3;  // the scoring kernels' groups of 4 / 128 postings are aligned to this
             const int lo_off = (int)(lo - a), hi_off = lo_off + n;
             // pass 1: postings per bank (lane b ends up holding the count of bank b)
             cnt[lane] = 0;
@@ -810,9 +1110,9 @@ bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_b
                     sidx += (cb < r ? cb : r) + (((uint32_t)bb < b && cb > r) ? 1u : 0u);
                 }
                 if (valid) {
-                    // the sidx-th position of the slice in access order (group g, element e, lane l)
+                    // the sidx-th position of the slice in access order (group g of 128, element e, lane l)
                     const int g = ((int)sidx + lo_off) >> 7;
-                    int k = (int)sidx - (g ? 128 * g - lo_off : 0);
+                    int kk = (int)sidx - (g ? 128 * g - lo_off : 0);
                     const int sg = g ? 0 : lo_off;
                     const int tg = hi_off - 128 * g < 128 ? hi_off - 128 * g : 128;
                     int pos = -1;
@@ -821,8 +1121,8 @@ bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_b
                         const int l0 = (sg - e + 3) >> 2, l1 = (tg - e + 3) >> 2;
                         const int ne = l1 > l0 ? l1 - l0 : 0;
                         if (pos < 0) {
-                            if (k < ne) pos = 128 * g + 4 * (l0 + k) + e;
-                            else k -= ne;
+                            if (kk < ne) pos = 128 * g + 4 * (l0 + kk) + e;
+                            else kk -= ne;
                         }
                     }
                     doc_out[a + pos] = d;
@@ -834,12 +1134,13 @@ bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_b
     }
 }
 
-int bm25_blocks(int64_t n_docs) { return (int)((n_docs + BM25_BLOCK_DOCS - 1) / BM25_BLOCK_DOCS); }
+int bm25_blocks(int64_t n_docs) { return (int)((n_docs + BM25_BLOCK_DOCS - 1) / BM25_BLOCK_DOCS); }  // tiles
+int bm25_subs(int64_t n_docs) { return (int)((n_docs + BM25_SUB_DOCS - 1) / BM25_SUB_DOCS); }       // index granularity
 constexpr int BM25_Q_CHUNK = 1024;  // queries whose per-block lists are resident at once (0.5 GB at 10 M docs, k = 100)
 
 }  // namespace
 
-extern "C" int srag_bm25_block_docs(void) { return BM25_BLOCK_DOCS; }
+extern "C" int srag_bm25_block_docs(void) { return BM25_SUB_DOCS; }
 
 extern "C" int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32_t* post_doc, const int32_t* post_tf,
                                  int64_t nnz, const float* idf, const int32_t* dl, float avgdl, float* post_imp,
@@ -858,10 +1159,10 @@ extern "C" int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32
 
 extern "C" int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* post_doc, int vocab, int64_t n_docs,
                                      int block_docs, int64_t* block_ptr, void* stream) {
-    SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF && block_docs == BM25_BLOCK_DOCS,
+    SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF && block_docs == BM25_SUB_DOCS,
                    "bad sizes vocab=%d n_docs=%lld block_docs=%d", vocab, (long long)n_docs, block_docs);
     SRAG_CHECK_ARG(term_ptr && block_ptr, "null pointer argument");
-    const int nb = bm25_blocks(n_docs);
+    const int nb = bm25_subs(n_docs) > 0 ? bm25_subs(n_docs) : 1;
     int64_t total = (int64_t)vocab * (nb + 1);
     int64_t blocks = (total + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
@@ -878,7 +1179,7 @@ extern "C" int srag_bm25_bank_order(const int64_t* block_ptr, int vocab, int64_t
     if (n_docs == 0) return SRAG_OK;
     SRAG_CHECK_ARG(block_ptr && doc_in && imp_in && doc_out && imp_out, "null pointer argument");
     SRAG_CHECK_ARG(doc_in != doc_out && imp_in != imp_out, "the permutation is not in place");
-    const int nb = bm25_blocks(n_docs);
+    const int nb = bm25_subs(n_docs);
     const int64_t rounds = ((int64_t)vocab * nb + 32 * BANK_ORDER_WARPS - 1) / (32 * BANK_ORDER_WARPS);
     const int64_t blocks = rounds < 148 * 64 ? rounds : 148 * 64;
     bm25_bank_order_kernel<<<(int)blocks, 32 * BANK_ORDER_WARPS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
@@ -904,12 +1205,14 @@ static size_t bm25_sample_bytes(int qc, int nb, int k) {
     return stride > 1 ? bm25_partial_bytes(qc, (nb + stride - 1) / stride, k) : 0;
 }
 static size_t bm25_tau_bytes(int qc, int k) { return (((size_t)qc * k * (sizeof(float) + sizeof(int64_t))) + 255) & ~(size_t)255; }
+// bm25_sub_kernel: candidate counter and overflow flag per query + the number of flagged queries
+static size_t bm25_ctr_bytes(int qc) { return (((size_t)(2 * qc + 1) * sizeof(uint32_t)) + 255) & ~(size_t)255; }
 
 extern "C" int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes) {
     SRAG_CHECK_ARG(bytes && n_queries >= 1 && k >= 1 && k <= SRAG_MAX_BM25_K && n_docs >= 0, "bad sizes");
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
-    *bytes = bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) + bm25_tau_bytes(qc, k) + 256;
+    *bytes = bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) + bm25_tau_bytes(qc, k) + bm25_ctr_bytes(qc) + 256;
     return SRAG_OK;
 }
 
@@ -931,7 +1234,8 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
-    const size_t need = bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) + bm25_tau_bytes(qc, k);
+    const int n_sub = bm25_subs(n_docs) > 0 ? bm25_subs(n_docs) : 1;
+    const size_t need = bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) + bm25_tau_bytes(qc, k) + bm25_ctr_bytes(qc);
     if (workspace_bytes < need) {
         srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
         return SRAG_E_WORKSPACE;
@@ -943,6 +1247,10 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
                                        (int)sizeof(Bm25Smem)));
         SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)sizeof(Bm25Smem)));
+        SRAG_CUDA(cudaFuncSetAttribute(bm25_sub_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(SubSmem)));
+        SRAG_CUDA(cudaFuncSetAttribute(bm25_sub_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(SubSmem)));
         int dev = 0;
         SRAG_CUDA(cudaGetDevice(&dev));
         SRAG_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
@@ -953,6 +1261,15 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
     uint64_t* sample = reinterpret_cast<uint64_t*>(ws + bm25_partial_bytes(qc, nb, k));
     float* tau_scores = reinterpret_cast<float*>(ws + bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k));
     int64_t* tau_ids = reinterpret_cast<int64_t*>(tau_scores + (size_t)qc * k);
+    uint32_t* q_count = reinterpret_cast<uint32_t*>(ws + bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) +
+                                                    bm25_tau_bytes(qc, k));
+    uint32_t* q_flag = q_count + qc;
+    uint32_t* n_flagged = q_flag + qc;
+    static int use_sub = -1;  // SRAG_BM25_SUBKERNEL=0: phase 1 on bm25_items_kernel alone (A/B measurements)
+    if (use_sub < 0) {
+        const char* e = getenv("SRAG_BM25_SUBKERNEL");
+        use_sub = e ? atoi(e) != 0 : 1;
+    }
     const int stride = bm25_stride(nb);
     const int nb0 = (nb + stride - 1) / stride;
     const char* dbg_env = getenv("SRAG_BM25_DEBUG");
@@ -966,9 +1283,10 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
             auto kern = filtered ? bm25_items_kernel<true> : bm25_items_kernel<false>;
-            kern<<<grid0, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, q_terms, max_terms, k,
-                                                                    q0, nq, 0, stride, nullptr,
-                                                                    stride > 1 ? sample : partial, dbg, flt, n_docs);
+            kern<<<grid0, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms,
+                                                                    k, q0, nq, 0, stride, nullptr,
+                                                                    stride > 1 ? sample : partial, dbg, flt, n_docs, nullptr,
+                                                                    nullptr);
             SRAG_CUDA(cudaGetLastError());
             if (stride > 1) {
                 // top-k of the sample: scores give tau; the keys seed the final merge in block 0's slot of
@@ -978,9 +1296,24 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
                 if (rc) return rc;
                 const long long items1 = (long long)nq * (nb - nb0);
                 const int grid1 = (int)(items1 < resident ? items1 : resident);
-                kern<<<grid1, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, q_terms, max_terms,
-                                                                        k, q0, nq, 1, stride, tau_scores, partial, dbg, flt,
-                                                                        n_docs);
+                if (use_sub) {
+                    // every (query, sub-block) on its own warp; queries whose candidates overflow are flagged, their
+                    // region cleared and redone below with the exact per-block selection
+                    SRAG_CUDA(cudaMemsetAsync(q_count, 0, bm25_ctr_bytes(qc), st));
+                    const long long witems = items1 * BM25_SUBS;
+                    const long long wg = (witems + SUB_WARPS - 1) / SUB_WARPS;
+                    auto skern = filtered ? bm25_sub_kernel<true> : bm25_sub_kernel<false>;
+                    skern<<<(int)(wg < sm_count ? wg : sm_count), 32 * SUB_WARPS, sizeof(SubSmem), st>>>(
+                        block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms, k, q0, nq, stride, tau_scores, partial,
+                        q_count, q_flag, n_flagged, flt);
+                    SRAG_CUDA(cudaGetLastError());
+                    bm25_clear_flagged_kernel<<<nq, 256, 0, st>>>(partial, k, (uint32_t)nb * (uint32_t)k, q_flag, n_flagged);
+                    SRAG_CUDA(cudaGetLastError());
+                }
+                kern<<<grid1, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, n_sub, q_terms,
+                                                                        max_terms, k, q0, nq, 1, stride, tau_scores, partial,
+                                                                        dbg, flt, n_docs, use_sub ? q_flag : nullptr,
+                                                                        use_sub ? n_flagged : nullptr);
                 SRAG_CUDA(cudaGetLastError());
             }
         }

