@@ -1197,8 +1197,10 @@ static int bm25_stride(int nb) {
         const char* e = getenv("SRAG_BM25_STRIDE");
         forced = e ? atoi(e) : 0;
     }
-    const int stride = forced >= 2 ? forced : 16;
-    return nb >= 2 * stride ? stride : 1;
+    if (forced >= 2) return nb >= 2 * forced ? forced : 1;
+    // every 32nd block when there are plenty (C3: 12.12 ms at 16, 11.64 at 32, 12.06 at 64: the sample costs an exact
+    // selection per block, a lower tau costs candidates), every 16th for mid-sized indexes, no sample below 32 blocks
+    return nb >= 64 ? 32 : nb >= 32 ? 16 : 1;
 }
 static size_t bm25_sample_bytes(int qc, int nb, int k) {
     const int stride = bm25_stride(nb);
