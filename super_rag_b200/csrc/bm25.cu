@@ -1279,8 +1279,15 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
     const int resident = sm_count * BM25_CTAS_PER_SM;
     for (int q0 = 0; q0 < n_queries; q0 += qc) {
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
-        // the memset covers the sample lists too (they follow `partial` in the workspace)
-        SRAG_CUDA(cudaMemsetAsync(partial, 0, bm25_partial_bytes(qc, nb, k) + (stride > 1 ? (size_t)nq * nb0 * k * sizeof(uint64_t) : 0), st));
+        const bool sub_path = use_sub && stride > 1 && n_docs > 0;
+        if (sub_path) {
+            // candidate regions are filled from the front and read up to their fill level: only the sample lists
+            // (they follow `partial` in the workspace) must start out empty
+            SRAG_CUDA(cudaMemsetAsync(sample, 0, (size_t)nq * nb0 * k * sizeof(uint64_t), st));
+        } else {
+            // the memset covers the sample lists too
+            SRAG_CUDA(cudaMemsetAsync(partial, 0, bm25_partial_bytes(qc, nb, k) + (stride > 1 ? (size_t)nq * nb0 * k * sizeof(uint64_t) : 0), st));
+        }
         if (n_docs > 0) {
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
@@ -1319,8 +1326,11 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
                 SRAG_CUDA(cudaGetLastError());
             }
         }
-        int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, id_base, out_scores + (size_t)q0 * k,
-                                      out_ids + (size_t)q0 * k, st);
+        int rc = sub_path ? srag_launch_finalize_live(partial, (size_t)nb * k, nq, nb * k, k, nullptr, id_base,
+                                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, nullptr, 0,
+                                                      q_count, q_flag, k, st)
+                          : srag_launch_finalize(partial, nq, nb * k, k, nullptr, id_base, out_scores + (size_t)q0 * k,
+                                                 out_ids + (size_t)q0 * k, st);
         if (rc) return rc;
     }
     return SRAG_OK;

@@ -22,6 +22,12 @@ int srag_launch_finalize_ex(const uint64_t* partial, size_t src_stride, int n_qu
                             const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
                             uint64_t* out_keys, size_t out_keys_stride, cudaStream_t st);
 
+// same for regions filled from the front: query q holds live_base + live_count[q] keys (all `total` if live_all[q])
+int srag_launch_finalize_live(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                              const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                              uint64_t* out_keys, size_t out_keys_stride, const uint32_t* live_count,
+                              const uint32_t* live_all, int live_base, cudaStream_t st);
+
 #define SRAG_CHECK_ARG(cond, ...)                 \
     do {                                          \
         if (!(cond)) {                            \

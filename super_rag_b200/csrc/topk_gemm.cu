@@ -583,16 +583,24 @@ __device__ void block_bitonic_desc(uint64_t* a, int P) {
 }
 
 __global__ void __launch_bounds__(FIN_THREADS)
-topk_finalize_kernel(const uint64_t* __restrict__ partial, size_t src_stride, int total /* lists * k */, int k, int kcap,
+topk_finalize_kernel(const uint64_t* __restrict__ partial, size_t src_stride, int total_max /* lists * k */, int k, int kcap,
                      int P, const float* __restrict__ q_scale, int64_t id_base, float* __restrict__ out_scores,
-                     int64_t* __restrict__ out_ids, uint64_t* __restrict__ out_keys, size_t out_keys_stride) {
+                     int64_t* __restrict__ out_ids, uint64_t* __restrict__ out_keys, size_t out_keys_stride,
+                     const uint32_t* __restrict__ live_count, const uint32_t* __restrict__ live_all, int live_base) {
     extern __shared__ uint64_t fin_keys[];
     __shared__ int fin_count;
     const int q = blockIdx.x;
     const uint64_t* src = partial + (size_t)q * src_stride;
     const int chunk = P - kcap;
     bool sorted = false;
-    if (total > chunk) {
+    // K2's candidate regions are filled from the front: only the first live_base + live_count[q] keys of a query exist
+    // (nothing beyond them was ever written), unless the query was redone into per-block lists (live_all[q]).
+    int total = total_max;
+    if (live_count && !live_all[q]) {
+        const long long t = (long long)live_base + live_count[q];
+        total = t < total_max ? (int)t : total_max;
+    }
+    if (total > chunk || live_count) {
         // Sparse lists (K2 with a sample threshold leaves most block lists empty): compact the non-empty keys
         // in ONE pass; when they all fit, sort one small power of two instead of total/chunk passes.
         for (int i = threadIdx.x; i < P; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
@@ -1000,9 +1008,10 @@ extern "C" int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int*
 }
 
 // Shared with K2 (bm25.cu): per-query lists of sortable keys -> sorted top-k (score, id).
-int srag_launch_finalize_ex(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
-                            const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
-                            uint64_t* out_keys, size_t out_keys_stride, cudaStream_t st) {
+int srag_launch_finalize_live(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                              const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                              uint64_t* out_keys, size_t out_keys_stride, const uint32_t* live_count,
+                              const uint32_t* live_all, int live_base, cudaStream_t st) {
     const int kcap = (k <= 128) ? 128 : 256;
     int P = 2 * kcap;
     while (P < total + kcap && P < FIN_MAX_P) P <<= 1;
@@ -1013,9 +1022,17 @@ int srag_launch_finalize_ex(const uint64_t* partial, size_t src_stride, int n_qu
         fin_attr = true;
     }
     topk_finalize_kernel<<<n_queries, FIN_THREADS, (size_t)P * sizeof(uint64_t), st>>>(
-        partial, src_stride, total, k, kcap, P, q_scale, id_base, out_scores, out_ids, out_keys, out_keys_stride);
+        partial, src_stride, total, k, kcap, P, q_scale, id_base, out_scores, out_ids, out_keys, out_keys_stride, live_count,
+        live_all, live_base);
     SRAG_CUDA(cudaGetLastError());
     return SRAG_OK;
+}
+
+int srag_launch_finalize_ex(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                            const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                            uint64_t* out_keys, size_t out_keys_stride, cudaStream_t st) {
+    return srag_launch_finalize_live(partial, src_stride, n_queries, total, k, q_scale, id_base, out_scores, out_ids, out_keys,
+                                     out_keys_stride, nullptr, nullptr, 0, st);
 }
 
 int srag_launch_finalize(const uint64_t* partial, int n_queries, int total, int k, const float* q_scale,
