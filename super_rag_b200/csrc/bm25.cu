@@ -1,17 +1,22 @@
 // K2: BM25 scoring over CSR postings. HBM-bound integer/float streaming work — no tensor cores.
 //
-//   bm25_items_kernel  persistent CTAs (2 per SM) walk work items = (query, block of BM25_BLOCK_DOCS
-//                      consecutive documents). The block's fp32 accumulators live in shared memory.
-//                      Query terms are applied in ASCENDING term id; inside a term every posting hits a
-//                      distinct document, so plain (non-atomic) read-add-write is race-free and the
-//                      per-document sum order is fixed -> bit-exact with oracle/bm25.py.
-//                      Two producer warps look the posting slices up and stream them through a packed
-//                      shared-memory ring with 1-D bulk copies; eight consumer warps follow the chunk
-//                      descriptors, accumulate, and select (details at the kernel).
-//                      Selection is two-phase: a sample of the blocks gets an exact block top-k, its
-//                      k-th best score tau bounds the query's global k-th score from below, and the other
-//                      blocks only record the documents whose accumulator crosses tau.
-//   srag_launch_finalize(_ex) (topk_gemm.cu) merges the per-block lists of a query.
+// Postings are CSR by term; block_ptr gives the first posting of every (term, BM25_SUB_DOCS = 2048 documents) slice.
+// Query terms are applied in ASCENDING term id; inside a term every posting hits a distinct document, so plain
+// (non-atomic) read-add-write is race-free and the per-document sum order is fixed -> bit-exact with oracle/bm25.py.
+// Selection is two-phase: a sample of the 16384-document blocks (every 32nd / 16th) gets an exact block top-k, its
+// k-th best score tau bounds the query's global k-th score from below, and the rest of the documents only report the
+// accumulators that cross tau.
+//
+//   bm25_items_kernel  sample phase (and: indexes too small to sample, queries flagged by bm25_sub_kernel). Persistent
+//                      CTAs (2 per SM) walk (query, 16384-document block) items; the block's fp32 accumulators live in
+//                      64 KB of shared memory; two producer warps stream the posting slices through a packed
+//                      shared-memory ring with 1-D bulk copies, eight consumer warps accumulate and select exactly.
+//   bm25_sub_kernel    phase 1, the bulk of the bytes: one WARP per (query, 2048-document sub-block), 8 KB of private
+//                      accumulators, no CTA barrier, no producer; documents crossing tau are appended to the query's
+//                      candidate region. Overflowing queries are flagged and redone by bm25_items_kernel.
+//   bm25_bank_order_kernel  index build: permutes every slice so that the accumulator accesses of a warp fall on
+//                      distinct shared-memory banks (scores unchanged: the order inside a slice is free).
+//   srag_launch_finalize(_ex/_live) (topk_gemm.cu) merges the lists / candidate region of a query.
 //
 // Algorithmic bytes per query = 8 * sum_t df(t)  (int32 doc + fp32 impact per posting).
 // The reference has no BM25 arithmetic; contract: oracle/bm25.py docstring.

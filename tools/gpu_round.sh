@@ -20,9 +20,13 @@ ncu --set full --clock-control none --import-source on -k regex:topk_gemm_kernel
     -o gpurun_out/prof_topk $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out
-# C3 / C4 lines and a full capture of the BM25 phase-1 kernel
+# C3 / C4 lines, the K2 launch list and a full capture of the BM25 phase-1 kernel (bm25_sub_kernel)
 timeout 600 python tools/bench_hybrid.py --docs 10000000 --check 4 > gpurun_out/c3_c4.jsonl 2> gpurun_out/c3_c4.err; cat gpurun_out/c3_c4.jsonl | cut -c1-600
 CMD2="python tools/bench_hybrid.py --docs 4000000 --skip-c4 --check 0 --steps 1 --warmup 0"
 $CMD2 > gpurun_out/plain3.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:bm25_items -s 1 -c 1 -f -o gpurun_out/prof_bm25 $CMD2 > gpurun_out/ncu_bm25.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:bm25_sub_kernel -s 0 -c 1 -f -o gpurun_out/prof_bm25 $CMD2 > gpurun_out/ncu_bm25.log 2>&1
 echo "ncu bm25 rc=$?"
+CMD3="python tools/bench_hybrid.py --docs 10000000 --skip-c4 --check 0 --steps 2 --warmup 1"
+$CMD3 > gpurun_out/plain4.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'bm25|finalize' -c 40 --csv --log-file gpurun_out/c3_launches.csv $CMD3 > gpurun_out/ncu_c3_launches.log 2>&1
+echo "ncu c3 launches rc=$?"
