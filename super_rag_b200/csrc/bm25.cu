@@ -736,6 +736,11 @@ constexpr int SUB_CAND = 64;
 #define SRAG_BM25_SUB_DEPTH 2
 #endif
 constexpr int SUB_DEPTH = SRAG_BM25_SUB_DEPTH;  // rounds (of 128 postings) in flight per warp
+#ifndef SRAG_BM25_SUB_NARROW
+#define SRAG_BM25_SUB_NARROW 32
+#endif
+constexpr uint32_t SUB_NARROW = SRAG_BM25_SUB_NARROW;  // slices up to this long: one posting per lane (0 = never)
+constexpr uint32_t SUB_NARROW_BIT = 0x10u;
 
 struct SubSmem {
     float acc[SUB_WARPS][BM25_SUB_DOCS];
@@ -743,6 +748,16 @@ struct SubSmem {
     uint32_t cand_count[SUB_WARPS];
 };
 
+__device__ __forceinline__ int32_t ldg_stream_s32(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ldg_stream_f32(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
 __device__ __forceinline__ int4 ldg_stream_s32x4(const int32_t* p) {
     int4 v;
     asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
@@ -855,7 +870,9 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                 // Lane u plans term j0 + u: its slice rounded out to aligned groups of 4 postings (the arrays are padded)
                 // and cut into rounds of 128 postings = one 16-byte load per lane and array.
                 const uint32_t n_l = n0;
-                const uint32_t cnt = n_l == 0 ? 0u : (((uint32_t)lo & 3u) + n_l + 127u) >> 7;
+                // a slice of up to SUB_NARROW postings is one NARROW round (one posting per lane), a longer one is cut into
+                // wide rounds of 128 (an aligned group of 4 per lane)
+                const uint32_t cnt = n_l == 0 ? 0u : n_l <= SUB_NARROW ? 1u : (((uint32_t)lo & 3u) + n_l + 127u) >> 7;
                 uint32_t incl = cnt;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -881,6 +898,16 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                     const int u = __popc(__ballot_sync(FULL, incl <= r));
                     const int64_t lo_u = __shfl_sync(FULL, lo, u);
                     const uint32_t n_u = __shfl_sync(FULL, n_l, u);
+                    dd = make_int4(0, 0, 0, 0);
+                    ww = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (n_u <= SUB_NARROW) {  // warp-uniform
+                        mask = SUB_NARROW_BIT | ((uint32_t)lane < n_u ? 1u : 0u);
+                        if ((uint32_t)lane < n_u) {
+                            dd.x = ldg_stream_s32(post_doc + lo_u + lane);
+                            ww.x = ldg_stream_f32(post_imp + lo_u + lane);
+                        }
+                        return;
+                    }
                     const uint32_t off_u = (uint32_t)lo_u & 3u;  // the slice starts at this element of its first group
                     const int32_t pos = (int32_t)(((r - __shfl_sync(FULL, excl, u)) << 7) + 4u * (uint32_t)lane);
                     // elements pos .. pos+3 of the rounded-out slice; the slice proper is [off_u, off_u + n_u)
@@ -888,8 +915,6 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                     const int32_t keep = (int32_t)(off_u + n_u) - pos;        // elements up to the slice's end
                     mask = keep <= 0 ? 0u : (0xFu >> (keep >= 4 ? 0 : 4 - keep));
                     if (skip > 0) mask &= 0xFu << skip;
-                    dd = make_int4(0, 0, 0, 0);
-                    ww = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (mask) {
                         const int64_t p = (lo_u & ~(int64_t)3) + pos;
                         dd = ldg_stream_s32x4(post_doc + p);
@@ -912,7 +937,25 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                             const float4 ww = wv[s_];
                             // refill the stage first: the loads must be in flight while this round is applied
                             if (r0 + s_ + SUB_DEPTH < rounds) load_round(r0 + s_ + SUB_DEPTH, d[s_], wv[s_], vm[s_]);
-                            if (mask) {
+                            if (mask & SUB_NARROW_BIT) {  // warp-uniform: one posting per lane
+                                if (mask & 1u) {
+                                    const int rel = dd.x - doc_base;
+                                    const float a0 = acc[rel];
+                                    const float n0 = __fadd_rn(a0, ww.x);
+                                    acc[rel] = n0;
+                                    if (__float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits) {
+                                        bool ok = true;
+                                        if constexpr (FILT) {
+                                            if (flt.doc_tags && (__ldg(flt.doc_tags + dd.x) & f_mask) == 0) ok = false;
+                                            if (f_group >= 0 && __ldg(flt.doc_group + dd.x) != f_group) ok = false;
+                                        }
+                                        if (ok) {
+                                            const uint32_t c = atomicAdd(cand_count, 1u);
+                                            if (c < (uint32_t)SUB_CAND) cand[c] = (uint16_t)rel;
+                                        }
+                                    }
+                                }
+                            } else if (mask) {
                                 const bool m0 = mask & 1u, m1 = mask & 2u, m2 = mask & 4u, m3 = mask & 8u;
                                 const int r0_ = m0 ? dd.x - doc_base : 0, r1_ = m1 ? dd.y - doc_base : 0;
                                 const int r2_ = m2 ? dd.z - doc_base : 0, r3_ = m3 ? dd.w - doc_base : 0;
