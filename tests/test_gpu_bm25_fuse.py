@@ -246,3 +246,35 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
     # deterministic: a second build gives the same layout
     again = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
     assert torch.equal(again.post_doc, idx.post_doc) and torch.equal(again.post_imp.view(torch.int32), idx.post_imp.view(torch.int32))
+
+
+def test_bm25_sub_kernel_candidate_paths_and_fallback():
+    """Phase 1 runs one warp per (query, 2048-document sub-block) and appends the documents that cross tau to the
+    query's candidate region. Exercised here, bit-exact against the oracle:
+      * a term the block sample never sees (tau = 0: every matched document is a candidate) whose documents are spread
+        out — the append path with tau = 0;
+      * the same with ~1000 documents packed into two sub-blocks: more than 64 crossings per sub-block flag the query,
+        its region is cleared and it is redone by the exact per-block kernel;
+      * a frequent term with graded scores (tau > 0, ordinary crossing candidates), alone and mixed with the others;
+      * a document count that is not a multiple of the sub-block."""
+    n_docs, vocab = 600_123, 5
+    rng = np.random.default_rng(21)
+    filler = 1 + (np.arange(n_docs) % 5)                     # term 3 repeated: document lengths 1..5 (+ the others)
+    has1 = (np.arange(n_docs) % 7) == 0
+    tf1 = np.where(has1, 1 + (np.arange(n_docs) % 3), 0)
+    has0 = (np.arange(n_docs) >= 20_000) & (np.arange(n_docs) < 21_000)
+    rare = np.zeros(n_docs, dtype=bool)
+    rare[rng.choice(n_docs, 50, replace=False)] = True
+    rare[:16384] = False                                     # keep it out of sampled block 0
+    counts = np.stack([has0.astype(np.int64), tf1.astype(np.int64), rare.astype(np.int64), filler.astype(np.int64)], 1)
+    dl = counts.sum(1)
+    doc_ptr = np.zeros(n_docs + 1, dtype=np.int64)
+    np.cumsum(dl, out=doc_ptr[1:])
+    tokens = np.repeat(np.tile(np.arange(4, dtype=np.int64), n_docs), counts.reshape(-1))
+    idx, (tp, pd, ptf, dl_o, imp) = _build(tokens, doc_ptr, vocab)
+    queries = [[0], [2], [1], [1, 2], [0, 1], [0, 1, 2], [0, 2, 3], [4]]
+    for k in (10, 100):
+        s, i = idx.search(queries, k)
+        os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, k)
+        assert (i.cpu().numpy() == oi).all(), k
+        assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all(), k
