@@ -128,6 +128,22 @@ int srag_bm25_block_docs(void);   /* doc-range width one CTA accumulates in shar
 int srag_bm25_bank_order(const int64_t* block_ptr, int vocab, int64_t n_docs, const int32_t* doc_in,
                          const float* imp_in, int32_t* doc_out, float* imp_out, void* stream);
 int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes);
+/* Index build from tokens without a global sort (the reference has no index build, contract:
+ * oracle/bm25.py build_postings). Two calls, because the number of postings is only known after the first:
+ *   srag_bm25_build_plan: tokens int32 [n_tokens] with term ids in [0, vocab), documents d = tokens[doc_ptr[d] ..
+ *     doc_ptr[d+1]) of at most 8192 tokens. Every document's tokens are sorted and run-length encoded IN PLACE:
+ *     afterwards tokens[doc_ptr[d] + i], uniq_tf[doc_ptr[d] + i] (i < doc_uniq[d]) are its distinct terms and their
+ *     frequencies. Also written: dl int32 [n_docs], df int64 [vocab], term_ptr int64 [vocab+1] (nnz = term_ptr[vocab])
+ *     and block_ptr int64 [vocab, n_sub+1] (n_sub = ceil(n_docs / srag_bm25_block_docs()), as srag_bm25_block_index
+ *     would produce it). *err_flag (device int): 0 ok, 1 a document is too long, 2 a term id is out of range.
+ *   srag_bm25_build_fill: post_doc / post_tf int32 [nnz] (ascending documents inside a term); fill uint32
+ *     [vocab * n_sub] is scratch.                                                                              */
+int srag_bm25_build_plan(int32_t* tokens, const int64_t* doc_ptr, int64_t n_docs, int vocab, int32_t* uniq_tf,
+                         int32_t* doc_uniq, int32_t* dl, int64_t* df, int64_t* term_ptr, int64_t* block_ptr,
+                         int* err_flag, void* stream);
+int srag_bm25_build_fill(const int32_t* uniq_term, const int32_t* uniq_tf, const int64_t* doc_ptr,
+                         const int32_t* doc_uniq, int64_t n_docs, int vocab, const int64_t* block_ptr,
+                         uint32_t* fill, int32_t* post_doc, int32_t* post_tf, void* stream);
 /* q_terms int32 [n_queries, max_terms]: unique term ids in ASCENDING order, -1 padded.
  * out_* [n_queries, k]; only documents matching >= 1 term are candidates.               */
 int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,

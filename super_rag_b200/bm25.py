@@ -6,8 +6,8 @@ docs/design/nodeflow/nodeflow.md:83 names "BM25"). Layout and numeric contract a
 include/srag_b200.h and DESIGN.md §4.2.
 
 Host logic here is limited to: collection statistics (df, avgdl, idf in float64 -> fp32, as the
-contract requires), sorting tokens into CSR postings with torch device ops, and shaping query
-term lists. Scoring, impacts, block index and top-k are CUDA kernels.
+contract requires) and shaping query term lists. The index build from tokens, impacts, block index, bank order,
+scoring and top-k are CUDA kernels.
 """
 from __future__ import annotations
 
@@ -85,23 +85,15 @@ class Bm25Index:
     # ---- build -----------------------------------------------------------------------------
     @staticmethod
     def postings_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int):
-        """Sort (term, doc) pairs on the device -> (term_ptr int64 [V+1], post_doc int32, post_tf int32, dl int32)."""
-        dev = tokens.device
-        n_docs = doc_ptr.numel() - 1
-        dl = (doc_ptr[1:] - doc_ptr[:-1]).to(torch.int32)
-        doc_of_tok = torch.repeat_interleave(torch.arange(n_docs, device=dev, dtype=torch.int64), dl.to(torch.int64))
-        key = tokens.to(torch.int64) * n_docs + doc_of_tok
-        key, _ = torch.sort(key)
-        uniq, counts = torch.unique_consecutive(key, return_counts=True)
-        term = torch.div(uniq, n_docs, rounding_mode="floor")
-        post_doc = (uniq - term * n_docs).to(torch.int32)
-        df = torch.bincount(term, minlength=vocab)
-        term_ptr = torch.zeros(vocab + 1, dtype=torch.int64, device=dev)
-        term_ptr[1:] = torch.cumsum(df, 0)
-        return term_ptr, post_doc, counts.to(torch.int32), dl
+        """(term_ptr int64 [V+1], post_doc int32, post_tf int32, dl int32) from tokens on the device, with the library's
+        build kernels (per-document sort + run-length encode, counting, scans, scatter, per-slice sort — ops.
+        bm25_build_from_tokens); documents ascend inside a term."""
+        term_ptr, post_doc, post_tf, dl, _, _ = ops.bm25_build_from_tokens(tokens, doc_ptr, vocab)
+        return term_ptr, post_doc, post_tf, dl
 
     @classmethod
-    def from_postings(cls, term_ptr, post_doc, post_tf, dl, stats: Optional[Bm25Stats] = None, id_base: int = 0):
+    def from_postings(cls, term_ptr, post_doc, post_tf, dl, stats: Optional[Bm25Stats] = None, id_base: int = 0,
+                      block_ptr=None):
         dev = post_doc.device
         vocab = term_ptr.numel() - 1
         n_docs = dl.numel()
@@ -116,7 +108,8 @@ class Bm25Index:
         pd[:nnz] = post_doc
         post_doc = pd[:nnz]
         imp = ops.bm25_impacts(term_ptr, post_doc, post_tf, idf, dl, stats.avgdl)
-        block_ptr = ops.bm25_block_index(term_ptr, post_doc, n_docs)
+        if block_ptr is None:   # the token build produces the sub-block offsets itself
+            block_ptr = ops.bm25_block_index(term_ptr, post_doc, n_docs)
         idx = cls(term_ptr, post_doc, imp, block_ptr, n_docs, vocab, dl, stats, id_base)
         idx._bank_order()
         return idx
@@ -124,8 +117,8 @@ class Bm25Index:
     @classmethod
     def from_tokens(cls, tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int, stats: Optional[Bm25Stats] = None,
                     id_base: int = 0):
-        term_ptr, post_doc, post_tf, dl = cls.postings_from_tokens(tokens, doc_ptr, vocab)
-        return cls.from_postings(term_ptr, post_doc, post_tf, dl, stats, id_base)
+        term_ptr, post_doc, post_tf, dl, _, block_ptr = ops.bm25_build_from_tokens(tokens, doc_ptr, vocab)
+        return cls.from_postings(term_ptr, post_doc, post_tf, dl, stats, id_base, block_ptr=block_ptr)
 
     # ---- persistence (on-disk shard) ------------------------------------
     def save(self, path: str) -> None:

@@ -183,6 +183,43 @@ def bm25_block_index(term_ptr, post_doc, n_docs: int) -> torch.Tensor:
     return bp
 
 
+def bm25_build_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int):
+    """CSR postings from tokens with the library's own kernels (srag_bm25_build_plan / _fill; no global sort).
+    tokens: integer term ids [n_tokens] on the GPU, doc_ptr int64 [n_docs+1]. Returns (term_ptr int64 [V+1], post_doc int32
+    [nnz], post_tf int32 [nnz], dl int32 [n_docs], df int64 [V], block_ptr int64 [V, n_sub+1]); documents ascend inside a term."""
+    _need_cuda(tokens, doc_ptr)
+    lib = _lib.load()
+    dev = tokens.device
+    n_docs = doc_ptr.numel() - 1
+    bd = bm25_block_docs()
+    n_sub = max(1, (n_docs + bd - 1) // bd)
+    with torch.cuda.device(dev):
+        toks = tokens.to(torch.int32, copy=True).contiguous()   # consumed: becomes the per-document distinct terms
+        dp = doc_ptr.to(torch.int64).contiguous()
+        uniq_tf = torch.empty_like(toks)
+        doc_uniq = torch.empty(max(1, n_docs), dtype=torch.int32, device=dev)
+        dl = torch.empty(max(1, n_docs), dtype=torch.int32, device=dev)
+        df = torch.empty(vocab, dtype=torch.int64, device=dev)
+        term_ptr = torch.empty(vocab + 1, dtype=torch.int64, device=dev)
+        block_ptr = torch.empty(vocab, n_sub + 1, dtype=torch.int64, device=dev)
+        err = torch.zeros(1, dtype=torch.int32, device=dev)
+        st = _stream(dev)
+        _lib.check(lib.srag_bm25_build_plan(_ptr(toks), _ptr(dp), n_docs, vocab, _ptr(uniq_tf), _ptr(doc_uniq), _ptr(dl),
+                                            _ptr(df), _ptr(term_ptr), _ptr(block_ptr), _ptr(err), st), "srag_bm25_build_plan")
+        nnz, flag = int(term_ptr[vocab].item()), int(err.item())   # the one host sync of the build
+        if flag == 1:
+            raise SragError("srag_bm25_build_plan: a document has more than 8192 tokens")
+        if flag == 2:
+            raise SragError(f"srag_bm25_build_plan: a term id is outside [0, {vocab})")
+        post_doc = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]   # padded: 128-bit loads stay inside
+        post_tf = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]
+        fill = torch.empty(max(1, vocab * n_sub), dtype=torch.int32, device=dev)
+        _lib.check(lib.srag_bm25_build_fill(_ptr(toks), _ptr(uniq_tf), _ptr(dp), _ptr(doc_uniq), n_docs, vocab,
+                                            _ptr(block_ptr), _ptr(fill), _ptr(post_doc), _ptr(post_tf), st),
+                   "srag_bm25_build_fill")
+    return term_ptr, post_doc, post_tf, dl[:n_docs], df, block_ptr
+
+
 def bm25_bank_order(block_ptr, post_doc, post_imp, n_docs: int):
     """Permute the postings inside every (term, doc-block) slice for conflict-free shared-memory accumulation
     (srag_bm25_bank_order). Returns new (post_doc, post_imp), padded like the inputs; scores are unchanged."""

@@ -278,3 +278,50 @@ def test_bm25_sub_kernel_candidate_paths_and_fallback():
         os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, k)
         assert (i.cpu().numpy() == oi).all(), k
         assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all(), k
+
+
+def test_bm25_native_build_matches_oracle_postings():
+    """srag_bm25_build_plan / _fill (per-document sort + run-length encode, counting, scans, scatter, per-slice sort)
+    against oracle.build_postings: term_ptr, postings (documents ascending inside a term), tf, dl and the sub-block
+    offsets, all exact. Covers empty documents, a single-token document repeated 5000 times, slices longer than 32
+    postings (bitonic path) and short ones (ranking path), and the two error flags."""
+    import torch
+    from super_rag_b200 import ops
+    from super_rag_b200._lib import SragError
+    n_docs, vocab = 9000, 700
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, 60, seed=3)
+    # splice in: an empty document, a very long repetitive one, a long varied one
+    dl = np.diff(doc_ptr)
+    docs = [tokens[doc_ptr[d]:doc_ptr[d + 1]] for d in range(n_docs)]
+    docs[17] = docs[17][:0]
+    docs[4000] = np.full(5000, vocab - 1, dtype=np.int64)
+    docs[8999] = np.arange(8192, dtype=np.int64) % vocab
+    tokens = np.concatenate(docs)
+    doc_ptr = np.zeros(n_docs + 1, dtype=np.int64)
+    np.cumsum([len(x) for x in docs], out=doc_ptr[1:])
+    tp, pd, ptf, dl = oracle.build_postings(tokens, doc_ptr, vocab)
+    t = torch.from_numpy(tokens).cuda()
+    dp = torch.from_numpy(doc_ptr).cuda()
+    term_ptr, post_doc, post_tf, dl_g, df, block_ptr = ops.bm25_build_from_tokens(t, dp, vocab)
+    assert (term_ptr.cpu().numpy() == tp).all()
+    assert (post_doc.cpu().numpy() == pd).all()
+    assert (post_tf.cpu().numpy() == ptf).all()
+    assert (dl_g.cpu().numpy() == dl).all()
+    assert (df.cpu().numpy() == np.diff(tp)).all()
+    assert torch.equal(block_ptr, ops.bm25_block_index(term_ptr, post_doc, n_docs))
+    assert (t.cpu().numpy() == tokens).all(), "the caller's tokens must not be consumed"
+    # deterministic
+    again = ops.bm25_build_from_tokens(t, dp, vocab)
+    assert torch.equal(again[1], post_doc) and torch.equal(again[2], post_tf)
+    # errors are loud
+    bad = t.clone()
+    bad[5] = vocab
+    with pytest.raises(SragError):
+        ops.bm25_build_from_tokens(bad, dp, vocab)
+    long_ptr = torch.tensor([0, 8193], dtype=torch.int64, device="cuda")
+    with pytest.raises(SragError):
+        ops.bm25_build_from_tokens(torch.zeros(8193, dtype=torch.int64, device="cuda"), long_ptr, vocab)
+    # degenerate: no documents
+    e = ops.bm25_build_from_tokens(torch.zeros(0, dtype=torch.int64, device="cuda"),
+                                   torch.zeros(1, dtype=torch.int64, device="cuda"), 5)
+    assert e[0].tolist() == [0] * 6 and e[1].numel() == 0
