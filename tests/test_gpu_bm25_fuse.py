@@ -325,3 +325,17 @@ def test_bm25_native_build_matches_oracle_postings():
     e = ops.bm25_build_from_tokens(torch.zeros(0, dtype=torch.int64, device="cuda"),
                                    torch.zeros(1, dtype=torch.int64, device="cuda"), 5)
     assert e[0].tolist() == [0] * 6 and e[1].numel() == 0
+
+
+def test_bm25_sub_kernel_queries_longer_than_32_terms():
+    """Two-phase path (35 blocks) with queries of 33 .. 90 terms: the warp-granular kernel walks the term slots in
+    groups of 32; summation order must stay ascending term id across the groups."""
+    n_docs, vocab = 560_000, 200
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, 12, seed=5)
+    idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    rng = np.random.default_rng(6)
+    queries = [rng.choice(vocab, size=n, replace=False).tolist() for n in (33, 40, 64, 65, 90, 8)]
+    s, i = idx.search(queries, 50)
+    os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, 50)
+    assert (i.cpu().numpy() == oi).all()
+    assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all()
