@@ -14,6 +14,8 @@ corpus is row-sharded across the ranks (strong scaling; the metric is quoted on 
   roofline  dominant kernel (topk_gemm_kernel) timed live with CUDA events on its stream
   cpu_baseline / --impl reference   the CPU oracle port (numpy BLAS, all host threads) on a
             bounded row sample of the same workload, extrapolated linearly in rows
+  other_configs  (N = 1 only, after the timed region; not part of `value`) BASELINE.json configs[2] and [3]: BM25 top-100 over
+            a 10 M-document Zipfian index with its own HBM roofline, and the hybrid vector + BM25 -> RRF pipeline
 """
 from __future__ import annotations
 
@@ -43,6 +45,7 @@ def parse_args():
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--cpu-sample-rows", type=int, default=0, help="rows of the CPU baseline sample (0 = default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-hybrid", action="store_true", help="skip the C3 (BM25) / C4 (hybrid) lines attached at N=1")
     return ap.parse_args()
 
 
@@ -308,6 +311,17 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             base, _ = time_cpu_oracle(args, args.cpu_sample_rows or 262144, steps=2, warmup=1)
             line["cpu_baseline"] = base
+        if world == 1 and not args.no_hybrid and args.rows == 10_000_000:
+            # BASELINE.json configs[2] / configs[3] beside the headline (not part of `value`): BM25 top-100 over a 10 M-document
+            # Zipfian index and the hybrid vector + BM25 -> RRF pipeline, through tools/bench_hybrid.py
+            try:
+                torch.cuda.empty_cache()
+                sys.path.insert(0, os.path.join(ROOT, "tools"))
+                import bench_hybrid
+                hy = argparse.Namespace(docs=args.rows, queries=B, terms=8, steps=5, warmup=3, check=2, skip_c4=False, dim=DIM)
+                line["other_configs"] = list(bench_hybrid.run(hy, dev))
+            except Exception as e:  # the headline line must still be printed
+                line["other_configs"] = {"error": f"{type(e).__name__}: {e}"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -131,7 +131,13 @@ def main():
     ap.add_argument("--skip-c4", action="store_true")
     ap.add_argument("--dim", type=int, default=1024)
     args = ap.parse_args()
-    dev = torch.device("cuda:0")
+    for line in run(args):
+        print(json.dumps(line), flush=True)
+
+
+def run(args, dev=None):
+    """Generator of the C3 line and (unless args.skip_c4) the C4 line; bench.py attaches them to its own line."""
+    dev = dev or torch.device("cuda:0")
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))
@@ -154,13 +160,13 @@ def main():
             n = int((wi >= 0).sum().item())
             ok &= bool(torch.equal(bi[q, :n], wi[:n])) and bool(torch.equal(bs[q, :n].view(torch.int32), ws[:n].view(torch.int32)))
     sorted_ok = bool((bs[:, :-1] >= bs[:, 1:]).all().item())
-    print(json.dumps({"config": "C3", "workload": f"BM25 {args.docs} docs, V={VOCAB}, nnz={idx.nnz}, {args.queries} queries x "
+    yield ({"config": "C3", "workload": f"BM25 {args.docs} docs, V={VOCAB}, nnz={idx.nnz}, {args.queries} queries x "
                       f"{args.terms} terms (Zipf ranks 101..V), top-100", "queries_per_s": args.queries / (ms * 1e-3),
                       "ms_per_batch": ms, "posting_bytes_per_batch": post_bytes,
                       "roofline": {"bound": "hbm", "achieved": post_bytes / (ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
                                    "frac": post_bytes / (ms * 1e-3) / 1e9 / hbm},
                       "index_bytes": idx.nnz * 8, "index_build_s": build_s, "restatement_check_ok": ok,
-                      "scores_sorted": sorted_ok}), flush=True)
+                      "scores_sorted": sorted_ok})
     if args.skip_c4:
         return
 
@@ -187,11 +193,11 @@ def main():
     ms_v, _ = timed(lambda: ops.topk_search(corpus, cs, *ops.ingest_rows(q32, "cosine"), 100, workspace=ws), 1, args.steps)
     ms_f, _ = timed(lambda: ops.fuse(torch.stack([vi, bi]), None, ops.FUSE_RRF, 10, rank_const=60), 1, args.steps)
     planted_ok = bool((vi[:h, 0] == src).all().item())
-    print(json.dumps({"config": "C4", "workload": f"hybrid: vector top-100 ({args.docs}x{args.dim} bf16) + BM25 top-100 -> RRF(60) -> top-10, "
+    yield ({"config": "C4", "workload": f"hybrid: vector top-100 ({args.docs}x{args.dim} bf16) + BM25 top-100 -> RRF(60) -> top-10, "
                       f"{args.queries} queries", "queries_per_s": args.queries / (ms4 * 1e-3), "ms_per_batch": ms4,
                       "ms_vector_top100": ms_v, "ms_bm25_top100": ms, "ms_fuse": ms_f,
                       "vector_tflops": 2.0 * args.queries * args.docs * args.dim / (ms_v * 1e-3) / 1e12,
-                      "planted_top1_ok": planted_ok}), flush=True)
+                      "planted_top1_ok": planted_ok})
 
 
 if __name__ == "__main__":
