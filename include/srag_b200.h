@@ -131,7 +131,7 @@ int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* byte
 /* Index build from tokens without a global sort (the reference has no index build, contract:
  * oracle/bm25.py build_postings). Two calls, because the number of postings is only known after the first:
  *   srag_bm25_build_plan: tokens int32 [n_tokens] with term ids in [0, vocab), documents d = tokens[doc_ptr[d] ..
- *     doc_ptr[d+1]) of at most 8192 tokens. Every document's tokens are sorted and run-length encoded IN PLACE:
+ *     doc_ptr[d+1]) of at most 57344 tokens. Every document's tokens are sorted and run-length encoded IN PLACE:
  *     afterwards tokens[doc_ptr[d] + i], uniq_tf[doc_ptr[d] + i] (i < doc_uniq[d]) are its distinct terms and their
  *     frequencies. Also written: dl int32 [n_docs], df int64 [vocab], term_ptr int64 [vocab+1] (nnz = term_ptr[vocab])
  *     and block_ptr int64 [vocab, n_sub+1] (n_sub = ceil(n_docs / srag_bm25_block_docs()), as srag_bm25_block_index

@@ -2,7 +2,8 @@
 // (term_ptr, post_doc, post_tf, dl) and the sub-block offset table block_ptr, without a global sort.
 // HBM-bound integer work; every step is one pass over its input.
 //
-//   build_doc_terms_kernel   one CTA per document: its tokens are sorted in shared memory (bitonic) and run-length
+//   build_doc_terms_kernel   one CTA per document (a second launch with 224 KB of shared memory takes the documents
+//                            of more than 8192 tokens): its tokens are sorted in shared memory (bitonic) and run-length
 //                            encoded IN PLACE into (term, tf) pairs at the start of the document's token range; every
 //                            pair is counted into cnt[term][sub-block of the document].
 //   build_row_sum / build_scan_terms / build_row_scan
@@ -20,27 +21,27 @@
 namespace {
 
 constexpr int BUILD_SUB_DOCS = 2048;   // = BM25_SUB_DOCS (bm25.cu); srag_bm25_block_docs() is checked by the caller
-constexpr int BUILD_MAX_DL = 8192;     // tokens of one document (32 KB of shared memory)
+constexpr int BUILD_MAX_DL = 8192;     // tokens of one document in the main pass (32 KB of shared memory, 7 CTAs per SM)
+constexpr int BUILD_LONG_DL = 57344;   // ... in the pass for long documents (224 KB, one CTA per SM)
 constexpr int BUILD_THREADS = 128;
 constexpr uint32_t PAD = 0xFFFFFFFFu;
 
 __global__ void __launch_bounds__(BUILD_THREADS)
 build_doc_terms_kernel(int32_t* __restrict__ tokens, const int64_t* __restrict__ doc_ptr, int64_t n_docs, int vocab,
                        int n_sub, int32_t* __restrict__ tf_out, int32_t* __restrict__ doc_uniq, int32_t* __restrict__ dl_out,
-                       unsigned long long* __restrict__ cnt, int* __restrict__ err) {
+                       unsigned long long* __restrict__ cnt, int* __restrict__ err,
+                       int min_len /* documents of min_len < tokens <= max_len are this launch's */, int max_len) {
     extern __shared__ uint32_t buf[];
     __shared__ int warp_heads[BUILD_THREADS / 32];
     __shared__ int running;
+    __shared__ uint32_t sel[BUILD_THREADS / 32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int64_t d = blockIdx.x; d < n_docs; d += gridDim.x) {
-        const int64_t a = doc_ptr[d], b = doc_ptr[d + 1];
-        const int64_t len64 = b - a;
-        if (threadIdx.x == 0) dl_out[d] = (int32_t)len64;
-        if (len64 > BUILD_MAX_DL || len64 < 0) {
-            if (threadIdx.x == 0) { atomicExch(err, 1); doc_uniq[d] = 0; }
-            continue;
-        }
-        const int len = (int)len64;
+
+    // the whole CTA on one document: sort, run-length encode in place, count the pairs
+    auto process_doc = [&](int64_t d) {
+        const int64_t a = doc_ptr[d];
+        const int len = (int)(doc_ptr[d + 1] - a);
+        if (threadIdx.x == 0) dl_out[d] = len;
         int P = 2;
         while (P < len) P <<= 1;
         for (int i = threadIdx.x; i < P; i += BUILD_THREADS) buf[i] = i < len ? (uint32_t)tokens[a + i] : PAD;
@@ -58,7 +59,7 @@ build_doc_terms_kernel(int32_t* __restrict__ tokens, const int64_t* __restrict__
                 __syncthreads();
             }
         }
-        // run-length encode: a head is the first token of a run of equal terms
+        // a head is the first token of a run of equal terms
         const int sub = (int)(d / BUILD_SUB_DOCS);
         for (int base = 0; base < len; base += BUILD_THREADS) {
             const int i = base + threadIdx.x;
@@ -90,6 +91,32 @@ build_doc_terms_kernel(int32_t* __restrict__ tokens, const int64_t* __restrict__
         }
         if (threadIdx.x == 0) doc_uniq[d] = running;
         __syncthreads();
+    };
+
+    // A CTA takes BUILD_THREADS consecutive documents at a time: every thread looks at one document's length, the ones
+    // that belong to this launch are then processed one after the other.
+    for (int64_t d0 = (int64_t)blockIdx.x * BUILD_THREADS; d0 < n_docs; d0 += (int64_t)gridDim.x * BUILD_THREADS) {
+        const int64_t dd = d0 + threadIdx.x;
+        bool mine = false;
+        if (dd < n_docs) {
+            const int64_t l = doc_ptr[dd + 1] - doc_ptr[dd];
+            if (l > BUILD_LONG_DL || l < 0) {
+                if (min_len == 0) { atomicExch(err, 1); doc_uniq[dd] = 0; dl_out[dd] = 0; }
+            } else {
+                mine = (l > min_len || (min_len == 0 && l == 0)) && l <= max_len;
+            }
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, mine);
+        if (lane == 0) sel[w] = bal;
+        __syncthreads();
+        for (int sw = 0; sw < BUILD_THREADS / 32; ++sw) {
+            uint32_t todo = sel[sw];
+            while (todo) {
+                process_doc(d0 + 32 * sw + (__ffs(todo) - 1));
+                todo &= todo - 1;
+            }
+        }
+        __syncthreads();  // sel is rewritten by the next round
     }
 }
 
@@ -266,7 +293,7 @@ extern "C" int srag_bm25_build_plan(int32_t* tokens, const int64_t* doc_ptr, int
     static bool attr_done = false;
     if (!attr_done) {
         SRAG_CUDA(cudaFuncSetAttribute(build_doc_terms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       BUILD_MAX_DL * (int)sizeof(uint32_t)));
+                                       BUILD_LONG_DL * (int)sizeof(uint32_t)));
         SRAG_CUDA(cudaFuncSetAttribute(build_sort_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        SORT_WARPS * BUILD_SUB_DOCS * (int)sizeof(unsigned long long)));
         attr_done = true;
@@ -275,8 +302,12 @@ extern "C" int srag_bm25_build_plan(int32_t* tokens, const int64_t* doc_ptr, int
     SRAG_CUDA(cudaMemsetAsync(cnt, 0, (size_t)vocab * (n_sub + 1) * sizeof(unsigned long long), st));
     SRAG_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
     if (n_docs > 0) {
-        build_doc_terms_kernel<<<grid_for(n_docs, 1, 148 * 16), BUILD_THREADS, BUILD_MAX_DL * sizeof(uint32_t), st>>>(
-            tokens, doc_ptr, n_docs, vocab, n_sub, uniq_tf, doc_uniq, dl, cnt, err_flag);
+        build_doc_terms_kernel<<<grid_for(n_docs, BUILD_THREADS, 148 * 16), BUILD_THREADS, BUILD_MAX_DL * sizeof(uint32_t), st>>>(
+            tokens, doc_ptr, n_docs, vocab, n_sub, uniq_tf, doc_uniq, dl, cnt, err_flag, 0, BUILD_MAX_DL);
+        SRAG_CUDA(cudaGetLastError());
+        // documents of more than 8192 tokens (rare): same kernel, one CTA per SM with 224 KB of shared memory
+        build_doc_terms_kernel<<<grid_for(n_docs, BUILD_THREADS, 148), BUILD_THREADS, BUILD_LONG_DL * sizeof(uint32_t), st>>>(
+            tokens, doc_ptr, n_docs, vocab, n_sub, uniq_tf, doc_uniq, dl, cnt, err_flag, BUILD_MAX_DL, BUILD_LONG_DL);
         SRAG_CUDA(cudaGetLastError());
     }
     build_row_sum_kernel<<<grid_for(vocab, 8, 148 * 8), 256, 0, st>>>(cnt, vocab, n_sub, df);

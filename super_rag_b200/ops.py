@@ -208,7 +208,7 @@ def bm25_build_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: i
                                             _ptr(df), _ptr(term_ptr), _ptr(block_ptr), _ptr(err), st), "srag_bm25_build_plan")
         nnz, flag = int(term_ptr[vocab].item()), int(err.item())   # the one host sync of the build
         if flag == 1:
-            raise SragError("srag_bm25_build_plan: a document has more than 8192 tokens")
+            raise SragError("srag_bm25_build_plan: a document has more than 57344 tokens")
         if flag == 2:
             raise SragError(f"srag_bm25_build_plan: a term id is outside [0, {vocab})")
         post_doc = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]   # padded: 128-bit loads stay inside

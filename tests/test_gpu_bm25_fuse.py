@@ -283,7 +283,7 @@ def test_bm25_sub_kernel_candidate_paths_and_fallback():
 def test_bm25_native_build_matches_oracle_postings():
     """srag_bm25_build_plan / _fill (per-document sort + run-length encode, counting, scans, scatter, per-slice sort)
     against oracle.build_postings: term_ptr, postings (documents ascending inside a term), tf, dl and the sub-block
-    offsets, all exact. Covers empty documents, a single-token document repeated 5000 times, slices longer than 32
+    offsets, all exact. Covers empty documents, a single-token document repeated 5000 times, a 20 000-token document (long-document pass), slices longer than 32
     postings (bitonic path) and short ones (ranking path), and the two error flags."""
     import torch
     from super_rag_b200 import ops
@@ -296,6 +296,7 @@ def test_bm25_native_build_matches_oracle_postings():
     docs[17] = docs[17][:0]
     docs[4000] = np.full(5000, vocab - 1, dtype=np.int64)
     docs[8999] = np.arange(8192, dtype=np.int64) % vocab
+    docs[123] = (np.arange(20_000, dtype=np.int64) * 7) % vocab          # longer than the main pass takes: long-document pass
     tokens = np.concatenate(docs)
     doc_ptr = np.zeros(n_docs + 1, dtype=np.int64)
     np.cumsum([len(x) for x in docs], out=doc_ptr[1:])
@@ -318,9 +319,9 @@ def test_bm25_native_build_matches_oracle_postings():
     bad[5] = vocab
     with pytest.raises(SragError):
         ops.bm25_build_from_tokens(bad, dp, vocab)
-    long_ptr = torch.tensor([0, 8193], dtype=torch.int64, device="cuda")
+    long_ptr = torch.tensor([0, 57345], dtype=torch.int64, device="cuda")
     with pytest.raises(SragError):
-        ops.bm25_build_from_tokens(torch.zeros(8193, dtype=torch.int64, device="cuda"), long_ptr, vocab)
+        ops.bm25_build_from_tokens(torch.zeros(57345, dtype=torch.int64, device="cuda"), long_ptr, vocab)
     # degenerate: no documents
     e = ops.bm25_build_from_tokens(torch.zeros(0, dtype=torch.int64, device="cuda"),
                                    torch.zeros(1, dtype=torch.int64, device="cuda"), 5)
