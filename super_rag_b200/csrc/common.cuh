@@ -196,12 +196,6 @@ __device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, uint32_
                  "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
-// pull one box of a 2-D tensor map into L2 (no shared-memory destination, no barrier)
-__device__ __forceinline__ void tma_prefetch_2d(const void* tmap, int c0, int c1) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(tmap)),
-                 "r"(c0), "r"(c1)
-                 : "memory");
-}
 __device__ __forceinline__ void prefetch_tmap(const void* tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
 }

@@ -87,7 +87,6 @@ struct TopkParams {
     int share_j;      // j = ceil(k / lists), 1..8; 0 = threshold sharing off
     int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
     int window;       // tiles the leader may run ahead of the slowest follower
-    int prefetch;     // 1: the unit that pulls a corpus tile from HBM also pulls the NEXT one into L2 (TMA prefetch)
     int debug;        // SRAG_TOPK_DEBUG perf-dissection bits (results are WRONG when set): 2 no MMA, 4 no epilogue work
     // metadata pre-filter (all null = off): a row is eligible for query q iff
     //   (row_tags == null  || (row_tags[row] & q_tag_mask[q]) != 0) &&
@@ -233,16 +232,9 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     while (prog[0] < it + 1 && ++spins <= 4096u) __nanosleep(64);
                 }
             }
-            // HBM-bound side (few query tiles): the ring holds query AND corpus k-blocks, so only half of it is HBM
-            // requests in flight. The unit that reads a tile from HBM therefore also asks for the next tile of its
-            // slab, k-block by k-block, as an L2 prefetch: no shared memory, no barrier, one tile ahead.
-            const int c_next = c + p.num_slabs;
-            const bool pf = p.prefetch && (!paced || q_tile == 0) && c_next < num_c_tiles;
-            const int c_row_next = c_next * BLOCK_N + (int)cta_rank * C::B_ROWS;
             for (int kb = 0; kb < num_kb; ++kb) {
                 ptx::mbar_wait(&tail->empty[stage], phase ^ 1);
                 if (ptx::elect_one()) {
-                    if (pf) ptx::tma_prefetch_2d(&tmap_c, kb * BLOCK_K, c_row_next);
                     uint8_t* s_dst = ring + stage * C::STAGE_BYTES;
                     uint8_t* b_dst = RQ ? s_dst : s_dst + C::A_BYTES;
                     if constexpr (G == 1) {
@@ -910,7 +902,6 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
         prm.share_j = (env_int("SRAG_TOPK_SHARE", 1) != 0 && lists >= 2 && worth && j <= 8) ? j : 0;
     }
     prm.window = pl.window;
-    prm.prefetch = env_int("SRAG_TOPK_PREFETCH", 0);  // opt-in until measured
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
     prm.row_tags = n_rows > 0 ? row_tags : nullptr;
     prm.row_group = n_rows > 0 ? row_group : nullptr;
