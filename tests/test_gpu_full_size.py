@@ -115,7 +115,7 @@ def test_c3_two_phase_selection_matches_restatement():
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
     import bench_hybrid as bh
     dev = torch.device("cuda:0")
-    idx = bh.build_index(2_000_000, dev)            # 123 blocks: phase 0 samples every 16th
+    idx = bh.build_index(2_000_000, dev)            # 123 blocks: phase 0 samples every 32nd, phase 1 runs on the warp-granular kernel
     qt = bh.make_queries(48, 8, dev)
     qt[0, 4:] = -1                                   # short query
     qt[1] = torch.tensor([0, 1, 2, 3, 4, 5, 6, 7], dtype=torch.int32, device=dev)   # the 8 most frequent terms
