@@ -775,9 +775,12 @@ template <bool FILT>
 __global__ void __launch_bounds__(32 * SUB_WARPS, 1)
 bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, const int32_t* __restrict__ post_doc,
                 const float* __restrict__ post_imp, int n_blocks, int n_sub, const int32_t* __restrict__ q_terms,
-                int max_terms, int k, int q_offset, int nq, int stride, const float* __restrict__ tau /* [nq][k] */,
-                uint64_t* __restrict__ partial /* [nq][n_blocks * k] */, uint32_t* __restrict__ q_count /* [nq], zeroed */,
-                uint32_t* __restrict__ q_flag /* [nq], zeroed */, uint32_t* __restrict__ n_flagged, Bm25Filter flt) {
+                int max_terms, int k, int q_offset, int nq, int stride,
+                const float* __restrict__ tau /* [nq][k]; nullptr = SAMPLE pass */,
+                uint64_t* __restrict__ partial /* [nq][n_blocks * k]; sample pass: [nq][nb0 * BM25_SUBS * 32] */,
+                uint32_t* __restrict__ q_count /* [nq], zeroed */, uint32_t* __restrict__ q_flag /* [nq], zeroed */,
+                uint32_t* __restrict__ n_flagged, Bm25Filter flt,
+                int sample_group /* sample pass: 1 or 4 lanes share one report (32 or 8 reports per sub-block) */) {
     extern __shared__ uint8_t bm25_smem_raw[];
     SubSmem* sm = reinterpret_cast<SubSmem*>(bm25_smem_raw);
     constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -785,8 +788,13 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
     float* acc = sm->acc[w];
     uint16_t* cand = sm->cand[w];
     uint32_t* cand_count = &sm->cand_count[w];
+    // Two passes share this kernel. SAMPLE pass (tau == nullptr): the sub-blocks of every stride-th block; nothing is
+    // tracked while the terms are applied, and at the end of an item every lane reports the best of the 64 accumulators
+    // it scans (32 true scores per sampled sub-block; the k-th best of a query's reports is tau, a lower bound of its
+    // global k-th score). MAIN pass: ALL sub-blocks, the sampled ones again, with the crossing rule.
+    const bool sample_pass = tau == nullptr;
     const int nb0 = (n_blocks + stride - 1) / stride;
-    const int per_q = (n_blocks - nb0) * BM25_SUBS;            // phase-1 sub-blocks of one query
+    const int per_q = (sample_pass ? nb0 : n_blocks) * BM25_SUBS;   // sub-blocks of one query in this pass
     const long long n_items = (long long)nq * per_q;
     const long long step = (long long)gridDim.x * SUB_WARPS;
     const uint32_t cap = (uint32_t)n_blocks * (uint32_t)k;     // key slots of one query in `partial`
@@ -802,9 +810,7 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
     };
     auto sub_of = [&](Item x) -> int {  // sub-block index, -1 past the end of the queries or of the documents
         if (x.q >= nq) return -1;
-        const int jb = x.j / BM25_SUBS;
-        const int blk = jb + jb / (stride - 1) + 1;  // the jb-th block that is not in the sample
-        const int sub = blk * BM25_SUBS + (x.j - jb * BM25_SUBS);
+        const int sub = sample_pass ? (x.j / BM25_SUBS) * stride * BM25_SUBS + x.j % BM25_SUBS : x.j;
         return sub < n_sub ? sub : -1;
     };
     auto term_of = [&](Item x, int sub, int j0) -> int32_t {
@@ -836,15 +842,15 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
     bounds_of(s0, term_of(x0, s0, 0), lo, n0);
     bounds_of(s1, term_of(x1, s1, 0), lo1, n1);
     bounds_of(s2, term_of(x2, s2, 0), lo2, n2);
-    float tau0 = s0 >= 0 ? __ldg(tau + (size_t)x0.q * k + (k - 1)) : 0.f;
-    float tau1 = s1 >= 0 ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
+    float tau0 = s0 >= 0 && !sample_pass ? __ldg(tau + (size_t)x0.q * k + (k - 1)) : 0.f;
+    float tau1 = s1 >= 0 && !sample_pass ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
 
     for (; x0.q < nq;) {
         if (s0 >= 0) {
             const int q = x0.q;
             const int32_t doc_base = s0 * BM25_SUB_DOCS;
             // tau = 0 (the sample matched fewer than k documents): every matched document is a candidate
-            const uint32_t cross_bits = tau0 > 0.f ? __float_as_uint(tau0) : 1u;
+            const uint32_t cross_bits = sample_pass ? 0xFFFFFFFFu : tau0 > 0.f ? __float_as_uint(tau0) : 1u;
             uint32_t f_mask = 0xFFFFFFFFu;
             int32_t f_group = -1;
             if constexpr (FILT) {
@@ -997,7 +1003,37 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                     }
                 }
             }
-            if (zeroed) {
+            if (zeroed && sample_pass) {
+                // lane l scans accumulators l, l + 32, ... (conflict-free) and reports its best (ties: lowest document)
+                __syncwarp();
+                uint32_t best = 0, best_rel = 0;
+#pragma unroll 8
+                for (int i = 0; i < BM25_SUB_DOCS / 32; ++i) {
+                    const uint32_t rel = (uint32_t)(lane + 32 * i);
+                    bool ok = true;
+                    const uint32_t v = __float_as_uint(acc[rel]);
+                    if constexpr (FILT) {
+                        if (v > best) {
+                            const int32_t doc = doc_base + (int32_t)rel;
+                            if (flt.doc_tags && (__ldg(flt.doc_tags + doc) & f_mask) == 0) ok = false;
+                            if (f_group >= 0 && __ldg(flt.doc_group + doc) != f_group) ok = false;
+                        }
+                    }
+                    if (v > best && ok) { best = v; best_rel = rel; }
+                }
+                const int ssub = (s0 / (stride * BM25_SUBS)) * BM25_SUBS + s0 % BM25_SUBS;  // index among the sampled ones
+                uint64_t key = best ? srag_pack_key(best, (uint32_t)doc_base + best_rel) : SRAG_KEY_EMPTY;
+                if (sample_group == 4) {  // the best of four lanes: fewer keys for the tau merge to sort
+                    uint64_t o = __shfl_xor_sync(FULL, key, 1);
+                    key = o > key ? o : key;
+                    o = __shfl_xor_sync(FULL, key, 2);
+                    key = o > key ? o : key;
+                }
+                const int per_sub = 32 / sample_group;
+                if ((lane & (sample_group - 1)) == 0)
+                    partial[((size_t)q * per_q + ssub) * per_sub + lane / sample_group] = key;
+                __syncwarp();
+            } else if (zeroed) {
                 __syncwarp();
                 const uint32_t nc = *cand_count;
                 if (nc > (uint32_t)SUB_CAND) {
@@ -1005,11 +1041,11 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                 } else if (nc > 0) {
                     uint32_t base = 0;
                     if (lane == 0) base = atomicAdd(&q_count[q], nc);
-                    base = __shfl_sync(FULL, base, 0) + (uint32_t)k;  // slots 0..k-1: the sample's top-k
+                    base = __shfl_sync(FULL, base, 0);
                     if (base + nc > cap) {
                         flag_query(q);
                     } else {
-                        uint64_t* out = partial + (size_t)q * cap + base;
+                        uint64_t* out = partial + (size_t)q * cap + base;  // the region fills from the front
                         for (uint32_t i = lane; i < nc; i += 32) {
                             const uint32_t rel = cand[i];
                             out[i] = srag_pack_key(__float_as_uint(acc[rel]), (uint32_t)doc_base + rel);
@@ -1034,7 +1070,7 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
         n1 = n2;
         tau0 = tau1;
         bounds_of(s2, t3, lo2, n2);
-        tau1 = s1 >= 0 ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
+        tau1 = s1 >= 0 && !sample_pass ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
         t3 = term_of(x3, s3, 0);
     }
 }
@@ -1250,9 +1286,10 @@ static int bm25_stride(int nb) {
     // selection per block, a lower tau costs candidates), every 16th for mid-sized indexes, no sample below 32 blocks
     return nb >= 64 ? 32 : nb >= 32 ? 16 : 1;
 }
+constexpr int SUB_SAMPLE_KEYS = BM25_SUBS * 32;  // sample reports per sampled block on the sub-kernel path (32 per sub-block)
 static size_t bm25_sample_bytes(int qc, int nb, int k) {
     const int stride = bm25_stride(nb);
-    return stride > 1 ? bm25_partial_bytes(qc, (nb + stride - 1) / stride, k) : 0;
+    return stride > 1 ? bm25_partial_bytes(qc, (nb + stride - 1) / stride, k > SUB_SAMPLE_KEYS ? k : SUB_SAMPLE_KEYS) : 0;
 }
 static size_t bm25_tau_bytes(int qc, int k) { return (((size_t)qc * k * (sizeof(float) + sizeof(int64_t))) + 255) & ~(size_t)255; }
 // bm25_sub_kernel: candidate counter and overflow flag per query + the number of flagged queries
@@ -1329,13 +1366,47 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
         const int nq = (n_queries - q0) < qc ? (n_queries - q0) : qc;
         const bool sub_path = use_sub && stride > 1 && n_docs > 0;
         if (sub_path) {
-            // candidate regions are filled from the front and read up to their fill level: only the sample lists
-            // (they follow `partial` in the workspace) must start out empty
-            SRAG_CUDA(cudaMemsetAsync(sample, 0, (size_t)nq * nb0 * k * sizeof(uint64_t), st));
-        } else {
-            // the memset covers the sample lists too
-            SRAG_CUDA(cudaMemsetAsync(partial, 0, bm25_partial_bytes(qc, nb, k) + (stride > 1 ? (size_t)nq * nb0 * k * sizeof(uint64_t) : 0), st));
+            // Warp-granular path. SAMPLE pass over every stride-th block -> 32 true scores per sampled sub-block -> tau =
+            // the k-th best of them; MAIN pass over ALL sub-blocks (the sampled ones again: 1/stride more postings, but no
+            // exact per-block selection anywhere) appends the documents that cross tau to the query's region, which is
+            // filled from the front and read up to its fill level, so it needs no zeroing. Queries whose candidates
+            // overflow are flagged, their region cleared, and redone by the exact per-block kernel over all blocks.
+            auto kern = filtered ? bm25_items_kernel<true> : bm25_items_kernel<false>;
+            auto skern = filtered ? bm25_sub_kernel<true> : bm25_sub_kernel<false>;
+            // 8 reports per sampled sub-block when that still leaves plenty more than k of them, else 32
+            const int sgroup = (long long)nb0 * BM25_SUBS * 8 >= 8ll * k ? 4 : 1;
+            const size_t sample_keys = (size_t)nb0 * (SUB_SAMPLE_KEYS / sgroup);
+            SRAG_CUDA(cudaMemsetAsync(sample, 0, (size_t)nq * sample_keys * sizeof(uint64_t), st));
+            SRAG_CUDA(cudaMemsetAsync(q_count, 0, bm25_ctr_bytes(qc), st));
+            const long long w0 = ((long long)nq * nb0 * BM25_SUBS + SUB_WARPS - 1) / SUB_WARPS;
+            skern<<<(int)(w0 < sm_count ? w0 : sm_count), 32 * SUB_WARPS, sizeof(SubSmem), st>>>(
+                block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms, k, q0, nq, stride, nullptr, sample, q_count,
+                q_flag, n_flagged, flt, sgroup);
+            SRAG_CUDA(cudaGetLastError());
+            int rc = srag_launch_finalize_ex(sample, sample_keys, nq, (int)sample_keys, k, nullptr, 0, tau_scores, tau_ids,
+                                             nullptr, 0, st);
+            if (rc) return rc;
+            const long long w1 = ((long long)nq * nb * BM25_SUBS + SUB_WARPS - 1) / SUB_WARPS;
+            skern<<<(int)(w1 < sm_count ? w1 : sm_count), 32 * SUB_WARPS, sizeof(SubSmem), st>>>(
+                block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms, k, q0, nq, stride, tau_scores, partial, q_count,
+                q_flag, n_flagged, flt, 1);
+            SRAG_CUDA(cudaGetLastError());
+            bm25_clear_flagged_kernel<<<nq, 256, 0, st>>>(partial, 0, (uint32_t)nb * (uint32_t)k, q_flag, n_flagged);
+            SRAG_CUDA(cudaGetLastError());
+            const long long itemsf = (long long)nq * nb;
+            kern<<<(int)(itemsf < resident ? itemsf : resident), BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(
+                block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms, k, q0, nq, 0, 1, nullptr, partial, dbg, flt,
+                n_docs, q_flag, n_flagged);
+            SRAG_CUDA(cudaGetLastError());
+            rc = srag_launch_finalize_live(partial, (size_t)nb * k, nq, nb * k, k, nullptr, id_base,
+                                           out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, nullptr, 0, q_count, q_flag,
+                                           0, st);
+            if (rc) return rc;
+            continue;
         }
+        // producer / consumer kernel only (indexes too small to sample, SRAG_BM25_SUBKERNEL=0): the memset covers the
+        // sample lists too
+        SRAG_CUDA(cudaMemsetAsync(partial, 0, bm25_partial_bytes(qc, nb, k) + (stride > 1 ? (size_t)nq * nb0 * k * sizeof(uint64_t) : 0), st));
         if (n_docs > 0) {
             const long long items0 = (long long)nq * nb0;
             const int grid0 = (int)(items0 < resident ? items0 : resident);
@@ -1353,32 +1424,14 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
                 if (rc) return rc;
                 const long long items1 = (long long)nq * (nb - nb0);
                 const int grid1 = (int)(items1 < resident ? items1 : resident);
-                if (use_sub) {
-                    // every (query, sub-block) on its own warp; queries whose candidates overflow are flagged, their
-                    // region cleared and redone below with the exact per-block selection
-                    SRAG_CUDA(cudaMemsetAsync(q_count, 0, bm25_ctr_bytes(qc), st));
-                    const long long witems = items1 * BM25_SUBS;
-                    const long long wg = (witems + SUB_WARPS - 1) / SUB_WARPS;
-                    auto skern = filtered ? bm25_sub_kernel<true> : bm25_sub_kernel<false>;
-                    skern<<<(int)(wg < sm_count ? wg : sm_count), 32 * SUB_WARPS, sizeof(SubSmem), st>>>(
-                        block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms, k, q0, nq, stride, tau_scores, partial,
-                        q_count, q_flag, n_flagged, flt);
-                    SRAG_CUDA(cudaGetLastError());
-                    bm25_clear_flagged_kernel<<<nq, 256, 0, st>>>(partial, k, (uint32_t)nb * (uint32_t)k, q_flag, n_flagged);
-                    SRAG_CUDA(cudaGetLastError());
-                }
                 kern<<<grid1, BM25_CTA_THREADS, sizeof(Bm25Smem), st>>>(block_ptr, post_doc, post_imp, nb, n_sub, q_terms,
                                                                         max_terms, k, q0, nq, 1, stride, tau_scores, partial,
-                                                                        dbg, flt, n_docs, use_sub ? q_flag : nullptr,
-                                                                        use_sub ? n_flagged : nullptr);
+                                                                        dbg, flt, n_docs, nullptr, nullptr);
                 SRAG_CUDA(cudaGetLastError());
             }
         }
-        int rc = sub_path ? srag_launch_finalize_live(partial, (size_t)nb * k, nq, nb * k, k, nullptr, id_base,
-                                                      out_scores + (size_t)q0 * k, out_ids + (size_t)q0 * k, nullptr, 0,
-                                                      q_count, q_flag, k, st)
-                          : srag_launch_finalize(partial, nq, nb * k, k, nullptr, id_base, out_scores + (size_t)q0 * k,
-                                                 out_ids + (size_t)q0 * k, st);
+        int rc = srag_launch_finalize(partial, nq, nb * k, k, nullptr, id_base, out_scores + (size_t)q0 * k,
+                                      out_ids + (size_t)q0 * k, st);
         if (rc) return rc;
     }
     return SRAG_OK;
