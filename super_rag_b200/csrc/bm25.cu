@@ -3,17 +3,17 @@
 // Postings are CSR by term; block_ptr gives the first posting of every (term, BM25_SUB_DOCS = 2048 documents) slice.
 // Query terms are applied in ASCENDING term id; inside a term every posting hits a distinct document, so plain
 // (non-atomic) read-add-write is race-free and the per-document sum order is fixed -> bit-exact with oracle/bm25.py.
-// Selection is two-phase: a sample of the 16384-document blocks (every 32nd / 16th) gets an exact block top-k, its
-// k-th best score tau bounds the query's global k-th score from below, and the rest of the documents only report the
-// accumulators that cross tau.
+// Selection is two-pass: a SAMPLE pass over the sub-blocks of every 32nd / 16th block reports a few true document scores
+// per sampled sub-block, their k-th best tau bounds the query's global k-th score from below, and the MAIN pass over
+// all documents only reports the accumulators that cross tau.
 //
-//   bm25_items_kernel  sample phase (and: indexes too small to sample, queries flagged by bm25_sub_kernel). Persistent
-//                      CTAs (2 per SM) walk (query, 16384-document block) items; the block's fp32 accumulators live in
-//                      64 KB of shared memory; two producer warps stream the posting slices through a packed
-//                      shared-memory ring with 1-D bulk copies, eight consumer warps accumulate and select exactly.
-//   bm25_sub_kernel    phase 1, the bulk of the bytes: one WARP per (query, 2048-document sub-block), 8 KB of private
+//   bm25_sub_kernel    both passes, nearly all of the bytes: one WARP per (query, 2048-document sub-block), 8 KB of private
 //                      accumulators, no CTA barrier, no producer; documents crossing tau are appended to the query's
 //                      candidate region. Overflowing queries are flagged and redone by bm25_items_kernel.
+//   bm25_items_kernel  exact top-k of every (query, 16384-document block): indexes too small to sample, flagged queries
+//                      (and the whole of the first design, SRAG_BM25_SUBKERNEL=0). Persistent CTAs (2 per SM); the block's
+//                      fp32 accumulators live in 64 KB of shared memory; two producer warps stream the posting slices
+//                      through a packed shared-memory ring with 1-D bulk copies, eight consumer warps accumulate and select.
 //   bm25_bank_order_kernel  index build: permutes every slice so that the accumulator accesses of a warp fall on
 //                      distinct shared-memory banks (scores unchanged: the order inside a slice is free).
 //   srag_launch_finalize(_ex/_live) (topk_gemm.cu) merges the lists / candidate region of a query.
@@ -714,21 +714,22 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// bm25_sub_kernel: phase 1 (tau known) at WARP granularity. A work item is (query, sub-block of BM25_SUB_DOCS
-// documents); the sub-block's fp32 accumulators are 8 KB of shared memory private to ONE warp, so every add to a
-// document is made by the same warp: terms are applied in ascending order with nothing but __syncwarp() between
+// bm25_sub_kernel: scoring at WARP granularity (sample pass and main pass). A work item is (query, sub-block of
+// BM25_SUB_DOCS documents); the sub-block's fp32 accumulators are 8 KB of shared memory private to ONE warp, so every add
+// to a document is made by the same warp: terms are applied in ascending order with nothing but __syncwarp() between
 // rounds — no CTA barrier, no producer warps, no descriptor ring. 27 independent warps per SM walk the items
 // round-robin; neighbouring warps take neighbouring sub-blocks, i.e. neighbouring pieces of the same posting lists.
-//   * lane u holds the bounds of query term u inside the sub-block (block_ptr), fetched one item ahead (term ids two
-//     ahead), so no dependent load is waited for;
-//   * a round = 32 consecutive postings of one term (one coalesced load per array, L1 no-allocate); rounds of all
-//     terms form one stream in ascending-term order that is loaded SUB_DEPTH rounds ahead of the adds;
-//   * a document whose accumulator crosses tau is remembered (<= SUB_CAND per item); at the end of the item its
-//     final score goes into the query's candidate region — the query's slice of `partial`, filled from slot k up
-//     (slots 0..k-1 hold the sample's top-k) through one atomic counter per query. tau is the k-th best score of a
-//     1/stride sample, so a query collects about stride * k candidates over all its items;
+//   * lane u holds the bounds of query term u inside the sub-block (block_ptr), fetched two items ahead (term ids three
+//     ahead), so no dependent load is waited for; the next item's slices are pulled into L2 a whole item early;
+//   * a round = 128 postings of one term (one 16-byte load per lane and array, L1 no-allocate), or one NARROW round
+//     (one posting per lane) for a slice of up to 32 postings; the rounds of all terms form one stream in ascending-term
+//     order that is loaded SUB_DEPTH rounds ahead of the adds;
+//   * main pass: a document whose accumulator crosses tau is remembered (<= SUB_CAND per item); at the end of the item
+//     its final score goes into the query's candidate region — the query's slice of `partial`, filled from the front
+//     through one atomic counter per query. tau is the k-th best of the scores a 1/stride sample reported, so a query
+//     collects about stride * k candidates over all its items;
 //   * more crossings in one sub-block than SUB_CAND, or a full region, flags the QUERY; flagged queries are redone
-//     by bm25_items_kernel (exact per-block selection) after their region is cleared. Massive ties end up there.
+//     by bm25_items_kernel (exact top-k of every block) after their region is cleared. Massive ties end up there.
 // Per-document sums are formed exactly as in bm25_items_kernel: bit-exact with the oracle.
 constexpr int SUB_WARPS = 27;   // 27 x 8 KB of accumulators + candidate lists = 222 KB: one CTA per SM
 constexpr int SUB_CAND = 64;
