@@ -24,7 +24,7 @@ ls -la gpurun_out
 timeout 600 python tools/bench_hybrid.py --docs 10000000 --check 4 > gpurun_out/c3_c4.jsonl 2> gpurun_out/c3_c4.err; cat gpurun_out/c3_c4.jsonl | cut -c1-600
 CMD2="python tools/bench_hybrid.py --docs 4000000 --skip-c4 --check 0 --steps 1 --warmup 0"
 $CMD2 > gpurun_out/plain3.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:bm25_sub_kernel -s 0 -c 1 -f -o gpurun_out/prof_bm25 $CMD2 > gpurun_out/ncu_bm25.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:bm25_sub_kernel -s 1 -c 1 -f -o gpurun_out/prof_bm25 $CMD2 > gpurun_out/ncu_bm25.log 2>&1
 echo "ncu bm25 rc=$?"
 CMD3="python tools/bench_hybrid.py --docs 10000000 --skip-c4 --check 0 --steps 2 --warmup 1"
 $CMD3 > gpurun_out/plain4.log 2>&1 &&
