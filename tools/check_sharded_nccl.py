@@ -82,6 +82,24 @@ def main():
     torch.cuda.synchronize()
     ok_b = ok_b and bool(torch.equal(hi_ids, w_ids)) and bool(torch.equal(hi_sc, w_sc))
 
+    # the same on an index large enough for the two-pass warp-granular path on every shard (>= 32 blocks per shard)
+    n_big, vocab_b = 540_000 * world, 400
+    rngb = np.random.default_rng(5)
+    dlb = rngb.integers(4, 16, n_big)
+    pb = 1.0 / np.arange(1, vocab_b + 1)
+    tok_b = rngb.choice(vocab_b, size=int(dlb.sum()), p=pb / pb.sum()).astype(np.int64)
+    ptr_b = np.concatenate([[0], np.cumsum(dlb)]).astype(np.int64)
+    full_b = Bm25Index.from_tokens(torch.from_numpy(tok_b).to(dev), torch.from_numpy(ptr_b).to(dev), vocab_b)
+    stats_b = Bm25Stats(n_docs=n_big, df=full_b.stats.df, avgdl=full_b.stats.avgdl)
+    sb_b = ShardedBm25Index.from_tokens(torch.from_numpy(tok_b).to(dev), torch.from_numpy(ptr_b).to(dev), vocab_b, n_big,
+                                        stats_b, rank, world)
+    q_b = [rngb.integers(0, vocab_b, 6).tolist() for _ in range(96)]
+    qt_b = torch.from_numpy(prepare_query_terms(q_b, vocab_b)).to(dev)
+    bs_, bi_ = sb_b.search_terms(qt_b, 50)
+    ws_, wi_ = full_b.search_terms(qt_b, 50)
+    torch.cuda.synchronize()
+    ok_b = ok_b and bool(torch.equal(bi_, wi_)) and bool(torch.equal(bs_.view(torch.int32), ws_.view(torch.int32)))
+
     flags = torch.tensor([int(ok_v), int(ok_b)], device=dev)
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
