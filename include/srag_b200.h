@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define SRAG_ABI_VERSION 1
+#define SRAG_ABI_VERSION 2
 
 #define SRAG_OK              0
 #define SRAG_E_INVALID      -1   /* bad argument (null pointer, size, alignment, k) */
@@ -81,6 +81,16 @@ int srag_topk_search(const void* corpus_bf16, const float* row_scale, int64_t n_
                      const void* queries_bf16, const float* q_scale, int n_queries, int k,
                      int64_t id_base, float* out_scores, int64_t* out_ids,
                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same scan, additionally (or only: out_scores = out_ids = NULL) emitting the cross-shard EXCHANGE KEYS of SURVEY §8(e):
+ * out_keys uint64 [n_queries, k], key = orderable(final fp32 score) << 32 | (0xFFFFFFFF - (id_base + row)), 0 = empty
+ * slot, so that key descending <=> (score descending, id ascending). The finalize kernel writes them straight into
+ * the buffer the caller hands to the all-gather; srag_merge_keys consumes the gathered buffer. Needs
+ * id_base + n_rows < 2^32 - 1 (SRAG_E_INVALID otherwise: use out_scores / out_ids + srag_merge_candidates).       */
+int srag_topk_search_keys(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                          const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                          int64_t id_base, uint64_t* out_keys, float* out_scores, int64_t* out_ids,
+                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* Same scan with the metadata pre-filter the reference BUILDS but its connector drops
  * (ContextManager._create_combined_filter, super_rag/context/context.py:74-111;
@@ -194,6 +204,13 @@ int srag_mmr_rerank(const void* corpus_bf16, const float* row_scale, int64_t n_r
  * Final step after the all-gather of per-shard candidates.
  *   scores fp32 [n_shards, n_queries, kk], ids int64 same shape (id < 0 = padding)
  *   out_* [n_queries, k];  n_shards * kk <= 2048                                        */
+/* The same merge on exchange keys (srag_topk_search_keys / srag_pack_keys): keys uint64 [n_shards, n_queries, kk] as the
+ * all-gather leaves them; 8 bytes per candidate on the wire instead of 12.                                   */
+int srag_merge_keys(const uint64_t* keys, int n_shards, int n_queries, int kk, int k, float* out_scores,
+                    int64_t* out_ids, void* stream);
+/* (score, id) -> exchange key, for candidate lists that were not produced by srag_topk_search_keys (BM25 shards).
+ * ids must be < 2^32 - 1; *err_flag (device int, may be NULL) is set to 1 otherwise. id < 0 -> empty key.        */
+int srag_pack_keys(const float* scores, const int64_t* ids, int64_t n, uint64_t* keys, int* err_flag, void* stream);
 int srag_merge_candidates(const float* scores, const int64_t* ids, int n_shards, int n_queries,
                           int kk, int k, float* out_scores, int64_t* out_ids, void* stream);
 

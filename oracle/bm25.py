@@ -107,8 +107,9 @@ def bm25_scores_one(term_ptr, post_doc, post_imp, n_docs: int, query_terms):
     return acc, hit
 
 
-def bm25_topk(term_ptr, post_doc, post_imp, n_docs: int, queries, k: int, id_base: int = 0):
+def bm25_topk(term_ptr, post_doc, post_imp, n_docs: int, queries, k: int, id_base: int = 0, valid=None):
     """Top-k per query. ``queries`` is a list of term-id sequences (negative ids = padding).
+    ``valid``: optional bool [n_docs] — only these documents are candidates (metadata pre-filter; sums untouched).
 
     Returns (scores fp32 [B,k], ids int64 [B,k]) padded with (-inf, -1).
     """
@@ -117,6 +118,8 @@ def bm25_topk(term_ptr, post_doc, post_imp, n_docs: int, queries, k: int, id_bas
     out_i = np.full((B, k), -1, dtype=np.int64)
     for b, q in enumerate(queries):
         acc, hit = bm25_scores_one(term_ptr, post_doc, post_imp, n_docs, q)
+        if valid is not None:
+            hit = hit & np.asarray(valid, dtype=bool)
         ids = np.nonzero(hit)[0].astype(np.int64)
         s = acc[ids]
         if ids.size > 4 * k + 64:

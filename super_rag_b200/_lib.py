@@ -28,6 +28,7 @@ SIGNATURES = {
     "srag_topk_workspace_bytes": [_i64, _i32, _i32, C.POINTER(_sz)],
     "srag_topk_workspace_bytes_ex": [_i64, _i32, _i32, _i32, C.POINTER(_sz)],
     "srag_topk_search": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _sz, _vp],
+    "srag_topk_search_keys": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _sz, _vp],
     "srag_topk_search_filtered": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                   _sz, _vp],
     "srag_mmr_rerank": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp, _i32, _i64, _f32, _f32, _vp, _vp, _vp],
@@ -45,6 +46,8 @@ SIGNATURES = {
                                   _vp, _sz, _vp],
     "srag_fuse": [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _f64, C.POINTER(_f64), _i32, _vp, _vp, _vp],
     "srag_merge_candidates": [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
+    "srag_merge_keys": [_vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
+    "srag_pack_keys": [_vp, _vp, _i64, _vp, _vp, _vp],
 }
 _RESTYPE = {"srag_last_error": C.c_char_p}
 
@@ -78,7 +81,7 @@ def load():
             fn = getattr(lib, name)  # AttributeError if the header and the library disagree
             fn.argtypes = argtypes
             fn.restype = _RESTYPE.get(name, C.c_int)
-        if lib.srag_abi_version() != 1:
+        if lib.srag_abi_version() != 2:
             raise SragError(f"ABI version mismatch: library reports {lib.srag_abi_version()}")
         _lib = lib
     return _lib

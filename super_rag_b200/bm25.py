@@ -12,6 +12,7 @@ scoring and top-k are CUDA kernels.
 from __future__ import annotations
 
 import os
+import threading
 from dataclasses import dataclass
 from typing import Iterable, List, Optional, Sequence
 
@@ -58,6 +59,8 @@ class Bm25Index:
         self.n_docs, self.vocab, self.dl, self.stats, self.id_base = n_docs, vocab, dl, stats, id_base
         self.bank_ordered = bank_ordered
         self._ws = None
+        self._ws_event = None
+        self._lock = threading.Lock()   # the scoring workspace belongs to the index: one search at a time
 
     def _bank_order(self) -> None:
         """Permute every (term, doc-block) slice for conflict-free accumulation (ops.bm25_bank_order). Scores do not
@@ -168,11 +171,18 @@ class Bm25Index:
     def search_terms(self, q_terms: torch.Tensor, k: int, **filter_kw):
         """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids).
         filter_kw: doc_tags / q_tag_mask / doc_group / q_group (ops.bm25_search)."""
-        need = ops.bm25_workspace_bytes(self.n_docs, q_terms.shape[0], k)
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
-        return ops.bm25_search(self.block_ptr, self.post_doc, self.post_imp, self.n_docs, q_terms, k,
-                               id_base=self.id_base, workspace=self._ws, **filter_kw)
+        with self._lock:   # ctypes drops the GIL inside srag_*: two searches must not interleave on one workspace
+            need = ops.bm25_workspace_bytes(self.n_docs, q_terms.shape[0], k)
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            stream = torch.cuda.current_stream(self.device)
+            if self._ws_event is not None:   # ... nor overlap on it from two streams
+                stream.wait_event(self._ws_event)
+            out = ops.bm25_search(self.block_ptr, self.post_doc, self.post_imp, self.n_docs, q_terms, k,
+                                  id_base=self.id_base, workspace=self._ws, **filter_kw)
+            self._ws_event = torch.cuda.Event()
+            self._ws_event.record(stream)
+        return out
 
     def search(self, queries: Sequence[Iterable[int]], k: int, **filter_kw):
         qt = torch.from_numpy(prepare_query_terms(queries, self.vocab)).to(self.device)

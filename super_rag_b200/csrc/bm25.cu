@@ -1230,9 +1230,9 @@ extern "C" int srag_bm25_block_docs(void) { return BM25_SUB_DOCS; }
 extern "C" int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32_t* post_doc, const int32_t* post_tf,
                                  int64_t nnz, const float* idf, const int32_t* dl, float avgdl, float* post_imp,
                                  void* stream) {
-    SRAG_CHECK_ARG(nnz >= 0 && vocab >= 1 && avgdl > 0.f, "bad sizes nnz=%lld vocab=%d avgdl=%f", (long long)nnz,
-                   vocab, (double)avgdl);
-    if (nnz == 0) return SRAG_OK;
+    SRAG_CHECK_ARG(nnz >= 0 && vocab >= 1, "bad sizes nnz=%lld vocab=%d", (long long)nnz, vocab);
+    if (nnz == 0) return SRAG_OK;  // a collection whose texts all tokenise to nothing: avgdl = 0 is fine, no postings
+    SRAG_CHECK_ARG(avgdl > 0.f, "bad avgdl=%f with nnz=%lld", (double)avgdl, (long long)nnz);
     SRAG_CHECK_ARG(term_ptr && post_doc && post_tf && idf && dl && post_imp, "null pointer argument");
     int64_t blocks = (nnz + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
@@ -1328,27 +1328,22 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
         srag_set_error("workspace too small: %zu < %zu", workspace_bytes, need);
         return SRAG_E_WORKSPACE;
     }
-    static bool attr_done = false;
-    static int sm_count = 0;
-    if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(Bm25Smem)));
-        SRAG_CUDA(cudaFuncSetAttribute(bm25_items_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(Bm25Smem)));
-        SRAG_CUDA(cudaFuncSetAttribute(bm25_sub_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(SubSmem)));
-        SRAG_CUDA(cudaFuncSetAttribute(bm25_sub_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(SubSmem)));
-        int dev = 0;
-        SRAG_CUDA(cudaGetDevice(&dev));
-        SRAG_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-        attr_done = true;
+    int sm_count = 0;
+    {
+        int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_items_kernel<false>), (int)sizeof(Bm25Smem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_items_kernel<true>), (int)sizeof(Bm25Smem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<false>), (int)sizeof(SubSmem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<true>), (int)sizeof(SubSmem));
+        if (!rc) rc = srag_current_device_props(&sm_count, nullptr, nullptr);
+        if (rc) return rc;
     }
     uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
     uint64_t* partial = reinterpret_cast<uint64_t*>(ws);
     uint64_t* sample = reinterpret_cast<uint64_t*>(ws + bm25_partial_bytes(qc, nb, k));
-    float* tau_scores = reinterpret_cast<float*>(ws + bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k));
-    int64_t* tau_ids = reinterpret_cast<int64_t*>(tau_scores + (size_t)qc * k);
+    // ids first: the region starts 256-byte aligned, so the 8-byte id stores of the finalize kernel stay aligned for any
+    // qc * k (scores first put the ids on a 4-byte boundary whenever qc * k was odd, e.g. B = 1, k = 5)
+    int64_t* tau_ids = reinterpret_cast<int64_t*>(ws + bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k));
+    float* tau_scores = reinterpret_cast<float*>(tau_ids + (size_t)qc * k);
     uint32_t* q_count = reinterpret_cast<uint32_t*>(ws + bm25_partial_bytes(qc, nb, k) + bm25_sample_bytes(qc, nb, k) +
                                                     bm25_tau_bytes(qc, k));
     uint32_t* q_flag = q_count + qc;

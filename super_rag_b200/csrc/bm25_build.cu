@@ -290,13 +290,12 @@ extern "C" int srag_bm25_build_plan(int32_t* tokens, const int64_t* doc_ptr, int
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     int n_sub = (int)((n_docs + BUILD_SUB_DOCS - 1) / BUILD_SUB_DOCS);
     if (n_sub < 1) n_sub = 1;
-    static bool attr_done = false;
-    if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(build_doc_terms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       BUILD_LONG_DL * (int)sizeof(uint32_t)));
-        SRAG_CUDA(cudaFuncSetAttribute(build_sort_slices_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       SORT_WARPS * BUILD_SUB_DOCS * (int)sizeof(unsigned long long)));
-        attr_done = true;
+    {
+        int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&build_doc_terms_kernel),
+                                      BUILD_LONG_DL * (int)sizeof(uint32_t));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&build_sort_slices_kernel),
+                                           SORT_WARPS * BUILD_SUB_DOCS * (int)sizeof(unsigned long long));
+        if (rc) return rc;
     }
     unsigned long long* cnt = reinterpret_cast<unsigned long long*>(block_ptr);
     SRAG_CUDA(cudaMemsetAsync(cnt, 0, (size_t)vocab * (n_sub + 1) * sizeof(unsigned long long), st));

@@ -12,6 +12,11 @@
 // host-side error plumbing (api.cu owns the storage)
 // ---------------------------------------------------------------------------------------
 void srag_set_error(const char* fmt, ...);
+// api.cu: per-DEVICE caches (one process may drive several GPUs), mutex-guarded.
+//   srag_func_smem_optin: cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, current device)
+//   srag_current_device_props: SM count / compute capability of the current device
+int srag_func_smem_optin(const void* func, int bytes);
+int srag_current_device_props(int* sms, int* major, int* minor);
 
 // topk_gemm.cu: per-query lists of sortable keys [n_queries][total] -> sorted top-k (k <= 256)
 int srag_launch_finalize(const uint64_t* partial, int n_queries, int total, int k, const float* q_scale,
@@ -27,6 +32,12 @@ int srag_launch_finalize_live(const uint64_t* partial, size_t src_stride, int n_
                               const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
                               uint64_t* out_keys, size_t out_keys_stride, const uint32_t* live_count,
                               const uint32_t* live_all, int live_base, cudaStream_t st);
+
+// same, plus (optionally) the cross-shard exchange keys: pack(final score bits, id_base + row) per slot, 0 = empty
+int srag_launch_finalize_gkeys(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                               const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                               uint64_t* out_keys, size_t out_keys_stride, const uint32_t* live_count,
+                               const uint32_t* live_all, int live_base, uint64_t* out_gkeys, cudaStream_t st);
 
 #define SRAG_CHECK_ARG(cond, ...)                 \
     do {                                          \
@@ -57,6 +68,8 @@ __host__ __device__ __forceinline__ uint32_t srag_f32_from_orderable(uint32_t o)
     return (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
 }
 __host__ __device__ __forceinline__ uint64_t srag_pack_key(uint32_t score_bits, uint32_t idx) {
+    // -0.0 == +0.0 as scores (a zero query, a zero row): one pattern, so that such ties fall back to the id like the oracle's
+    if (score_bits == 0x80000000u) score_bits = 0u;
     return ((uint64_t)srag_f32_orderable(score_bits) << 32) | (uint64_t)(0xFFFFFFFFu - idx);
 }
 __host__ __device__ __forceinline__ uint32_t srag_key_score_bits(uint64_t key) {

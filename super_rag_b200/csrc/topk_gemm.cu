@@ -27,6 +27,8 @@
 //              any dim.
 #include <cuda.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -586,7 +588,8 @@ __global__ void __launch_bounds__(FIN_THREADS)
 topk_finalize_kernel(const uint64_t* __restrict__ partial, size_t src_stride, int total_max /* lists * k */, int k, int kcap,
                      int P, const float* __restrict__ q_scale, int64_t id_base, float* __restrict__ out_scores,
                      int64_t* __restrict__ out_ids, uint64_t* __restrict__ out_keys, size_t out_keys_stride,
-                     const uint32_t* __restrict__ live_count, const uint32_t* __restrict__ live_all, int live_base) {
+                     const uint32_t* __restrict__ live_count, const uint32_t* __restrict__ live_all, int live_base,
+                     uint64_t* __restrict__ out_gkeys /* [n_queries][k] exchange keys (final score, global id), or null */) {
     extern __shared__ uint64_t fin_keys[];
     __shared__ int fin_count;
     const int q = blockIdx.x;
@@ -658,8 +661,12 @@ topk_finalize_kernel(const uint64_t* __restrict__ partial, size_t src_stride, in
             s = __uint_as_float(srag_key_score_bits(key)) * qs;
             id = id_base + (int64_t)srag_key_idx(key);
         }
-        out_scores[(size_t)q * k + j] = s;
-        out_ids[(size_t)q * k + j] = id;
+        if (out_scores) out_scores[(size_t)q * k + j] = s;
+        if (out_ids) out_ids[(size_t)q * k + j] = id;
+        // the cross-shard exchange format: ONE sortable 64-bit key per candidate, carrying the final
+        // score bits and the GLOBAL row, written straight into the all-gather send buffer
+        if (out_gkeys)
+            out_gkeys[(size_t)q * k + j] = id >= 0 ? srag_pack_key(__float_as_uint(s), (uint32_t)id) : SRAG_KEY_EMPTY;
     }
 }
 
@@ -717,21 +724,13 @@ struct Plan {
 };
 
 int device_sm_count(int* sms) {
-    static int cached_dev = -1, cached_sms = 0, cached_major = 0;
-    int dev = 0;
-    SRAG_CUDA(cudaGetDevice(&dev));
-    if (dev != cached_dev) {
-        cudaDeviceProp prop;
-        SRAG_CUDA(cudaGetDeviceProperties(&prop, dev));
-        cached_dev = dev;
-        cached_sms = prop.multiProcessorCount;
-        cached_major = prop.major;
-    }
-    if (cached_major != 10) {
-        srag_set_error("device compute capability %d.x is not sm_100", cached_major);
+    int major = 0;
+    const int rc = srag_current_device_props(sms, &major, nullptr);
+    if (rc) return rc;
+    if (major != 10) {
+        srag_set_error("device compute capability %d.x is not sm_100", major);
         return SRAG_E_UNSUPPORTED;
     }
-    *sms = cached_sms;
     return SRAG_OK;
 }
 
@@ -782,18 +781,28 @@ constexpr int PROF_RING = 256;
 struct ProfState {
     bool on = false;
     int n = 0;
+    int dev = -1;  // events belong to the device that was current at srag_prof_enable(1); other devices are not timed
     cudaEvent_t ev[PROF_RING][3];
     bool created = false;
 } g_prof;
+std::mutex g_prof_mu;  // the ABI may be entered from several host threads
+
+// Claims the next event triple when profiling is on for the current device; -1 otherwise.
+int prof_claim() {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!g_prof.on || g_prof.n >= PROF_RING) return -1;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != g_prof.dev) return -1;
+    return g_prof.n++;
+}
 
 template <int G, bool RQ, int EW, bool FILT = false>
 int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, const TopkParams& prm,
                 cudaStream_t st) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        SRAG_CUDA(cudaFuncSetAttribute(topk_gemm_kernel<G, RQ, EW, FILT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem_bytes<G, RQ>()));
-        attr_done = true;
+    {
+        const int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&topk_gemm_kernel<G, RQ, EW, FILT>),
+                                            (int)smem_bytes<G, RQ>());
+        if (rc) return rc;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(pl.grid);
@@ -852,9 +861,11 @@ extern "C" int srag_topk_workspace_bytes_ex(int64_t n_rows, int dim, int n_queri
 static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
                             const void* queries_bf16, const float* q_scale, int n_queries, int k, int64_t id_base,
                             const uint32_t* row_tags, const int32_t* row_group, const uint32_t* q_tag_mask,
-                            const int32_t* q_group, float* out_scores, int64_t* out_ids, void* workspace,
-                            size_t workspace_bytes, void* stream) {
-    SRAG_CHECK_ARG(queries_bf16 && out_scores && out_ids && workspace, "null pointer argument");
+                            const int32_t* q_group, float* out_scores, int64_t* out_ids, uint64_t* out_gkeys,
+                            void* workspace, size_t workspace_bytes, void* stream) {
+    SRAG_CHECK_ARG(queries_bf16 && workspace && ((out_scores && out_ids) || out_gkeys), "null pointer argument");
+    SRAG_CHECK_ARG(!out_gkeys || (id_base >= 0 && id_base + n_rows <= (int64_t)0xFFFFFFFEll),
+                   "exchange keys hold 32-bit global rows: id_base + n_rows = %lld does not fit", (long long)(id_base + n_rows));
     SRAG_CHECK_ARG((row_tags == nullptr) == (q_tag_mask == nullptr) && (row_group == nullptr) == (q_group == nullptr),
                    "row_tags / q_tag_mask and row_group / q_group come in pairs");
     SRAG_CHECK_ARG(n_rows == 0 || (corpus_bf16 && row_scale), "null corpus / row_scale");
@@ -908,8 +919,9 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
     prm.q_tag_mask = q_tag_mask;
     prm.q_group = q_group;
     SRAG_CUDA(cudaMemsetAsync(prm.partial, 0, pl.partial_bytes + pl.gthr_bytes + pl.progress_bytes, st));
-    const bool prof = g_prof.on && g_prof.n < PROF_RING;
-    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][0], st));
+    const int prof_slot = prof_claim();
+    const bool prof = prof_slot >= 0;
+    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[prof_slot][0], st));
     if (n_rows > 0) {
         CUtensorMap tq, tc;
         // zero-padded copy of the queries when the batch is not whole q-tiles and the caller sized the
@@ -952,14 +964,14 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
         }
         if (rc) return rc;
     }
-    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][1], st));
-    rc = srag_launch_finalize(prm.partial, n_queries, pl.num_slabs * (ew / 4) * heap_stride(k), k, q_scale, id_base, out_scores, out_ids,
-                              st);
-    if (rc) return rc;
-    if (prof) {
-        SRAG_CUDA(cudaEventRecord(g_prof.ev[g_prof.n][2], st));
-        ++g_prof.n;
+    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[prof_slot][1], st));
+    {
+        const int total = pl.num_slabs * (ew / 4) * heap_stride(k);
+        rc = srag_launch_finalize_gkeys(prm.partial, (size_t)total, n_queries, total, k, q_scale, id_base, out_scores, out_ids,
+                                        nullptr, 0, nullptr, nullptr, 0, out_gkeys, st);
     }
+    if (rc) return rc;
+    if (prof) SRAG_CUDA(cudaEventRecord(g_prof.ev[prof_slot][2], st));
     return SRAG_OK;
 }
 
@@ -968,7 +980,17 @@ extern "C" int srag_topk_search(const void* corpus_bf16, const float* row_scale,
                                 int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
                                 size_t workspace_bytes, void* stream) {
     return topk_search_impl(corpus_bf16, row_scale, n_rows, dim, queries_bf16, q_scale, n_queries, k, id_base, nullptr,
-                            nullptr, nullptr, nullptr, out_scores, out_ids, workspace, workspace_bytes, stream);
+                            nullptr, nullptr, nullptr, out_scores, out_ids, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int srag_topk_search_keys(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                                     const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                                     int64_t id_base, uint64_t* out_keys, float* out_scores, int64_t* out_ids,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+    SRAG_CHECK_ARG(out_keys != nullptr, "out_keys is null");
+    SRAG_CHECK_ARG((out_scores == nullptr) == (out_ids == nullptr), "out_scores / out_ids come together (or both NULL)");
+    return topk_search_impl(corpus_bf16, row_scale, n_rows, dim, queries_bf16, q_scale, n_queries, k, id_base, nullptr,
+                            nullptr, nullptr, nullptr, out_scores, out_ids, out_keys, workspace, workspace_bytes, stream);
 }
 
 extern "C" int srag_topk_search_filtered(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
@@ -977,14 +999,23 @@ extern "C" int srag_topk_search_filtered(const void* corpus_bf16, const float* r
                                          const uint32_t* q_tag_mask, const int32_t* q_group, float* out_scores,
                                          int64_t* out_ids, void* workspace, size_t workspace_bytes, void* stream) {
     return topk_search_impl(corpus_bf16, row_scale, n_rows, dim, queries_bf16, q_scale, n_queries, k, id_base, row_tags,
-                            row_group, q_tag_mask, q_group, out_scores, out_ids, workspace, workspace_bytes, stream);
+                            row_group, q_tag_mask, q_group, out_scores, out_ids, nullptr, workspace, workspace_bytes, stream);
 }
 
 extern "C" int srag_prof_enable(int on) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    int dev = 0;
+    SRAG_CUDA(cudaGetDevice(&dev));
+    if (on && g_prof.created && g_prof.dev != dev) {  // re-home the events on the device now current
+        for (int i = 0; i < PROF_RING; ++i)
+            for (int j = 0; j < 3; ++j) cudaEventDestroy(g_prof.ev[i][j]);
+        g_prof.created = false;
+    }
     if (on && !g_prof.created) {
         for (int i = 0; i < PROF_RING; ++i)
             for (int j = 0; j < 3; ++j) SRAG_CUDA(cudaEventCreate(&g_prof.ev[i][j]));
         g_prof.created = true;
+        g_prof.dev = dev;
     }
     g_prof.on = on != 0;
     g_prof.n = 0;
@@ -992,6 +1023,7 @@ extern "C" int srag_prof_enable(int on) {
 }
 
 extern "C" int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int* n_calls) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
     double a = 0, b = 0;
     for (int i = 0; i < g_prof.n; ++i) {
         float x = 0, y = 0;
@@ -1012,18 +1044,25 @@ int srag_launch_finalize_live(const uint64_t* partial, size_t src_stride, int n_
                               const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
                               uint64_t* out_keys, size_t out_keys_stride, const uint32_t* live_count,
                               const uint32_t* live_all, int live_base, cudaStream_t st) {
+    return srag_launch_finalize_gkeys(partial, src_stride, n_queries, total, k, q_scale, id_base, out_scores, out_ids,
+                                      out_keys, out_keys_stride, live_count, live_all, live_base, nullptr, st);
+}
+
+int srag_launch_finalize_gkeys(const uint64_t* partial, size_t src_stride, int n_queries, int total, int k,
+                               const float* q_scale, int64_t id_base, float* out_scores, int64_t* out_ids,
+                               uint64_t* out_keys, size_t out_keys_stride, const uint32_t* live_count,
+                               const uint32_t* live_all, int live_base, uint64_t* out_gkeys, cudaStream_t st) {
     const int kcap = (k <= 128) ? 128 : 256;
     int P = 2 * kcap;
     while (P < total + kcap && P < FIN_MAX_P) P <<= 1;
-    static bool fin_attr = false;
-    if (!fin_attr) {
-        SRAG_CUDA(cudaFuncSetAttribute(topk_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       FIN_MAX_P * (int)sizeof(uint64_t)));
-        fin_attr = true;
+    {
+        const int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&topk_finalize_kernel),
+                                            FIN_MAX_P * (int)sizeof(uint64_t));
+        if (rc) return rc;
     }
     topk_finalize_kernel<<<n_queries, FIN_THREADS, (size_t)P * sizeof(uint64_t), st>>>(
         partial, src_stride, total, k, kcap, P, q_scale, id_base, out_scores, out_ids, out_keys, out_keys_stride, live_count,
-        live_all, live_base);
+        live_all, live_base, out_gkeys);
     SRAG_CUDA(cudaGetLastError());
     return SRAG_OK;
 }

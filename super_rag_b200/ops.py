@@ -89,8 +89,12 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
                 k: int, id_base: int = 0, workspace: Optional[torch.Tensor] = None,
                 out_scores: Optional[torch.Tensor] = None, out_ids: Optional[torch.Tensor] = None,
                 row_tags: Optional[torch.Tensor] = None, q_tag_mask: Optional[torch.Tensor] = None,
-                row_group: Optional[torch.Tensor] = None, q_group: Optional[torch.Tensor] = None):
+                row_group: Optional[torch.Tensor] = None, q_group: Optional[torch.Tensor] = None,
+                out_keys: Optional[torch.Tensor] = None, keys_only: bool = False):
     """Exact top-k of bf16 queries [B,D] against a bf16 corpus [N,D]; returns (scores fp32 [B,k], ids int64 [B,k]).
+
+    `out_keys` (int64 [B,k] holding uint64 bit patterns): also emit the cross-shard exchange keys (srag_topk_search_keys);
+    with `keys_only` scores / ids are not written and (None, None) is returned.
 
     Optional metadata pre-filter (int32 tensors holding 32-bit patterns): row r is eligible for query b iff
     ``row_tags[r] & q_tag_mask[b] != 0`` (when given) and ``q_group[b] < 0 or row_group[r] == q_group[b]`` (when given)."""
@@ -104,6 +108,12 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
             if t.dtype != torch.int32 or t.numel() != n_expect or not t.is_contiguous():
                 raise SragError(f"{what} must be a contiguous int32 tensor of {n_expect} elements")
     filtered = row_tags is not None or row_group is not None
+    if out_keys is not None:
+        _need_cuda(out_keys)
+        if filtered:
+            raise SragError("exchange keys are not available with the metadata filter")
+        if out_keys.dtype != torch.int64 or tuple(out_keys.shape) != (queries.shape[0], k) or not out_keys.is_contiguous():
+            raise SragError("out_keys must be a contiguous int64 [B, k] tensor")
     if corpus.dtype != torch.bfloat16 or queries.dtype != torch.bfloat16:
         raise SragError("corpus and queries must be bfloat16 (use ingest_rows)")
     lib = _lib.load()
@@ -113,8 +123,11 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
         raise SragError(f"dimension mismatch: corpus {tuple(corpus.shape)} vs queries {tuple(queries.shape)}")
     dev = queries.device
     with torch.cuda.device(dev):
-        scores = out_scores if out_scores is not None else torch.empty(B, k, dtype=torch.float32, device=dev)
-        ids = out_ids if out_ids is not None else torch.empty(B, k, dtype=torch.int64, device=dev)
+        want_pairs = not (keys_only and out_keys is not None)
+        scores = ids = None
+        if want_pairs:
+            scores = out_scores if out_scores is not None else torch.empty(B, k, dtype=torch.float32, device=dev)
+            ids = out_ids if out_ids is not None else torch.empty(B, k, dtype=torch.int64, device=dev)
         for b0 in range(0, B, MAX_QUERIES_PER_CALL):
             nb = min(MAX_QUERIES_PER_CALL, B - b0)
             need = topk_workspace_bytes(N, nb, k, D)
@@ -127,6 +140,13 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
                     _ptr(row_tags), _ptr(row_group), _ptr(q_tag_mask[b0:b0 + nb] if q_tag_mask is not None else None),
                     _ptr(q_group[b0:b0 + nb] if q_group is not None else None), _ptr(scores[b0:b0 + nb]),
                     _ptr(ids[b0:b0 + nb]), _ptr(workspace), workspace.numel(), _stream(dev)), "srag_topk_search_filtered")
+                continue
+            if out_keys is not None:
+                _lib.check(lib.srag_topk_search_keys(
+                    _ptr(corpus), _ptr(row_scale), N, D, _ptr(q), _ptr(q_scale[b0:b0 + nb]), nb, k, id_base,
+                    _ptr(out_keys[b0:b0 + nb]), _ptr(scores[b0:b0 + nb] if want_pairs else None),
+                    _ptr(ids[b0:b0 + nb] if want_pairs else None), _ptr(workspace), workspace.numel(), _stream(dev)),
+                    "srag_topk_search_keys")
                 continue
             _lib.check(lib.srag_topk_search(_ptr(corpus), _ptr(row_scale), N, D, _ptr(q), _ptr(q_scale[b0:b0 + nb]),
                                             nb, k, id_base, _ptr(scores[b0:b0 + nb]), _ptr(ids[b0:b0 + nb]),
@@ -333,3 +353,31 @@ def merge_candidates(scores: torch.Tensor, ids: torch.Tensor, k: int):
         _lib.check(lib.srag_merge_candidates(_ptr(scores.contiguous()), _ptr(ids.contiguous()), G, B, KK, k,
                                              _ptr(os_), _ptr(oi), _stream(dev)), "srag_merge_candidates")
     return os_, oi
+
+
+def merge_keys(keys: torch.Tensor, k: int, out_scores: Optional[torch.Tensor] = None,
+               out_ids: Optional[torch.Tensor] = None):
+    """keys int64 [G, B, KK] (uint64 exchange-key bit patterns, as all-gathered) -> global top-k (scores [B,k], ids [B,k])."""
+    _need_cuda(keys)
+    if keys.dtype != torch.int64 or keys.ndim != 3 or not keys.is_contiguous():
+        raise SragError("keys must be a contiguous int64 [G, B, KK] tensor")
+    G, B, KK = keys.shape
+    dev = keys.device
+    with torch.cuda.device(dev):
+        os_ = out_scores if out_scores is not None else torch.empty(B, k, dtype=torch.float32, device=dev)
+        oi = out_ids if out_ids is not None else torch.empty(B, k, dtype=torch.int64, device=dev)
+        _lib.check(_lib.load().srag_merge_keys(_ptr(keys), G, B, KK, k, _ptr(os_), _ptr(oi), _stream(dev)), "srag_merge_keys")
+    return os_, oi
+
+
+def pack_keys(scores: torch.Tensor, ids: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(fp32 scores, int64 ids < 2^32 - 1; id < 0 = empty) -> int64 tensor of exchange-key bit patterns, same shape."""
+    _need_cuda(scores, ids)
+    if scores.dtype != torch.float32 or ids.dtype != torch.int64 or scores.shape != ids.shape:
+        raise SragError("pack_keys wants fp32 scores and int64 ids of one shape")
+    dev = ids.device
+    with torch.cuda.device(dev):
+        keys = out if out is not None else torch.empty(ids.shape, dtype=torch.int64, device=dev)
+        _lib.check(_lib.load().srag_pack_keys(_ptr(scores.contiguous()), _ptr(ids.contiguous()), ids.numel(), _ptr(keys),
+                                              _ptr(None), _stream(dev)), "srag_pack_keys")
+    return keys

@@ -8,6 +8,7 @@ The reference has no collective to compare with.
 """
 from __future__ import annotations
 
+import threading
 from typing import Optional, Tuple
 
 import torch
@@ -19,37 +20,78 @@ def shard_range(n_rows: int, world: int, rank: int) -> Tuple[int, int]:
     return (rank * n_rows) // world, ((rank + 1) * n_rows) // world
 
 
-def pack_candidates(scores: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
-    """(fp32 [B,k], int64 [B,k]) -> int64 [2,B,k]: plane 0 holds the score bits, plane 1 the ids."""
-    out = torch.empty((2,) + tuple(ids.shape), dtype=torch.int64, device=ids.device)
-    out[0] = scores.contiguous().view(torch.int32).to(torch.int64)
-    out[1] = ids
+KEY_ID_LIMIT = 0xFFFFFFFE   # exchange keys carry 32-bit global rows (srag_topk_search_keys)
+_M32 = 0xFFFFFFFF
+
+
+def pack_keys_torch(scores: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
+    """(fp32 [..], int64 [..]) -> int64 [..] exchange keys (uint64 bit patterns): orderable(score) << 32 | (2^32-1 - id),
+    0 for an empty slot (id < 0). Plain torch integer ops, any device: the host-side statement of what
+    `topk_finalize_kernel` / `srag_pack_keys` emit; the world_size-2 gloo tests run it on CPU tensors."""
+    bits = scores.contiguous().view(torch.int32).to(torch.int64) & _M32
+    bits = torch.where(bits == 0x80000000, torch.zeros_like(bits), bits)     # -0.0 -> +0.0, as srag_pack_key does
+    orderable = torch.where((bits >> 31) != 0, (~bits) & _M32, bits | 0x80000000)
+    hi = orderable - ((orderable >> 31) << 32)            # as a signed 32-bit value, so that << 32 cannot overflow
+    key = (hi << 32) | ((_M32 - ids) & _M32)
+    return torch.where(ids >= 0, key, torch.zeros_like(key))
+
+
+def unpack_keys_torch(keys: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Inverse of pack_keys_torch: int64 keys -> (fp32 scores, int64 ids); empty -> (-inf, -1)."""
+    orderable = (keys >> 32) & _M32
+    bits = torch.where((orderable >> 31) != 0, orderable & 0x7FFFFFFF, (~orderable) & _M32)
+    bits = bits - ((bits >> 31) << 32)
+    scores = bits.to(torch.int32).view(torch.float32)
+    ids = _M32 - (keys & _M32)
+    empty = keys == 0
+    return (torch.where(empty, torch.full_like(scores, float("-inf")), scores),
+            torch.where(empty, torch.full_like(ids, -1), ids))
+
+
+def gather_keys(keys: torch.Tensor, group=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """All-gather every rank's [B,k] exchange keys -> [g,B,k] on every rank: ONE collective of 8 bytes per candidate
+    (80 KiB per rank at B = 1024, k = 10). NCCL for device tensors, gloo for the CPU tests."""
+    world = dist.get_world_size(group)
+    B, k = keys.shape
+    if out is None:
+        out = torch.empty((world, B, k), dtype=torch.int64, device=keys.device)
+    dist.all_gather_into_tensor(out.view(world * B, k), keys, group=group)
     return out
-
-
-def unpack_candidates(packed: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-    """int64 [g,2,B,k] -> (scores fp32 [g,B,k], ids int64 [g,B,k])."""
-    scores = packed[:, 0].to(torch.int32).contiguous().view(torch.float32)
-    ids = packed[:, 1].contiguous()
-    return scores, ids
 
 
 def exchange_candidates(scores: torch.Tensor, ids: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
     """All-gather every rank's [B,k] candidates -> ([g,B,k] scores, [g,B,k] ids) on every rank.
-    Works on NCCL (device tensors) and gloo (CPU tensors: the world_size-2 CPU tests)."""
+    Works on NCCL (device tensors) and gloo (CPU tensors: the world_size-2 CPU tests). Ids beyond the 32-bit key
+    range travel as two planes (score bits, ids) instead."""
     world = dist.get_world_size(group)
-    packed = pack_candidates(scores, ids)
-    # concatenation along dim 0 is the one output layout both NCCL and gloo accept
-    gathered = torch.empty((world * packed.shape[0],) + tuple(packed.shape[1:]), dtype=torch.int64,
-                           device=packed.device)
+    if int(ids.max().item() if ids.numel() else 0) < KEY_ID_LIMIT:
+        if ids.is_cuda:
+            from . import ops
+            keys = ops.pack_keys(scores.contiguous(), ids.contiguous())
+        else:
+            keys = pack_keys_torch(scores, ids)
+        return unpack_keys_torch(gather_keys(keys, group))
+    packed = torch.empty((2,) + tuple(ids.shape), dtype=torch.int64, device=ids.device)
+    packed[0] = scores.contiguous().view(torch.int32).to(torch.int64)
+    packed[1] = ids
+    gathered = torch.empty((world * 2,) + tuple(ids.shape), dtype=torch.int64, device=ids.device)
     dist.all_gather_into_tensor(gathered, packed, group=group)
-    return unpack_candidates(gathered.view((world,) + tuple(packed.shape)))
+    gathered = gathered.view((world, 2) + tuple(ids.shape))
+    return gathered[:, 0].to(torch.int32).contiguous().view(torch.float32), gathered[:, 1].contiguous()
 
 
 class ShardedVectorIndex:
-    """This rank's shard of a row-sharded corpus plus the exchange + merge step."""
+    """This rank's shard of a row-sharded corpus plus the exchange + merge step.
+
+    One step on N > 1 GPUs is: workspace memset, K1 (fused GEMM + top-k), the finalize kernel — which writes the
+    per-shard candidates as 64-bit exchange keys STRAIGHT INTO the all-gather send buffer —, one NCCL all-gather,
+    and the K4 merge kernel reading the gathered keys. Round 1 went through six torch elementwise launches to pack
+    and unpack (scores widened to int64, 16 bytes per candidate) around the collective; they cost more than the
+    collective itself. With `SRAG_SHARDED_GRAPH=1` the whole step is captured once per (batch, k) into a CUDA graph
+    and replayed (queries then live in fixed buffers owned by the index)."""
 
     def __init__(self, rows_bf16: torch.Tensor, row_scale: torch.Tensor, id_base: int, metric="cosine", group=None):
+        import os
         from . import ops
         self.ops = ops
         # the kernels want 16-byte aligned bases; a row slice of a larger tensor need not be
@@ -62,28 +104,97 @@ class ShardedVectorIndex:
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self._ws: Optional[torch.Tensor] = None
+        self._ws_event = None
+        self._lock = threading.Lock()   # the scan workspace belongs to the index: one search at a time
+        # exchange keys need every shard's global rows below 2^32 - 1; all ranks must take the same branch
+        fits = self.id_base >= 0 and self.id_base + self.rows.shape[0] < KEY_ID_LIMIT
+        if self.world > 1:
+            flag = torch.tensor([int(fits)], dtype=torch.int32, device=self.rows.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            fits = bool(flag.item())
+        self.use_keys = fits
+        self.use_graph = self.world > 1 and fits and os.environ.get("SRAG_SHARDED_GRAPH", "0") == "1"
+        self._bufs = {}     # (B, k) -> (send keys [B,k], gathered keys [g,B,k])
+        self._graphs = {}   # (B, k) -> (graph, static q_bf16, static q_scale, out scores, out ids)
 
-    def local_topk(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
-        need = self.ops.topk_workspace_bytes(self.rows.shape[0], min(q_bf16.shape[0], self.ops.MAX_QUERIES_PER_CALL), k, self.rows.shape[1])
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=self.rows.device)
-        return self.ops.topk_search(self.rows, self.row_scale, q_bf16, q_scale, k, id_base=self.id_base,
-                                    workspace=self._ws)
+    def local_topk(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int, out_keys: Optional[torch.Tensor] = None):
+        capturing = torch.cuda.is_current_stream_capturing()
+        with self._lock:
+            need = self.ops.topk_workspace_bytes(self.rows.shape[0], min(q_bf16.shape[0], self.ops.MAX_QUERIES_PER_CALL), k, self.rows.shape[1])
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=self.rows.device)
+            stream = torch.cuda.current_stream(self.rows.device)
+            if self._ws_event is not None and not capturing:
+                stream.wait_event(self._ws_event)
+            out = self.ops.topk_search(self.rows, self.row_scale, q_bf16, q_scale, k, id_base=self.id_base,
+                                       workspace=self._ws, out_keys=out_keys, keys_only=out_keys is not None)
+            if not capturing:
+                self._ws_event = torch.cuda.Event()
+                self._ws_event.record(stream)
+        return out
+
+    def _step(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
+        """local scan -> exchange -> merge, on the current stream."""
+        if not self.use_keys:
+            s, i = self.local_topk(q_bf16, q_scale, k)
+            gs, gi = exchange_candidates(s, i, self.group)
+            return self.ops.merge_candidates(gs, gi, k)
+        B = q_bf16.shape[0]
+        bufs = self._bufs.get((B, k))
+        if bufs is None:
+            dev = self.rows.device
+            bufs = (torch.empty(B, k, dtype=torch.int64, device=dev), torch.empty(self.world, B, k, dtype=torch.int64, device=dev))
+            self._bufs[(B, k)] = bufs
+        send, recv = bufs
+        self.local_topk(q_bf16, q_scale, k, out_keys=send)
+        gather_keys(send, self.group, out=recv)
+        return self.ops.merge_keys(recv, k)
 
     def search_device(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
         """Queries already resident (bf16 + multipliers, replicated on every rank)."""
-        s, i = self.local_topk(q_bf16, q_scale, k)
         if self.world == 1:
-            return s, i
-        gs, gi = exchange_candidates(s, i, self.group)
-        return self.ops.merge_candidates(gs, gi, k)
+            return self.local_topk(q_bf16, q_scale, k)
+        if not self.use_graph:
+            return self._step(q_bf16, q_scale, k)
+        return self._replay(q_bf16, q_scale, k)
+
+    def _replay(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int):
+        """CUDA-graph path: the step is captured once per (B, k) over fixed query buffers; later calls copy the
+        queries in (a no-op when the caller already wrote them there, see `query_buffers`) and replay. The returned
+        tensors are the graph's own outputs: consume them before the next search of the same shape."""
+        key = (q_bf16.shape[0], k)
+        ent = self._graphs.get(key)
+        if ent is None:
+            sq, ss = q_bf16.clone(), q_scale.clone()
+            self._step(sq, ss, k)                       # warm-up outside capture: workspace, buffers, NCCL communicator
+            torch.cuda.current_stream(self.rows.device).synchronize()
+            g = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(g):
+                    out_s, out_i = self._step(sq, ss, k)
+            except Exception:
+                self.use_graph = False                  # capture is an optimisation, never a requirement
+                return self._step(q_bf16, q_scale, k)
+            ent = (g, sq, ss, out_s, out_i)
+            self._graphs[key] = ent
+        g, sq, ss, out_s, out_i = ent
+        if q_bf16.data_ptr() != sq.data_ptr():
+            sq.copy_(q_bf16)
+        if q_scale.data_ptr() != ss.data_ptr():
+            ss.copy_(q_scale)
+        g.replay()
+        return out_s, out_i
 
     def search_batch(self, queries: torch.Tensor, k: int):
         """Public API: fp32/bf16 queries on host (pinned) or device -> global top-k on this rank's device."""
         q = queries.to(self.rows.device, non_blocking=True)
         if q.dtype not in (torch.float32, torch.bfloat16):
             q = q.to(torch.float32)
-        qb, qs = self.ops.ingest_rows(q.contiguous(), self.metric)
+        ent = self._graphs.get((q.shape[0], k)) if self.use_graph else None
+        if ent is not None and q.dtype == torch.float32:   # cast + normalise straight into the graph's query buffers
+            qb, qs = self.ops.ingest_rows(q.contiguous(), self.metric, out_bf16=ent[1], out_scale=ent[2])
+        else:
+            qb, qs = self.ops.ingest_rows(q.contiguous(), self.metric)
         return self.search_device(qb, qs, k)
 
 
@@ -114,6 +225,8 @@ class ShardedBm25Index:
         s, i = self.index.search_terms(q_terms, k)
         if self.world == 1:
             return s, i
+        if self.index.id_base + self.index.n_docs < KEY_ID_LIMIT:      # same on every rank: ranges of one collection
+            return self.ops.merge_keys(gather_keys(self.ops.pack_keys(s, i), self.group), k)
         gs, gi = exchange_candidates(s, i, self.group)
         return self.ops.merge_candidates(gs, gi, k)
 

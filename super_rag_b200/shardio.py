@@ -120,8 +120,9 @@ def read_footer(path: str) -> Dict[str, Any]:
 
 
 def read_shard(path: str, device: Optional[torch.device] = None, expect_kind: Optional[str] = None,
-               verify: bool = True) -> Tuple[Dict[str, Any], Dict[str, torch.Tensor], Dict[str, Any]]:
-    """-> (meta, arrays on `device` (host if None), blobs). Raises ShardError on any CRC / layout mismatch."""
+               verify: bool = True, host_sections=None) -> Tuple[Dict[str, Any], Dict[str, torch.Tensor], Dict[str, Any]]:
+    """-> (meta, arrays on `device` (host if None), blobs). Raises ShardError on any CRC / layout mismatch.
+    `host_sections`: predicate on the section name; matching arrays stay in host memory (the doc-table columns)."""
     footer = read_footer(path)
     if expect_kind is not None and footer["kind"] != expect_kind:
         raise ShardError(f"{path}: kind {footer['kind']!r}, expected {expect_kind!r}")
@@ -143,11 +144,12 @@ def read_shard(path: str, device: Optional[torch.device] = None, expect_kind: Op
             n_el = int(np.prod(s["shape"])) if s["shape"] else 1
             if dt is None or n_el * _ITEMSIZE[s["dtype"]] != s["nbytes"]:
                 raise ShardError(f"{path}: section {s['name']!r} has an inconsistent header")
-            out = torch.empty(s["nbytes"], dtype=torch.uint8, device=dev if dev is not None else "cpu")
+            to_gpu = on_gpu and not (host_sections is not None and host_sections(s["name"]))
+            out = torch.empty(s["nbytes"], dtype=torch.uint8, device=dev if to_gpu else "cpu")
             crc = 0
             for a in range(0, s["nbytes"], CHUNK_BYTES):
                 m = min(CHUNK_BYTES, s["nbytes"] - a)
-                if on_gpu:
+                if to_gpu:
                     torch.cuda.current_stream(dev).synchronize()        # staging buffer is free again
                     host = stage[:m].numpy()
                 else:
@@ -157,7 +159,7 @@ def read_shard(path: str, device: Optional[torch.device] = None, expect_kind: Op
                     raise ShardError(f"{path}: section {s['name']!r} is truncated")
                 if verify:
                     crc = zlib.crc32(host, crc)
-                if on_gpu:
+                if to_gpu:
                     out[a:a + m].copy_(stage[:m], non_blocking=True)
             if verify and (crc & 0xFFFFFFFF) != s["crc32"]:
                 raise ShardError(f"{path}: section {s['name']!r} failed its CRC-32")

@@ -18,57 +18,17 @@ from __future__ import annotations
 
 import logging
 import threading
-import uuid
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
+import numpy as np
 import torch
 
 from . import ops, shardio
 from ._lib import SragError
+from .doctable import HostDocTable
 from .models import DocumentWithScore, QueryResult, QueryWithEmbedding
 
 logger = logging.getLogger(__name__)
-
-
-class HostDocTable:
-    """Row -> (uuid, text, metadata) on the host; uuid -> row for deletes. Pure Python."""
-
-    def __init__(self):
-        self.ids: List[str] = []
-        self.texts: List[Optional[str]] = []
-        self.metas: List[Optional[dict]] = []
-        self.row_of: Dict[str, int] = {}
-        self.deleted: set = set()
-
-    def __len__(self):
-        return len(self.ids)
-
-    @property
-    def live(self) -> int:
-        return len(self.ids) - len(self.deleted)
-
-    def append(self, ids: Sequence[str], texts: Sequence[Optional[str]], metas: Sequence[Optional[dict]]) -> range:
-        start = len(self.ids)
-        for i, t, m in zip(ids, texts, metas):
-            if i in self.row_of:
-                raise ValueError(f"duplicate id {i!r}")
-            self.row_of[i] = len(self.ids)
-            self.ids.append(i)
-            self.texts.append(t)
-            self.metas.append(m)
-        return range(start, len(self.ids))
-
-    def delete(self, ids: Sequence[str]) -> List[int]:
-        rows = []
-        for i in ids:
-            r = self.row_of.pop(i, None)
-            if r is not None and r not in self.deleted:
-                self.deleted.add(r)
-                rows.append(r)
-        return rows
-
-    def get(self, row: int) -> Tuple[str, Optional[str], Optional[dict]]:
-        return self.ids[row], self.texts[row], self.metas[row]
 
 
 MISSING_BIT = 1 << 31      # row has no `indexer` field ({"indexer": {"$exists": False}})
@@ -103,6 +63,32 @@ class RowTagger:
         if meta.get("chat_id") is not None:
             group = self.chat_group.setdefault(str(meta["chat_id"]), len(self.chat_group) + 1)
         return tag, group
+
+    def encode_batch(self, metas: Sequence[Optional[dict]]) -> Tuple[np.ndarray, np.ndarray]:
+        """-> (tag words, chat groups) as int32 arrays for a batch of metadata dicts. Rows sharing one dict object
+        (the chunks of one document usually do) are encoded once; rows without metadata never enter Python code
+        beyond the loop header."""
+        m = len(metas)
+        tags = [MISSING_BIT] * m
+        groups = [0] * m
+        last, last_enc = None, (MISSING_BIT, 0)
+        for j, mt in enumerate(metas):
+            if not mt:
+                continue
+            if mt is not last:
+                last, last_enc = mt, self.encode(mt)
+            tags[j], groups[j] = last_enc
+        return (np.array(tags, dtype=np.uint32).view(np.int32), np.array(groups, dtype=np.int32))
+
+    def state(self) -> dict:
+        return {"indexer_bit": self.indexer_bit, "chat_group": self.chat_group}
+
+    @classmethod
+    def from_state(cls, st: dict) -> "RowTagger":
+        t = cls()
+        t.indexer_bit = {str(k): int(v) for k, v in st.get("indexer_bit", {}).items()}
+        t.chat_group = {str(k): int(v) for k, v in st.get("chat_group", {}).items()}
+        return t
 
     # -- filter dict -> (tag mask, group) ------------------------------------------------------
     def _tag_clause(self, cond) -> int:
@@ -168,6 +154,7 @@ class DeviceCollection:
         self._rows: Optional[torch.Tensor] = None
         self._scale: Optional[torch.Tensor] = None
         self._ws: Optional[torch.Tensor] = None
+        self._ws_event: Optional[torch.cuda.Event] = None   # last search that used the workspace
         self._tags: Optional[torch.Tensor] = None      # int32 [cap] tag words, int32 [cap] chat groups
         self._group: Optional[torch.Tensor] = None
         self.tagger = RowTagger()
@@ -210,15 +197,24 @@ class DeviceCollection:
                                                                                 device=self._dev())
 
     def append(self, embeddings, ids=None, texts=None, metas=None) -> List[str]:
-        """embeddings: [m, dim] tensor (any device, fp32 or bf16) or nested lists."""
+        """embeddings: [m, dim] tensor (any device, fp32 or bf16) or nested lists. All-or-nothing: lengths and
+        duplicate ids are rejected before the device or the doc table is touched."""
         emb = embeddings if isinstance(embeddings, torch.Tensor) else torch.tensor(embeddings, dtype=torch.float32)
         if emb.ndim != 2 or emb.shape[1] != self.dim:
             raise ValueError(f"embeddings must be [m, {self.dim}], got {tuple(emb.shape)}")
         m = emb.shape[0]
-        ids = list(ids) if ids is not None else [str(uuid.uuid4()) for _ in range(m)]
-        texts = list(texts) if texts is not None else [None] * m
-        metas = list(metas) if metas is not None else [None] * m
+        ids = list(ids) if ids is not None else None           # None: uuid4s generated in bulk (seekdb_connector.py:75)
+        texts = list(texts) if texts is not None else None
+        metas = list(metas) if metas is not None else None
         with self.lock:
+            self.docs.validate_new(ids, m, texts, metas)
+            tagger_before = (dict(self.tagger.indexer_bit), dict(self.tagger.chat_group))
+            try:
+                tags, groups = self.tagger.encode_batch(metas) if metas is not None else (
+                    np.full(m, _i32(MISSING_BIT), dtype=np.int32), np.zeros(m, dtype=np.int32))
+            except Exception:
+                self.tagger.indexer_bit, self.tagger.chat_group = tagger_before
+                raise
             dev = self._dev()
             self._grow(self.n + m)
             if emb.dtype not in (torch.float32, torch.bfloat16):
@@ -226,12 +222,11 @@ class DeviceCollection:
             emb = emb.to(dev, non_blocking=True).contiguous()
             ops.ingest_rows(emb, self.metric, out_bf16=self._rows[self.n:self.n + m],
                             out_scale=self._scale[self.n:self.n + m])
-            enc = [self.tagger.encode(mt) for mt in metas]
-            self._tags[self.n:self.n + m] = torch.tensor([_i32(t) for t, _ in enc], dtype=torch.int32).to(dev)
-            self._group[self.n:self.n + m] = torch.tensor([g for _, g in enc], dtype=torch.int32).to(dev)
-            self.docs.append(ids, texts, metas)
+            self._tags[self.n:self.n + m] = torch.from_numpy(tags).to(dev)
+            self._group[self.n:self.n + m] = torch.from_numpy(groups).to(dev)
+            out_ids = self.docs.append(ids, texts, metas, m)    # cannot fail any more: validated above
             self.n += m
-        return ids
+        return out_ids
 
     def delete(self, ids: Sequence[str]) -> int:
         with self.lock:
@@ -243,63 +238,93 @@ class DeviceCollection:
 
     # -- persistence (on-disk shard) ---------------------------------------
     def save(self, path: str) -> None:
-        """Write rows, multipliers (NaN tombstones included) and the doc table as one shard file."""
+        """Write rows, multipliers (NaN tombstones included), the filter columns and the doc table (id / text / metadata
+        columns as raw sections) as one shard file."""
         with self.lock:
-            meta = {"name": self.name, "dim": self.dim, "metric": self.metric, "n": self.n, "id_base": self.id_base}
-            docs = {"ids": self.docs.ids, "texts": self.docs.texts, "metas": self.docs.metas,
-                    "deleted": sorted(self.docs.deleted)}
-            shardio.write_shard(path, "vector", meta, {"rows": self.rows, "row_scale": self.row_scale}, {"docs": docs})
+            meta = {"name": self.name, "dim": self.dim, "metric": self.metric, "n": self.n, "id_base": self.id_base,
+                    "doc_table": "columns"}
+            arrays = {"rows": self.rows, "row_scale": self.row_scale}
+            if self.n:
+                arrays["row_tags"], arrays["row_group"] = self._tags[:self.n], self._group[:self.n]
+            arrays.update({k: torch.from_numpy(v) for k, v in self.docs.to_arrays().items()})
+            shardio.write_shard(path, "vector", meta, arrays, {"tagger": self.tagger.state()})
 
     @classmethod
     def load(cls, path: str, name: Optional[str] = None, device: Optional[str] = None) -> "DeviceCollection":
-        """Rebuild a collection from a shard written by save(); searches return bit-identical results."""
+        """Rebuild a collection from a shard written by save(); searches return bit-identical results. The doc table
+        comes back as columns (no per-row Python work; metadata is parsed when a hit asks for it)."""
         footer = shardio.read_footer(path)
         meta = footer["meta"]
         col = cls(name or meta["name"], int(meta["dim"]), int(meta["metric"]), device)
         dev = col._dev()
-        meta, arrays, blobs = shardio.read_shard(path, device=dev, expect_kind="vector")
+        host_sections = lambda nm: nm.startswith("doc_")
+        meta, arrays, blobs = shardio.read_shard(path, device=dev, expect_kind="vector", host_sections=host_sections)
         n = int(meta["n"])
         rows, scale = arrays["rows"], arrays["row_scale"]
         if tuple(rows.shape) != (n, col.dim) or rows.dtype != torch.bfloat16 or tuple(scale.shape) != (n,):
             raise shardio.ShardError(f"{path}: rows / row_scale do not match the header")
         col._rows, col._scale, col.n, col.id_base = rows, scale, n, int(meta["id_base"])
-        d = blobs["docs"]
+        if meta.get("doc_table") == "columns":
+            try:
+                col.docs = HostDocTable.from_arrays({k: v.numpy() for k, v in arrays.items() if k.startswith("doc_")}, n)
+            except (KeyError, ValueError) as e:
+                raise shardio.ShardError(f"{path}: doc table does not match the header ({e})") from e
+            col.tagger = RowTagger.from_state(blobs.get("tagger", {}))
+            if n:
+                col._tags, col._group = arrays["row_tags"].contiguous(), arrays["row_group"].contiguous()
+                if col._tags.numel() != n or col._group.numel() != n:
+                    raise shardio.ShardError(f"{path}: filter columns do not match the header")
+            else:
+                col._tags = torch.empty(0, dtype=torch.int32, device=dev)
+                col._group = torch.empty(0, dtype=torch.int32, device=dev)
+            return col
+        d = blobs["docs"]                                     # shards written before the column format
         if not (len(d["ids"]) == len(d["texts"]) == len(d["metas"]) == n):
             raise shardio.ShardError(f"{path}: doc table does not match the header")
-        col.docs.ids, col.docs.texts, col.docs.metas = list(d["ids"]), list(d["texts"]), list(d["metas"])
-        col.docs.deleted = set(int(r) for r in d["deleted"])
-        col.docs.row_of = {i: r for r, i in enumerate(col.docs.ids) if r not in col.docs.deleted}
-        enc = [col.tagger.encode(mt) for mt in col.docs.metas]      # same interning order as the original appends
-        col._tags = torch.tensor([_i32(t) for t, _ in enc], dtype=torch.int32).to(dev)
-        col._group = torch.tensor([g for _, g in enc], dtype=torch.int32).to(dev)
+        col.docs = HostDocTable.from_lists(d["ids"], d["texts"], d["metas"], d["deleted"])
+        tags, groups = col.tagger.encode_batch(list(d["metas"]))   # same interning order as the original appends
+        col._tags, col._group = torch.from_numpy(tags).to(dev), torch.from_numpy(groups).to(dev)
         return col
 
     # -- search -------------------------------------------------------------------------------
     def search_batch(self, queries: torch.Tensor, top_k: int, filters=None):
         """queries [B, dim] (host or device, fp32 or bf16) -> (scores fp32 [B,k], ids int64 [B,k]) on device.
         `filters`: None, one filter dict for the whole batch, or a list of B dicts (context.py:74-111 grammar);
-        the result is the exact top-k among the rows each query's filter admits."""
+        the result is the exact top-k among the rows each query's filter admits.
+
+        The collection lock is held from the snapshot of (n, rows, multipliers, filter columns) to the last launch:
+        the scan workspace (per-thread heaps, shared thresholds, pacing counters) belongs to the collection, ctypes
+        releases the GIL during srag_* calls, and two interleaved searches — or a search racing an append that swaps
+        the buffers — would silently merge each other's state."""
         dev = self._dev()
         q = queries.to(dev, non_blocking=True)
         if q.dtype not in (torch.float32, torch.bfloat16):
             q = q.to(torch.float32)
-        qb, qs = ops.ingest_rows(q.contiguous(), self.metric)
-        need = ops.topk_workspace_bytes(self.n, min(q.shape[0], ops.MAX_QUERIES_PER_CALL), top_k, self.dim)
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
-        kw = {}
-        if filters is not None and self.n:
-            per_q = filters if isinstance(filters, (list, tuple)) else [filters] * q.shape[0]
-            if len(per_q) != q.shape[0]:
-                raise ValueError(f"{len(per_q)} filters for {q.shape[0]} queries")
-            comp = [self.tagger.compile(f) for f in per_q]
-            if any(m != 0xFFFFFFFF for m, _ in comp):
-                kw["row_tags"] = self._tags[:self.n]
-                kw["q_tag_mask"] = torch.tensor([_i32(m) for m, _ in comp], dtype=torch.int32).to(dev)
-            if any(g >= 0 for _, g in comp):
-                kw["row_group"] = self._group[:self.n]
-                kw["q_group"] = torch.tensor([g for _, g in comp], dtype=torch.int32).to(dev)
-        return ops.topk_search(self.rows, self.row_scale, qb, qs, top_k, id_base=self.id_base, workspace=self._ws, **kw)
+        with self.lock:
+            n = self.n
+            rows, scale = self.rows, self.row_scale
+            qb, qs = ops.ingest_rows(q.contiguous(), self.metric)
+            need = ops.topk_workspace_bytes(n, min(q.shape[0], ops.MAX_QUERIES_PER_CALL), top_k, self.dim)
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            kw = {}
+            if filters is not None and n:
+                per_q = filters if isinstance(filters, (list, tuple)) else [filters] * q.shape[0]
+                if len(per_q) != q.shape[0]:
+                    raise ValueError(f"{len(per_q)} filters for {q.shape[0]} queries")
+                comp = [self.tagger.compile(f) for f in per_q]
+                if any(m != 0xFFFFFFFF for m, _ in comp):
+                    kw["row_tags"] = self._tags[:n]
+                    kw["q_tag_mask"] = torch.tensor([_i32(m) for m, _ in comp], dtype=torch.int32).to(dev)
+                if any(g >= 0 for _, g in comp):
+                    kw["row_group"] = self._group[:n]
+                    kw["q_group"] = torch.tensor([g for _, g in comp], dtype=torch.int32).to(dev)
+            if self._ws_event is not None:   # a search issued on another stream may still be using the workspace
+                torch.cuda.current_stream(dev).wait_event(self._ws_event)
+            out = ops.topk_search(rows, scale, qb, qs, top_k, id_base=self.id_base, workspace=self._ws, **kw)
+            self._ws_event = torch.cuda.Event()
+            self._ws_event.record(torch.cuda.current_stream(dev))
+        return out
 
 
 _REGISTRY: Dict[str, DeviceCollection] = {}

@@ -19,6 +19,9 @@ Pinned here:
   SeekDBVectorStoreConnector.search / _convert_scored_point_to_document_with_score
                              super_rag/vectorstore/seekdb_connector.py:98-156
   maximal_marginal_relevance graphiti_core/search/search_utils.py:1884-1922  (-> mmr_golden.json)
+  brute-force cosine RANKING  the Neptune branch of edge_similarity_search scores every stored embedding with
+                             calculate_cosine_similarity and orders by score descending
+                             (graphiti_core/search/search_utils.py:337-366 with :56-67)  (-> topk_golden.json)
 """
 from __future__ import annotations
 
@@ -186,10 +189,55 @@ def make_mmr_golden():
     print("wrote", path, len(cases))
 
 
+def make_topk_golden():
+    """Full ranked lists from the reference's own in-tree brute-force cosine ranking: the Neptune branch
+    (search_utils.py:337-366) calls `calculate_cosine_similarity(search_vector, embedding)` (:56-67) for every row, keeps
+    `score > min_score`, and orders by score descending with a limit. Here that loop runs over a seeded 2000 x 64 corpus
+    with zero rows, exact duplicates, near-ties and a zero query; the ORDER BY is a stable sort, so equal scores stay in
+    row order (= the north-star tie rule). Values are multiples of 1/64 in [-4, 4]: exact in bf16, so the GPU path
+    sees the very numbers the reference function saw. Stored: the inputs (as integer numerators), every pair score
+    (float64, as the function returned it) and the ranked top-20 per query."""
+    _, cos, _ = _load_graphiti_functions()
+    rng = np.random.default_rng(4242)
+    n, d, k = 2000, 64, 20
+    C = rng.integers(-256, 257, (n, d))
+    C[17] = 0                                     # zero rows: score 0 whatever the query (search_utils.py:63-64)
+    C[1999] = 0
+    for a, b in [(5, 1200), (6, 7), (300, 1500), (1500, 1900)]:
+        C[b] = C[a]                               # exact duplicates (a chain of three: 300, 1500, 1900)
+    C[41] = C[40]
+    C[41, 3] += 1                                 # near-ties: one numerator step in one coordinate
+    C[900] = 2 * C[40]                            # same direction, twice the length: cosine equal up to rounding
+    Q = rng.integers(-256, 257, (14, d))
+    Q[0] = C[5]                                   # hits the duplicate pair 5 / 1200
+    Q[1] = C[300]                                 # hits the triple
+    Q[2] = C[40]                                  # near-tie neighbourhood
+    Q[3] = 0                                      # zero query: every score is 0, ranking = row order
+    Q[4] = -C[6]                                  # most scores negative around the duplicates 6 / 7
+    Q[5] = C[123] + rng.integers(-8, 9, d)        # a planted neighbour
+    min_scores = [-2.0] * 12 + [0.0, 0.2]         # the branch's `score > min_score` filter (last two queries)
+    cases = []
+    for qi in range(Q.shape[0]):
+        qv = (Q[qi] / 64.0).tolist()
+        scores = [float(cos(qv, (C[r] / 64.0).tolist())) for r in range(n)]
+        kept = [{"id": r, "score": sc} for r, sc in enumerate(scores) if sc > min_scores[qi]]
+        kept.sort(key=lambda e: -e["score"])      # ORDER BY i.score DESC (stable), LIMIT $limit
+        top = kept[:k]
+        cases.append({"query_num": Q[qi].tolist(), "min_score": min_scores[qi], "scores": scores,
+                      "top_ids": [e["id"] for e in top], "top_scores": [e["score"] for e in top]})
+    path = os.path.join(OUT, "topk_golden.json")
+    with open(path, "w", encoding="utf-8") as f:
+        json.dump({"reference_commit": "49de377", "denominator": 64, "k": k, "corpus_num": C.tolist(), "cases": cases}, f)
+    print("wrote", path, len(cases))
+
+
 def main():
     if "--mmr-only" in sys.argv:
         return make_mmr_golden()
+    if "--topk-only" in sys.argv:
+        return make_topk_golden()
     make_mmr_golden()
+    make_topk_golden()
     rng = np.random.default_rng(20261104)
     rrf, cos, norm_l2 = _load_graphiti_functions()
     golden = {"reference_commit": "49de377", "cases": {}}

@@ -75,7 +75,7 @@ def test_abi_library_builds_loads_and_exports_header_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/srag_b200.h but not exported"
     assert declared == set(_lib.SIGNATURES), "python binding and header disagree"
-    assert lib.srag_abi_version() == 1
+    assert lib.srag_abi_version() == 2
 
 
 def test_sass_has_tcgen05_and_tma():

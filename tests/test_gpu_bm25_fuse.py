@@ -335,3 +335,112 @@ def test_bm25_sub_kernel_queries_longer_than_32_terms():
     os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, queries, 50)
     assert (i.cpu().numpy() == oi).all()
     assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("filtered", [False, True])
+def test_bm25_two_phase_single_query_odd_k(filtered):
+    """B = 1 with k in {1, 5} on an index of >= 32 blocks (the default fulltext_search node shape: one query, top_k = 5).
+    B * k is odd, so the sample's (ids, scores) region of the workspace must keep its 8-byte id stores aligned for any
+    B * k (round-1 layout put the ids behind B * k floats: a misaligned-address fault on exactly this shape)."""
+    import torch
+    n_docs, vocab = 560_000, 200
+    tokens, doc_ptr = zipf_corpus(n_docs, vocab, 12, seed=5)
+    idx, (tp, pd, ptf, dl, imp) = _build(tokens, doc_ptr, vocab)
+    kw = {}
+    valid = None
+    if filtered:
+        tags = (1 << (np.arange(n_docs) % 3)).astype(np.int32)
+        kw = {"doc_tags": torch.from_numpy(tags).cuda(), "q_tag_mask": torch.tensor([0b101], dtype=torch.int32).cuda()}
+        valid = (tags & 0b101) != 0
+    for k in (1, 5, 7):
+        for q in ([3, 17, 150], [0], [199, 42]):
+            s, i = idx.search([q], k, **kw)
+            torch.cuda.synchronize()
+            os_, oi = oracle.bm25_topk(tp, pd, imp, n_docs, [q], k, valid=valid)
+            assert (i.cpu().numpy() == oi).all(), (k, q)
+            assert (s.cpu().numpy().view(np.uint32) == os_.view(np.uint32)).all(), (k, q)
+
+
+def test_fulltext_collection_whose_texts_tokenise_to_nothing():
+    """avgdl = 0 and nnz = 0: the index builds and every search returns no hits (srag_bm25_impacts used to reject it)."""
+    from super_rag_b200.fulltext import FulltextCollection, hash_tokenizer
+    col = FulltextCollection("empty-texts", hash_tokenizer(1024), 1024, device="cuda")
+    col.add(["", "   ", "!!!"])
+    assert col.search("anything at all", 5) == []
+    col.add(["now a real word"])
+    assert [d.text for d in col.search("word", 5)] == ["now a real word"]
+
+
+def test_exchange_keys_pack_merge_and_fused_emission():
+    """The 8-byte cross-shard exchange format: srag_pack_keys == the torch statement (sharded.pack_keys_torch);
+    srag_merge_keys == srag_merge_candidates == the oracle on ties across positions and shards, ragged lists, -0.0 and
+    negative scores; srag_topk_search_keys emits exactly pack(scores, ids) of the ordinary search."""
+    import torch
+    from super_rag_b200 import ops
+    from super_rag_b200.sharded import pack_keys_torch, unpack_keys_torch
+    rng = np.random.default_rng(19)
+    G, B, KK = 8, 37, 100
+    s = rng.standard_normal((G, B, KK)).astype(np.float32)
+    s[:, :, 50:60] = s[:, :, 40:50]
+    s[1] = s[0]
+    s[2, :, :5] = -0.0
+    s[3, :, :5] = 0.0
+    i = rng.permutation(G * B * KK).reshape(G, B, KK).astype(np.int64) + 4_000_000_000 - G * B * KK - 8
+    i[3, :, 90:] = -1
+    st, it = torch.from_numpy(s).cuda(), torch.from_numpy(i).cuda()
+    keys = ops.pack_keys(st, it)
+    assert torch.equal(keys.cpu(), pack_keys_torch(torch.from_numpy(s), torch.from_numpy(i)))
+    us, ui = unpack_keys_torch(keys)
+    m = it >= 0
+    assert torch.equal(ui[m], it[m]) and torch.equal(us[m], st[m]) and (ui[~m] == -1).all()       # -0.0 comes back as +0.0
+    for k in (1, 10, 100):
+        ms, mi = ops.merge_keys(keys, k)
+        cs, ci = ops.merge_candidates(st, it, k)
+        ws, wi = oracle.merge_shard_candidates(s, i, k)
+        assert (mi.cpu().numpy() == wi).all() and (ci.cpu().numpy() == wi).all(), k
+        assert (ms.cpu().numpy() == ws).all() and (cs.cpu().numpy() == ws).all(), k
+    # fused emission from the finalize kernel
+    n, d, b, k = 30_000, 256, 200, 10
+    C = torch.randn(n, d, device="cuda")
+    Q = torch.randn(b, d, device="cuda")
+    C[20_000] = C[5]
+    Q[0] = C[5]
+    cb, cs_ = ops.ingest_rows(C, "cosine")
+    qb, qs = ops.ingest_rows(Q, "cosine")
+    base = 1_000_000_007
+    s0, i0 = ops.topk_search(cb, cs_, qb, qs, k, id_base=base)
+    kbuf = torch.empty(b, k, dtype=torch.int64, device="cuda")
+    s1, i1 = ops.topk_search(cb, cs_, qb, qs, k, id_base=base, out_keys=kbuf)
+    assert torch.equal(i0, i1) and torch.equal(s0, s1) and torch.equal(kbuf, ops.pack_keys(s0, i0))
+    kbuf2 = torch.zeros_like(kbuf)
+    assert ops.topk_search(cb, cs_, qb, qs, k, id_base=base, out_keys=kbuf2, keys_only=True) == (None, None)
+    assert torch.equal(kbuf2, kbuf)
+    with pytest.raises(Exception):                          # global rows that do not fit 32 bits are refused loudly
+        ops.topk_search(cb, cs_, qb, qs, k, id_base=1 << 32, out_keys=kbuf)
+
+
+def test_fuse_at_the_abi_limit_with_duplicates():
+    """K3 is a segmented sort: 8 lists x 256 entries = the ABI's 2048-entry limit, ids drawn from a small pool so that
+    most chunks occur in several lists and some twice inside one list (the reference adds those again)."""
+    import torch
+    from super_rag_b200 import ops
+    rng = np.random.default_rng(23)
+    L, B, K = 8, 5, 256
+    ids = rng.integers(0, 700, (L, B, K)).astype(np.int64)
+    ids[:, :, 250:] = -1
+    ids[1, 2, :] = -1                                              # an empty list
+    sc = rng.random((L, B, K)).astype(np.float32)
+    it = torch.from_numpy(ids).cuda()
+    for rc in (1, 60):
+        oi, osc = ops.fuse(it, None, ops.FUSE_RRF, 300, rank_const=rc, min_score=0.02 if rc == 1 else 0.0)
+        for q in range(B):
+            wi, ws = oracle.rrf_fuse_topk([ids[l, q] for l in range(L)], rc, 0.02 if rc == 1 else 0.0, 300)
+            got_i, got_s = oi[q].cpu().numpy(), osc[q].cpu().numpy()
+            assert got_i[:len(wi)].tolist() == wi.tolist() and (got_i[len(wi):] == -1).all()
+            assert got_s[:len(ws)].tolist() == ws.tolist()
+    w = [0.5, 0.25, 1.0, 0.125, 2.0, 0.75, 0.3, 0.9]
+    oi, osc = ops.fuse(it, torch.from_numpy(sc).cuda(), ops.FUSE_WEIGHTED, 50, min_score=float("-inf"), weights=w)
+    for q in range(B):
+        wi, ws = oracle.weighted_fuse_topk([ids[l, q] for l in range(L)], [sc[l, q] for l in range(L)], w, 50)
+        assert oi[q].cpu().numpy()[:len(wi)].tolist() == wi.tolist()
+        assert osc[q].cpu().numpy()[:len(ws)].astype(np.float32).tolist() == ws.tolist()

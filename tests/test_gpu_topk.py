@@ -174,3 +174,38 @@ def test_empty_corpus_returns_padding():
     qb, qs = ops.ingest_rows(q, "cosine")
     s, i = ops.topk_search(torch.empty(0, 64, dtype=torch.bfloat16, device=dev), torch.empty(0, device=dev), qb, qs, 4)
     assert (i.cpu().numpy() == -1).all() and np.isinf(s.cpu().numpy()).all()
+
+
+def test_k1_against_reference_ranked_lists(topk_golden):
+    """K1 against ranked lists produced by the REFERENCE's own brute-force cosine ranking (tests/golden/topk_golden.json:
+    search_utils.py:337-366 with calculate_cosine_similarity :56-67, executed by tests/golden/make_golden.py). The inputs are
+    exact in bf16, so the kernel consumes the very numbers the reference function saw: scores within 1e-3 (north_star;
+    5e-5 in fact), ids equal position by position wherever the reference's scores separate neighbours by more than the
+    tolerance, duplicates in row order, zero rows and the zero query score 0."""
+    C, cases, k = topk_golden
+    Q = np.stack([c["query"] for c in cases])
+    ref_full = np.stack([c["scores"] for c in cases])
+    for cta_group in (None, 1):
+        s, i, cr, qr, _ = _run(C, Q, k, "cosine", cta_group)
+        assert (cr == C).all() and (qr == Q).all()
+        check_topk_against_full_scores(s, i, ref_full, k, TOL)
+        check_topk_against_full_scores(s, i, ref_full, k, TIGHT)
+        assert i[0, :2].tolist() == [5, 1200] and i[1, :3].tolist() == [300, 1500, 1900]     # duplicates: lower row first
+        assert i[3].tolist() == list(range(k)) and (s[3] == 0).all()                          # zero query: row order
+        exact = sum(int((i[qi] == c["top_ids"]).all()) for qi, c in enumerate(cases) if c["min_score"] < -1.5)
+        assert exact >= 8, exact
+        for qi, c in enumerate(cases):                    # the branch's `score > min_score` cut on our ranked list
+            if c["min_score"] > -1.5:
+                kept = [int(r) for r, x in zip(i[qi], s[qi]) if x > c["min_score"]]
+                assert kept == c["top_ids"].tolist()[:len(kept)] and abs(len(kept) - len(c["top_ids"])) <= 1
+    # through the batched connector API as well, and a single-row batch (B = 1 plan)
+    import torch
+    from super_rag_b200.vectorstore import B200Client
+    cl = B200Client()
+    cl.delete_collection("t_golden")
+    col = cl.create_collection("t_golden", C.shape[1], "cosine")
+    col.append(torch.from_numpy(C))
+    for qi in (0, 1, 3, 5):
+        s1, i1 = col.search_batch(torch.from_numpy(Q[qi:qi + 1]), k)
+        check_topk_against_full_scores(s1.cpu().numpy(), i1.cpu().numpy(), ref_full[qi:qi + 1], k, TIGHT)
+    cl.delete_collection("t_golden")

@@ -63,13 +63,56 @@ def test_adaptor_contract():
 
 
 def test_doc_table_and_tombstone_bookkeeping():
-    from super_rag_b200.vectorstore import HostDocTable
+    from super_rag_b200.doctable import HostDocTable
     t = HostDocTable()
-    assert list(t.append(["a", "b", "c"], ["ta", "tb", "tc"], [None, {"k": 1}, None])) == [0, 1, 2]
+    assert t.append(["a", "b", "c"], ["ta", "tb", "tc"], [None, {"k": 1}, None]) == ["a", "b", "c"]
     with pytest.raises(ValueError):
         t.append(["a"], ["dup"], [None])
+    with pytest.raises(ValueError):                    # a duplicate inside the batch, and nothing was appended
+        t.append(["x", "x"], ["1", "2"], [None, None])
+    with pytest.raises(ValueError):                    # ragged columns (zip() used to truncate them silently)
+        t.append(["y", "z"], ["only one"], [None, None])
+    assert len(t) == 3 and "x" not in t.row_of and "y" not in t.row_of
     assert t.delete(["b", "zz"]) == [1] and t.delete(["b"]) == [] and t.live == 2
-    assert t.get(2) == ("c", "tc", None)
+    assert t.get(2) == ("c", "tc", None) and t.get(1) == ("b", "tb", {"k": 1})
+    assert t.ids[0] == "a" and list(t.texts) == ["ta", "tb", "tc"] and len(t.metas) == 3
+
+
+def test_doc_table_columns_bulk_uuid_and_round_trip():
+    """Column storage: generated ids are valid, distinct uuid4s; arrays -> table round trip keeps every cell, parses
+    metadata lazily and keeps tombstones."""
+    import uuid
+    from super_rag_b200.doctable import HostDocTable, bulk_uuid4
+    raw = bulk_uuid4(1000).decode("ascii")
+    ids = [raw[36 * i:36 * i + 36] for i in range(1000)]
+    assert len(set(ids)) == 1000
+    for i in ids[:50]:
+        u = uuid.UUID(i)
+        assert u.version == 4 and u.variant == uuid.RFC_4122 and str(u) == i
+    t = HostDocTable()
+    shared = {"indexer": "pdf", "n": 1}
+    got = t.append(None, ["héllo", None, "", "x" * 1000], [shared, shared, None, {"chat_id": "c1"}])
+    assert len(got) == 4 and t.get(0) == (got[0], "héllo", shared) and t.get(1)[1] is None and t.get(2)[1] == ""
+    t.append(["mine"], ["t"], None)
+    assert t.delete([got[1]]) == [1]
+    t2 = HostDocTable.from_arrays(t.to_arrays(), len(t))
+    assert len(t2) == 5 and t2.deleted == {1}
+    for r in range(5):
+        assert t2.get(r) == t.get(r)
+    assert t2.row_of["mine"] == 4 and got[1] not in t2.row_of
+    assert t2.append(None, None, None, m=3) and len(t2) == 8 and t2.get(7)[1:] == (None, None)
+
+
+def test_row_tagger_encode_batch_matches_per_row_encode():
+    from super_rag_b200.vectorstore import RowTagger, MISSING_BIT
+    metas = [None, {}, {"indexer": "a"}, {"indexer": "b", "chat_id": 7}, {"chat_id": "7"}, {"indexer": "a"}]
+    metas += [metas[3]] * 3
+    t1, t2 = RowTagger(), RowTagger()
+    tags, groups = t1.encode_batch(metas)
+    ref = [t2.encode(m) for m in metas]
+    assert [int(x) & 0xFFFFFFFF for x in tags] == [r[0] for r in ref] and groups.tolist() == [r[1] for r in ref]
+    assert t1.state() == t2.state() and (int(tags[0]) & 0xFFFFFFFF) == MISSING_BIT
+    assert RowTagger.from_state(t1.state()).compile({"chat_id": 7}) == t1.compile({"chat_id": 7})
 
 
 def test_merge_union_matches_reference_golden(golden):

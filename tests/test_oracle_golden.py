@@ -126,3 +126,45 @@ def test_mmr_matches_reference(mmr_golden):
         order, scores = oracle.mmr_rerank(np.array(c["query"]), np.array(c["candidates"]), c["mmr_lambda"], c["min_score"])
         assert order.tolist() == c["order"]
         np.testing.assert_allclose(scores, np.array(c["scores"]), rtol=0, atol=1e-12)
+
+
+def test_cosine_topk_oracle_is_pinned_to_reference_ranking(topk_golden):
+    """oracle.exact_topk / exact_topk_scores_f64 against FULL RANKED LISTS produced by the reference's in-tree brute-force
+    cosine ranking (Neptune branch, search_utils.py:337-366 calling calculate_cosine_similarity :56-67): every pair score,
+    the ranked top-20 with duplicates (ties -> lower row first), zero rows, a zero query, near-ties. This is what moves the
+    cosine top-k oracle from "parity unpinned" to "pinned"."""
+    from parity import check_topk_against_full_scores
+    C, cases, k = topk_golden
+    assert C.shape == (2000, 64) and (oracle.bf16_round(C) == C).all()          # exact in bf16: both sides see the same numbers
+    Q = np.stack([c["query"] for c in cases])
+    ref_full = np.stack([c["scores"] for c in cases])
+    # 1. the float64 scorer reproduces the reference function's values (same formula, float64)
+    full = oracle.exact_topk_scores_f64(C, Q, "cosine")
+    assert np.abs(full - ref_full).max() < 1e-14
+    assert (full[:, [17, 1999]] == 0).all() and (full[3] == 0).all()            # zero rows, zero query -> 0 (:63-64)
+    # 2. the fp32 top-k oracle returns the reference's ranked list: same ids position by position wherever the
+    #    reference's own scores separate neighbours by more than fp32 noise, same scores to fp32 rounding
+    s, i = oracle.exact_topk(C, Q, k, "cosine")
+    exact = 0
+    for qi, c in enumerate(cases):
+        if c["min_score"] > -1.5:
+            continue                                                            # the score filter is exercised below
+        assert np.abs(s[qi] - c["top_scores"]).max() < 5e-7
+        check_topk_against_full_scores(s[qi:qi + 1], i[qi:qi + 1], ref_full[qi:qi + 1], k, tol=5e-7)
+        exact += int((i[qi] == c["top_ids"]).all())
+    assert exact >= 9, exact                     # every query whose top-20 has no near-tie matches id for id
+    # duplicates: identical rows score identically and the lower row comes first, in the reference list and in ours
+    assert cases[0]["top_ids"][:2].tolist() == [5, 1200] and i[0, :2].tolist() == [5, 1200]
+    assert cases[1]["top_ids"][:3].tolist() == [300, 1500, 1900] and i[1, :3].tolist() == [300, 1500, 1900]
+    assert i[3].tolist() == list(range(k)) and cases[3]["top_ids"].tolist() == list(range(k))   # zero query: row order
+    # 3. the branch's `score > min_score` filter == cutting our ranked list at the threshold
+    for qi, c in enumerate(cases):
+        if c["min_score"] <= -1.5:
+            continue
+        kept = [(int(r), float(x)) for r, x in zip(i[qi], s[qi]) if x > c["min_score"]]
+        assert [r for r, _ in kept] == c["top_ids"].tolist()[:len(kept)] and len(kept) == len(c["top_ids"])
+    # 4. the plain-C restatement agrees with the numpy one on the same inputs
+    from oracle import c_oracle
+    cs_, ci_ = c_oracle.topk(c_oracle.scores(C, Q, "cosine"), k)
+    assert (ci_ == i).mean() > 0.97 and np.abs(cs_ - s).max() < 1e-6
+    check_topk_against_full_scores(cs_, ci_, ref_full, k, tol=5e-7)

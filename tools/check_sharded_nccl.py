@@ -45,6 +45,27 @@ def main():
     torch.cuda.synchronize()
     ok_v = bool(torch.equal(i, fi)) and bool(torch.equal(s.view(torch.int32), fs.view(torch.int32)))
     assert i[0, 0].item() == 11 and i[0, 1].item() == 150_000
+    assert index.use_keys, "global rows fit 32 bits: the 8-byte exchange keys must be in use"
+    # the same step captured into a CUDA graph (SRAG_SHARDED_GRAPH=1): replayed twice, second time with other queries
+    index_g = ShardedVectorIndex(cb[lo:hi].contiguous(), cs[lo:hi].contiguous(), id_base=lo)
+    index_g.use_graph = True
+    gs1, gi1 = index_g.search_batch(Q, k)
+    gs1, gi1 = gs1.clone(), gi1.clone()
+    Q2 = Q.flip(0).contiguous()
+    gs2, gi2 = index_g.search_batch(Q2, k)
+    gs2, gi2 = gs2.clone(), gi2.clone()
+    gs3, gi3 = index_g.search_batch(Q, k)
+    torch.cuda.synchronize()
+    graph_used = index_g.use_graph and len(index_g._graphs) == 1
+    ok_g = bool(torch.equal(gi1, fi)) and bool(torch.equal(gs1.view(torch.int32), fs.view(torch.int32))) and \
+        bool(torch.equal(gi2, fi.flip(0))) and bool(torch.equal(gi3, fi)) and bool(torch.equal(gs3.view(torch.int32), fs.view(torch.int32)))
+    ok_v = ok_v and ok_g
+    # ids beyond the 32-bit key range take the two-plane exchange: same answers
+    big = ShardedVectorIndex(cb[lo:hi].contiguous(), cs[lo:hi].contiguous(), id_base=lo + (1 << 33))
+    assert not big.use_keys
+    bs2, bi2 = big.search_batch(Q, k)
+    torch.cuda.synchronize()
+    ok_v = ok_v and bool(torch.equal(bi2 - (1 << 33), fi)) and bool(torch.equal(bs2.view(torch.int32), fs.view(torch.int32)))
 
     # BM25: doc-range shards with GLOBAL statistics == single index
     n_docs, vocab = 120_000, 3000
@@ -104,7 +125,9 @@ def main():
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(f"world={world} vector_sharded_equals_single={bool(flags[0].item())} "
-              f"bm25_and_hybrid_sharded_equals_single={bool(flags[1].item())}", flush=True)
+              f"bm25_and_hybrid_sharded_equals_single={bool(flags[1].item())} cuda_graph_step={graph_used}", flush=True)
+        if flags[0].item() and flags[1].item():
+            print("PARITY OK", flush=True)
     dist.destroy_process_group()
     if not (flags[0].item() and flags[1].item()):
         sys.exit(1)
