@@ -7,7 +7,9 @@ only as a port / literal / view-model (super_rag/nodeflow/runners/merge.py:18-20
 super_rag/schema/view_models.py:1043-1047,1073-1081) and the design doc names "BM25"
 (docs/design/nodeflow/nodeflow.md:83,94); vendored graphiti delegates to the graph DB's
 Lucene index (graphiti_core/search/search_utils.py:562-574). This module restates the
-published Okapi/Lucene BM25:
+published Okapi BM25 in the variant that KEEPS the ``(k1 + 1)`` numerator (Robertson's
+formula, Lucene <= 7's BM25Similarity); Lucene >= 8 drops that constant factor, which leaves every
+ranking unchanged and divides every score by k1 + 1 = 2.2:
 
     idf(t)   = ln(1 + (N - df + 0.5) / (df + 0.5))
     s(q, d)  = sum over unique t in q of  idf(t) * tf * (k1 + 1) / (tf + k1 * (1 - b + b * dl/avgdl))

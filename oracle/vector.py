@@ -7,8 +7,15 @@ What it restates (reference paths relative to /root/reference):
     n_results)`` under ``distance="cosine"``
     (super_rag/vectorstore/seekdb_connector.py:38,58-61,98-107). The arithmetic lives
     in the external SeekDB server (pyseekdb==1.0.0b8, pylibseekdb==1.0.1.post1,
-    uv.lock:5747-5762,5550-5562; HNSW, approximate). The oracle is the *exact*
-    brute-force statement of that query: PARITY UNPINNED for this part.
+    uv.lock:5747-5762,5550-5562; HNSW, approximate) and cannot run here. The oracle is the
+    *exact* brute-force statement of that query and is PINNED to the reference's own in-tree
+    brute-force cosine ranking — the Neptune branch of ``edge_similarity_search`` scores every
+    stored embedding with ``calculate_cosine_similarity`` and orders by score descending
+    (graphiti_core/search/search_utils.py:337-366 with :56-67): full ranked lists produced by
+    that code, executed by ``tests/golden/make_golden.py``, are committed as
+    ``tests/golden/topk_golden.json`` and asserted in ``tests/test_oracle_golden.py``
+    (every pair score to 1e-14, ranked top-20 with duplicates, zero rows, a zero query,
+    near-ties, the ``score > min_score`` cut).
   * zero-norm rule and the cosine formula follow ``calculate_cosine_similarity``
     (super_rag/graphiti/graphiti_core/search/search_utils.py:56-67):
     ``dot / (|a| * |b|)``, and 0 when either norm is 0.
@@ -86,26 +93,23 @@ def row_scales(x: np.ndarray, metric="cosine") -> np.ndarray:
     return out.astype(np.float32)
 
 
-def exact_topk(corpus: np.ndarray, queries: np.ndarray, k: int, metric="cosine",
-               block_rows: int = 262144, id_base: int = 0, valid: np.ndarray | None = None):
-    """Exact top-k of every query against every corpus row, fp32.
-
-    score = (q . c) / (|q| |c|) for cosine (0 if either norm is 0), q . c for ip.
-    Returns (scores fp32 [B,k], ids int64 [B,k]); rows short of k (N < k) are padded
-    with (-inf, -1). ``valid`` (bool [N]) drops tombstoned rows.
-    """
-    corpus = np.asarray(corpus, dtype=np.float32)
+def exact_topk_blocks(blocks, queries: np.ndarray, k: int, metric="cosine", id_base: int = 0,
+                      valid: np.ndarray | None = None):
+    """Exact top-k of every query against a corpus delivered as an iterable of ``(first_row, fp32 block [m, D])``
+    pairs (any order, disjoint): lets a 20 GB device corpus be checked at full size by streaming it to the host block
+    by block. Same arithmetic as ``exact_topk``. ``valid`` is indexed by row."""
     queries = np.asarray(queries, dtype=np.float32)
     B = queries.shape[0]
-    N = corpus.shape[0]
     mc = _metric_code(metric)
     qs = row_scales(queries, mc)
     # running candidates as flat arrays (query, score, id); reduced to k per query after each block
     cq = np.zeros(0, dtype=np.int64)
     cs_ = np.zeros(0, dtype=np.float32)
     ci = np.zeros(0, dtype=np.int64)
-    for r0 in range(0, N, block_rows):
-        blk = corpus[r0:r0 + block_rows]
+    for r0, blk in blocks:
+        blk = np.asarray(blk, dtype=np.float32)
+        if blk.shape[0] == 0:
+            continue
         dots = queries @ blk.T  # fp32 BLAS
         if mc == METRIC_COSINE:
             cs = row_scales(blk, mc)
@@ -138,6 +142,19 @@ def exact_topk(corpus: np.ndarray, queries: np.ndarray, k: int, metric="cosine",
         out_s[cq, rank] = cs_
         out_i[cq, rank] = ci
     return out_s, out_i
+
+
+def exact_topk(corpus: np.ndarray, queries: np.ndarray, k: int, metric="cosine",
+               block_rows: int = 262144, id_base: int = 0, valid: np.ndarray | None = None):
+    """Exact top-k of every query against every corpus row, fp32.
+
+    score = (q . c) / (|q| |c|) for cosine (0 if either norm is 0), q . c for ip.
+    Returns (scores fp32 [B,k], ids int64 [B,k]); rows short of k (N < k) are padded
+    with (-inf, -1). ``valid`` (bool [N]) drops tombstoned rows.
+    """
+    corpus = np.asarray(corpus, dtype=np.float32)
+    blocks = ((r0, corpus[r0:r0 + block_rows]) for r0 in range(0, corpus.shape[0], block_rows))
+    return exact_topk_blocks(blocks, queries, k, metric, id_base, valid)
 
 
 def exact_topk_scores_f64(corpus: np.ndarray, queries: np.ndarray, metric="cosine") -> np.ndarray:

@@ -171,6 +171,8 @@ class Bm25Index:
     def search_terms(self, q_terms: torch.Tensor, k: int, **filter_kw):
         """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids).
         filter_kw: doc_tags / q_tag_mask / doc_group / q_group (ops.bm25_search)."""
+        if not q_terms.is_cuda:     # host term ids (pinned or not): one small H2D copy
+            q_terms = q_terms.to(self.device, non_blocking=True)
         with self._lock:   # ctypes drops the GIL inside srag_*: two searches must not interleave on one workspace
             need = ops.bm25_workspace_bytes(self.n_docs, q_terms.shape[0], k)
             if self._ws is None or self._ws.numel() < need:

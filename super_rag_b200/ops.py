@@ -215,6 +215,8 @@ def bm25_build_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: i
     n_sub = max(1, (n_docs + bd - 1) // bd)
     with torch.cuda.device(dev):
         toks = tokens.to(torch.int32, copy=True).contiguous()   # consumed: becomes the per-document distinct terms
+        if toks.numel() == 0:                                    # documents without a single token: keep the pointers non-null
+            toks = torch.zeros(1, dtype=torch.int32, device=dev)
         dp = doc_ptr.to(torch.int64).contiguous()
         uniq_tf = torch.empty_like(toks)
         doc_uniq = torch.empty(max(1, n_docs), dtype=torch.int32, device=dev)

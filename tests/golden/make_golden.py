@@ -122,28 +122,22 @@ def _load_runners():
     merge = _load_by_path("ref_merge_runner", "super_rag/nodeflow/runners/merge.py")
     rerank = _load_by_path("ref_rerank_runner", "super_rag/nodeflow/runners/rerank.py")
 
-    # pyseekdb stub: only the three names imported at seekdb_connector.py:1-2,7
-    class _Generic:
-        def __class_getitem__(cls, item):
-            return cls
+    # pyseekdb stub (tests/ref_stub.py): only the three names imported at seekdb_connector.py:1-2,7; here in its
+    # "canned" mode — every query returns the dict set through _Client.canned
+    sys.path.insert(0, os.path.dirname(OUT))
+    import ref_stub
 
-    class _Collection:
-        def __init__(self, canned):
-            self.canned = canned
+    class _CannedSwitch:
+        @property
+        def canned(self):
+            return ref_stub.STATE.canned
 
-        def query(self, query_embeddings=None, query_texts=None, n_results=None):
-            return self.canned
+        @canned.setter
+        def canned(self, value):
+            ref_stub.STATE.canned = value
 
-    class _Client:
-        canned = None
-
-        def __init__(self, **kw):
-            pass
-
-        def get_or_create_collection(self, name):
-            return _Collection(_Client.canned)
-
-    _stub("pyseekdb", Client=_Client, HNSWConfiguration=lambda **kw: kw, EmbeddingFunction=_Generic)
+    _Client = _CannedSwitch()
+    ref_stub.install()
     seek = _load_by_path("ref_seekdb_connector", "super_rag/vectorstore/seekdb_connector.py")
     return ref_models, merge, rerank, seek, _Client, SystemInput
 

@@ -165,16 +165,23 @@ def test_hash_tokenizer_and_collection_bookkeeping():
     assert col.search("alpha", 0) == []
 
 
-def test_shard_range_and_packing():
-    from super_rag_b200.sharded import pack_candidates, shard_range, unpack_candidates
+def test_shard_range_and_exchange_keys():
+    import numpy as np
+    from super_rag_b200.sharded import pack_keys_torch, shard_range, unpack_keys_torch
     for n, g in [(10_000_000, 8), (7, 3), (0, 2), (5, 8)]:
         edges = [shard_range(n, g, r) for r in range(g)]
         assert edges[0][0] == 0 and edges[-1][1] == n
         assert all(edges[r][1] == edges[r + 1][0] for r in range(g - 1))
-    s = torch.tensor([[1.5, -0.0, float("-inf")]], dtype=torch.float32)
-    i = torch.tensor([[7, 1 << 40, -1]], dtype=torch.int64)
-    s2, i2 = unpack_candidates(pack_candidates(s, i)[None])
-    assert torch.equal(s2[0].view(torch.int32), s.view(torch.int32)) and torch.equal(i2[0], i)
+    # exchange keys: orderable(score) << 32 | (2^32-1 - id); round trip, empty slots, unsigned order == (score desc, id asc)
+    s = torch.tensor([[1.5, -0.0, float("-inf"), 0.0, -2.25, 1.5]], dtype=torch.float32)
+    i = torch.tensor([[7, 3, -1, 9, (1 << 32) - 3, 6]], dtype=torch.int64)
+    keys = pack_keys_torch(s, i)
+    s2, i2 = unpack_keys_torch(keys)
+    assert torch.equal(i2, i) and torch.equal(s2[0, [0, 3, 4, 5]], s[0, [0, 3, 4, 5]])
+    assert float(s2[0, 1]) == 0.0 and float(s2[0, 2]) == float("-inf") and int(keys[0, 2]) == 0
+    ku = [int(x) for x in keys.numpy().view(np.uint64)[0]]
+    order = sorted(range(6), key=lambda j: -ku[j])
+    assert order == [5, 0, 1, 3, 4, 2]                   # 1.5 (id 6, then 7); the two zeros by id (-0.0 == +0.0); -2.25; empty
 
 
 @pytest.mark.skipif(not os.path.isdir(REFERENCE), reason="reference checkout not present on this machine")
@@ -207,3 +214,42 @@ def test_install_connector_into_unmodified_reference():
             vectorstore._REFERENCE_ADAPTOR = None
     finally:
         sys.path.remove(REFERENCE)
+
+
+def test_unmodified_reference_connector_over_the_pyseekdb_stub():
+    """SURVEY §8(c) last row: the reference's own SeekDBVectorStoreConnector.search + ContextManager.query, imported
+    unmodified from /root/reference with only `pyseekdb` stubbed (tests/ref_stub.py: exact-cosine collection.query),
+    return the oracle's ranked rows wrapped in the reference's DocumentWithScore. Skipped where the reference is absent."""
+    import numpy as np
+    import oracle
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__))))
+    import ref_stub
+    if not ref_stub.reference_available():
+        pytest.skip("needs /root/reference")
+    seek, ContextManager, models = ref_stub.load_reference_connector()
+    rng = np.random.default_rng(3)
+    n, d, k = 500, 32, 5
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    C[400] = C[7]
+    C[33] = 0
+    name = "t_ref_stub"
+    ref_stub.STATE.collections.pop(name, None)
+    cm = ContextManager(name, embedding_model=None, vectordb_type="seekdb", vectordb_ctx={"collection": name, "vector_size": d})
+    con = cm.adaptor.connector
+    assert type(con).__name__ == "SeekDBVectorStoreConnector" and type(con).__module__.startswith("super_rag.")
+    con.create_collection(vector_size=d)
+    from super_rag_b200.models import TextNode
+    ids = con.add([TextNode(text=f"t{r}", metadata={"row": r}, embedding=C[r].tolist()) for r in range(n)])
+    assert len(ids) == n
+    for qi in (7, 33, 123):
+        docs = cm.query("hello", score_threshold=0.2, topk=k, vector=C[qi].tolist(), index_types=["vector"], chat_id="c")
+        want_s, want_i = oracle.exact_topk(C, C[qi:qi + 1], k, "cosine")
+        assert [x.metadata["row"] for x in docs] == want_i[0].tolist()
+        assert np.allclose([x.score for x in docs], want_s[0], atol=1e-6)
+        assert isinstance(docs[0], models.DocumentWithScore) and docs[0].text == f"t{want_i[0, 0]}"
+    assert [x.metadata["row"] for x in cm.query("q", topk=2, vector=C[7].tolist())] == [7, 400]    # duplicates: lower row first
+    con.delete(ids=[ids[7]])
+    assert [x.metadata["row"] for x in cm.query("q", topk=1, vector=C[7].tolist())] == [400]
+    with pytest.raises(ValueError):
+        con.delete()
+    con.delete_collection()

@@ -1,13 +1,18 @@
 #!/usr/bin/env python
 """C1 (BASELINE.json configs[0]): exact cosine top-5 over 100k x 1024 fp32 chunk embeddings, 1000 queries,
-through the vector-store connector search API. Prints one JSON line:
+"via the vectorstore connector search API on CPU". One JSON line (also attached to bench.py's line at N = 1):
 
-  gpu_single   one `connector.search(QueryWithEmbedding)` call per query (the API the reference's
-               ContextManager.query uses, context/context.py:37-47) on the B200 path
-  gpu_batched  `connector.search_batch` over all queries
-  cpu_single   the CPU oracle port answering the same single-query calls (numpy fp32 on all host cores;
-               a 100-query sample) — what "the connector search API on CPU" costs
-and checks ids against the oracle (clear winners identical, scores within 1e-3).
+  gpu_single    one `connector.search(QueryWithEmbedding)` call per query — the API the reference's
+                ContextManager.query uses (context/context.py:37-47) — on the B200 connector
+  gpu_batched   `connector.search_batch` over all queries (pinned host queries in, results to the host)
+  ref_api_cpu   the UNMODIFIED reference path on the host cores: `ContextManager.query` (context/context.py:14-48) ->
+                `SeekDBVectorStoreConnector.search` (vectorstore/seekdb_connector.py:98-115) -> a `pyseekdb` stub whose
+                collection.query is the exact-cosine oracle (tests/ref_stub.py; the real client needs a SeekDB server).
+                Only where /root/reference exists (the build container); elsewhere the line says so and times the
+                stub's query directly (`cpu_stub_direct`), which is the same arithmetic without the reference wrapper.
+  parity        GPU results against the fp64 oracle on the bf16-rounded inputs (north-star rules) AND against the
+                unrounded fp32 inputs at 1e-3 — C1 is an fp32 config — with the number of ids that differ inside
+                the tolerance.
 """
 import json
 import os
@@ -21,73 +26,113 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import oracle  # noqa: E402  (checker + timed CPU baseline only)
+import ref_stub  # noqa: E402
 from parity import TOL, check_topk_against_full_scores  # noqa: E402
-from super_rag_b200.models import QueryWithEmbedding, TextNode  # noqa: E402
-from super_rag_b200.vectorstore import VectorStoreConnectorAdaptor  # noqa: E402
+from super_rag_b200.models import QueryWithEmbedding  # noqa: E402
+from super_rag_b200.vectorstore import B200Client, VectorStoreConnectorAdaptor  # noqa: E402
 
 
-def main():
-    n, d, nq, k = 100_000, 1024, 1000, 5
-    rng = np.random.default_rng(1234)
-    C = rng.standard_normal((n, d)).astype(np.float32)
+def c1_data(n=100_000, d=1024, nq=1000):
+    """SURVEY §8d C1 generator: corpus N(0,1) fp32 seed 1234 (not pre-normalised), queries seed 4321: half fresh, half
+    corpus rows + 0.1 N(0,1)."""
+    C = np.random.default_rng(1234).standard_normal((n, d)).astype(np.float32)
     rq = np.random.default_rng(4321)
     Q = rq.standard_normal((nq, d)).astype(np.float32)
-    Q[nq // 2:] = C[rq.integers(0, n, nq - nq // 2)] + 0.1 * rq.standard_normal((nq - nq // 2, d)).astype(np.float32)
-    con = VectorStoreConnectorAdaptor("b200", {"collection": "bench_c1", "vector_size": d}).connector
-    con.delete_collection()
+    src = rq.integers(0, n, nq - nq // 2)
+    Q[nq // 2:] = C[src] + 0.1 * rq.standard_normal((nq - nq // 2, d)).astype(np.float32)
+    return C, Q, src
+
+
+def run(dev=None, cpu_queries=200):
+    n, d, nq, k = 100_000, 1024, 1000, 5
+    C, Q, src = c1_data(n, d, nq)
+    B200Client().delete_collection("bench_c1")
+    con = VectorStoreConnectorAdaptor("b200", {"collection": "bench_c1", "vector_size": d,
+                                               **({"device": str(dev)} if dev is not None else {})}).connector
     con.create_collection(vector_size=d)
-    t0 = time.time()
-    for a in range(0, n, 10_000):      # bulk add in 10k-node batches (connector.add, seekdb_connector.py:68-85)
-        con.add([TextNode(text=None, metadata={"row": r}, embedding=torch.from_numpy(C[r])) for r in range(a, a + 10_000)])
+    metas = [{"row": r} for r in range(n)]
+    t0 = time.perf_counter()
+    con._collection().append(torch.from_numpy(C), metas=metas)          # bulk add, one call
     torch.cuda.synchronize()
-    add_s = time.time() - t0
+    add_s = time.perf_counter() - t0
 
     qs = [QueryWithEmbedding(query="q", top_k=k, embedding=Q[i].tolist()) for i in range(nq)]
     for q in qs[:20]:
         con.search(q)
-    t0 = time.time()
+    t0 = time.perf_counter()
     res = [con.search(q) for q in qs]
-    gpu_single_s = time.time() - t0
+    gpu_single_s = time.perf_counter() - t0
     ids_single = np.array([[r.metadata["row"] for r in x.results] for x in res])
     sc_single = np.array([[r.score for r in x.results] for x in res], dtype=np.float32)
 
     Qt = torch.from_numpy(Q).pin_memory()
     con.search_batch(Qt, k)
     torch.cuda.synchronize()
-    t0 = time.time()
+    t0 = time.perf_counter()
     for _ in range(10):
         s, i = con.search_batch(Qt, k)
         s, i = s.cpu(), i.cpu()
-    gpu_batched_s = (time.time() - t0) / 10
+    gpu_batched_s = (time.perf_counter() - t0) / 10
 
-    C_r, Q_r = oracle.bf16_round(C), oracle.bf16_round(Q)
-    full = oracle.exact_topk_scores_f64(C_r, Q_r[:200], "cosine")
-    check_topk_against_full_scores(sc_single[:200], ids_single[:200], full, k, TOL)
-    check_topk_against_full_scores(s.numpy()[:200], i.numpy()[:200], full, k, TOL)
+    # parity: (a) what the device stores (bf16-rounded inputs), (b) C1 proper: the UNROUNDED fp32 inputs at 1e-3
+    m = 250
+    full_bf16 = oracle.exact_topk_scores_f64(oracle.bf16_round(C), oracle.bf16_round(Q[-m:]), "cosine")
+    check_topk_against_full_scores(sc_single[-m:], ids_single[-m:], full_bf16, k, TOL)
+    check_topk_against_full_scores(s.numpy()[-m:], i.numpy()[-m:], full_bf16, k, TOL)
+    full_f32 = oracle.exact_topk_scores_f64(C, Q[-m:], "cosine")
+    swaps = check_topk_against_full_scores(s.numpy()[-m:], i.numpy()[-m:], full_f32, k, TOL)
+    err_f32 = float(np.abs(s.numpy()[-m:] - np.take_along_axis(full_f32, i.numpy()[-m:], 1)).max())
     assert (ids_single == i.numpy()).all()
-    planted_ok = True
-    # single-query CPU calls as the connector API would issue them: row norms precomputed at ingest (a fair
-    # store does that once), one fp32 matrix-vector product over all host cores + partition top-k per call
-    inv = oracle.row_scales(C, "cosine")
-    cpu_ids = []
-    t0 = time.time()
-    for j in range(100):
-        q = Q[j]
-        sc = (C @ q) * inv * np.float32(1.0 / np.linalg.norm(q))
-        top = np.argpartition(-sc, k)[:k]
-        cpu_ids.append(top[np.lexsort((top, -sc[top]))])
-    cpu_single_s = (time.time() - t0) / 100
-    agree = float(np.mean([set(cpu_ids[j].tolist()) == set(ids_single[j].tolist()) for j in range(100)]))
-    print(json.dumps({
-        "config": "C1", "workload": f"{n}x{d} fp32 embeddings -> bf16 on ingest, {nq} queries, top-{k}, connector search API",
+    planted_ok = bool((i.numpy()[nq // 2:, 0] == src).all())
+
+    line = {
+        "config": "C1", "workload": f"{n}x{d} fp32 embeddings (bf16 on ingest), {nq} queries, top-{k}, connector search API",
         "gpu_single_qps": nq / gpu_single_s, "gpu_single_ms_per_query": 1e3 * gpu_single_s / nq,
         "gpu_batched_qps": nq / gpu_batched_s, "gpu_batched_ms_per_batch": 1e3 * gpu_batched_s,
-        "cpu_single_qps": 1.0 / cpu_single_s, "cpu_single_ms_per_query": 1e3 * cpu_single_s,
-        "cpu_cores": os.cpu_count(), "cpu_kind": "oracle port (numpy fp32 matvec + partition, precomputed norms), 100-query sample",
-        "cpu_gpu_id_set_agreement": agree,
-        "bulk_add_s": add_s, "parity_ok": True, "planted_ok": planted_ok}), flush=True)
+        "bulk_add_s": add_s, "bulk_add_s_per_1M_rows": add_s * 1e6 / n,
+        "parity": {"queries": m, "vs_bf16_rounded_inputs_ok": True, "vs_unrounded_fp32_inputs_ok": True,
+                   "max_abs_score_error_vs_fp32": err_f32, "ids_differing_inside_tolerance_vs_fp32": int(swaps),
+                   "tolerance": TOL},
+        "planted_ok": planted_ok, "cpu_cores": os.cpu_count()}
+
+    # ---- the CPU side: the reference's own connector over the stub, one call per query -------------------------
+    sub = list(range(nq - cpu_queries, nq))
+    if ref_stub.reference_available():
+        seek, ContextManager, _ = ref_stub.load_reference_connector()
+        ref_stub.STATE.collections.pop("bench_c1_ref", None)
+        cm = ContextManager("bench_c1_ref", embedding_model=None, vectordb_type="seekdb",
+                            vectordb_ctx={"collection": "bench_c1_ref", "vector_size": d})
+        assert type(cm.adaptor.connector).__module__ == "super_rag.vectorstore.seekdb_connector"
+        coll = ref_stub.STATE.collections.setdefault("bench_c1_ref", ref_stub.StubCollection("bench_c1_ref", ref_stub.STATE))
+        coll.add([f"id{r}" for r in range(n)], embeddings=C, metadatas=metas, documents=[None] * n)
+        import logging
+        logging.getLogger("super_rag.vectorstore.seekdb_connector").setLevel(logging.WARNING)
+        cm.query("q", topk=k, vector=Q[sub[0]].tolist())
+        t0 = time.perf_counter()
+        ref_res = [cm.query("q", score_threshold=0.5, topk=k, vector=Q[j].tolist(), index_types=["vector"]) for j in sub]
+        ref_s = (time.perf_counter() - t0) / len(sub)
+        ref_ids = np.array([[r.metadata["row"] for r in x] for x in ref_res])
+        agree = float((ref_ids == ids_single[sub]).all(axis=1).mean())
+        line.update({"ref_api_cpu_qps": 1.0 / ref_s, "ref_api_cpu_ms_per_query": 1e3 * ref_s,
+                     "ref_api_cpu": f"unmodified ContextManager.query -> SeekDBVectorStoreConnector.search over the pyseekdb stub "
+                                    f"(exact fp32 cosine, numpy on {os.cpu_count()} host cpus), {len(sub)} queries",
+                     "ref_api_vs_gpu_identical_id_lists": agree})
+        ref_stub.STATE.collections.pop("bench_c1_ref", None)
+    else:
+        coll = ref_stub.StubCollection("direct", ref_stub.STATE)
+        coll.add([f"id{r}" for r in range(n)], embeddings=C, metadatas=metas, documents=[None] * n)
+        coll.query(query_embeddings=Q[sub[0]].tolist(), n_results=k)
+        t0 = time.perf_counter()
+        got = [coll.query(query_embeddings=Q[j].tolist(), n_results=k) for j in sub]
+        stub_s = (time.perf_counter() - t0) / len(sub)
+        ref_ids = np.array([[mm["row"] for mm in g["metadatas"][0]] for g in got])
+        line.update({"ref_api_cpu_qps": None, "ref_api_cpu": "unavailable: /root/reference is not present on this machine (the unmodified "
+                     "connector is driven in the build container: profiles/r02_c1_ref_api.json)",
+                     "cpu_stub_direct_qps": 1.0 / stub_s, "cpu_stub_direct_ms_per_query": 1e3 * stub_s,
+                     "cpu_stub_vs_gpu_identical_id_lists": float((ref_ids == ids_single[sub]).all(axis=1).mean())})
     con.delete_collection()
+    return line
 
 
 if __name__ == "__main__":
-    main()
+    print(json.dumps(run()), flush=True)

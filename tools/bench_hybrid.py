@@ -8,9 +8,13 @@
     python tools/bench_hybrid.py --docs 10000000 [--skip-c4] [--check 4]
 
 The index is generated on the device in document chunks (seeded, two passes: count, then scatter into
-the term-major CSR), so no 32 GB token array ever exists. --check Q re-scores Q queries with an
-independent torch restatement (index_add in ascending term order == the kernel's summation order) and
-compares ids and score bits.
+the term-major CSR), so no 32 GB token array ever exists.
+
+This module never imports `oracle/`: the full-size oracle checks and the CPU baselines are HOOKS that bench.py (the
+one place allowed to execute the oracle next to tests/) passes to run(): for the check queries the build keeps the
+(doc, tf) postings of their terms and the document lengths on the host, the hook recomputes impacts and scores with
+oracle/bm25.py and compares ids and score bits. Stand-alone (`python tools/bench_hybrid.py`) the lines carry
+"oracle_check": null.
 """
 import argparse
 import json
@@ -51,7 +55,10 @@ def gen_chunk(c, n_docs, cdf, dev):
     return t, uniq - t * m + lo, tf.to(torch.int32), dl.to(torch.int32)
 
 
-def build_index(n_docs, dev):
+def build_index(n_docs, dev, keep_terms=None, kept=None):
+    """`keep_terms` (sorted unique term ids): their canonical (ascending document) postings (doc int32, tf int32) and the
+    document lengths are copied to the host into `kept` = {"terms": {t: (doc, tf)}, "dl": int32 [n_docs]} before the
+    device copy of tf is dropped — the inputs of the full-size oracle check."""
     cdf = zipf_cdf(VOCAB, dev)
     n_chunks = (n_docs + CHUNK_DOCS - 1) // CHUNK_DOCS
     counts = torch.zeros(n_chunks, VOCAB, dtype=torch.int64, device=dev)
@@ -76,15 +83,21 @@ def build_index(n_docs, dev):
     del counts, chunk_base
     total = float(dl_all.to(torch.int64).sum().item())
     stats = Bm25Stats(n_docs=n_docs, df=df.cpu().numpy().astype(np.int64), avgdl=float(np.float32(total / n_docs)))
+    if keep_terms is not None and kept is not None:
+        kept["dl"] = dl_all.cpu().numpy()
+        kept["terms"] = {}
+        for t in keep_terms:
+            a, b = int(term_ptr[t].item()), int(term_ptr[t + 1].item())
+            kept["terms"][int(t)] = (post_doc[a:b].cpu().numpy(), post_tf[a:b].cpu().numpy())
     idx = Bm25Index.from_postings(term_ptr, post_doc, post_tf, dl_all, stats)
     del post_tf
     torch.cuda.empty_cache()
     return idx
 
 
-def make_queries(n_q, terms_per_q, dev, lo_rank=101):
+def make_queries(n_q, terms_per_q, dev, lo_rank=101, seed=4):
     """Distinct terms per query, Zipf(s=1) over ranks lo_rank..V (rank r == term id r-1)."""
-    rng = np.random.default_rng(4)
+    rng = np.random.default_rng(seed)
     r = np.arange(lo_rank, VOCAB + 1)
     p = 1.0 / r
     p /= p.sum()
@@ -127,46 +140,96 @@ def main():
     ap.add_argument("--terms", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--check", type=int, default=4)
+    ap.add_argument("--check", type=int, default=16)
     ap.add_argument("--skip-c4", action="store_true")
+    ap.add_argument("--skip-stopwords", action="store_true")
     ap.add_argument("--dim", type=int, default=1024)
     args = ap.parse_args()
     for line in run(args):
         print(json.dumps(line), flush=True)
 
 
-def run(args, dev=None):
-    """Generator of the C3 line and (unless args.skip_c4) the C4 line; bench.py attaches them to its own line."""
+class Hooks:
+    """What bench.py plugs in (it may execute oracle/; this module may not). Every hook gets the context dict and
+    returns a JSON-able dict (or None)."""
+    c3_check = None      # full-size oracle check of the C3 results
+    c3_cpu = None        # CPU baseline for C3
+    c4_check = None
+    c4_cpu = None
+
+
+def run(args, dev=None, hooks=None):
+    """Generator of the C3 line, the stop-word C3 line and (unless args.skip_c4) the C4 line; bench.py attaches them to
+    its own line."""
     dev = dev or torch.device("cuda:0")
+    hooks = hooks or Hooks()
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))
     except Exception:
         pass
     hbm = peaks.get("hbm_gbs", 6650.0)
+    hbm_src = "measured" if "hbm_gbs" in peaks else "fallback"
 
+    qt = make_queries(args.queries, args.terms, dev)
+    n_check = max(0, min(int(getattr(args, "check", 0) or 0), args.queries))
+    # the stop-word variant (SURVEY §8d "a second run includes them"): ranks 1..V, df up to ~N per term
+    qt_stop = make_queries(args.queries, args.terms, dev, lo_rank=1, seed=5)
+    n_check_stop = min(4, n_check)
+    keep = sorted(set(int(t) for t in qt[:n_check].reshape(-1).tolist() if t >= 0) |
+                  set(int(t) for t in qt_stop[:n_check_stop].reshape(-1).tolist() if t >= 0))
+    kept = {}
     t0 = time.time()
-    idx = build_index(args.docs, dev)
+    idx = build_index(args.docs, dev, keep_terms=keep if n_check else None, kept=kept)
     torch.cuda.synchronize()
     build_s = time.time() - t0
-    qt = make_queries(args.queries, args.terms, dev)
     post_bytes = idx.query_posting_bytes(qt)
     ms, (bs, bi) = timed(lambda: idx.search_terms(qt, 100), args.warmup, args.steps)
-    ok = None
-    if args.check:
-        ok = True
-        for q in range(args.check):
-            ws, wi = torch_restatement(idx, qt[q].tolist(), 100)
-            n = int((wi >= 0).sum().item())
-            ok &= bool(torch.equal(bi[q, :n], wi[:n])) and bool(torch.equal(bs[q, :n].view(torch.int32), ws[:n].view(torch.int32)))
     sorted_ok = bool((bs[:, :-1] >= bs[:, 1:]).all().item())
-    yield ({"config": "C3", "workload": f"BM25 {args.docs} docs, V={VOCAB}, nnz={idx.nnz}, {args.queries} queries x "
-                      f"{args.terms} terms (Zipf ranks 101..V), top-100", "queries_per_s": args.queries / (ms * 1e-3),
-                      "ms_per_batch": ms, "posting_bytes_per_batch": post_bytes,
-                      "roofline": {"bound": "hbm", "achieved": post_bytes / (ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-                                   "frac": post_bytes / (ms * 1e-3) / 1e9 / hbm},
-                      "index_bytes": idx.nnz * 8, "index_build_s": build_s, "restatement_check_ok": ok,
-                      "scores_sorted": sorted_ok})
+    # e2e through the public API with HOST buffers: pinned int32 term ids -> H2D -> K2 -> D2H of (scores, ids)
+    qt_host = qt.cpu().pin_memory()
+    out_s = torch.empty(args.queries, 100, dtype=torch.float32).pin_memory()
+    out_i = torch.empty(args.queries, 100, dtype=torch.int64).pin_memory()
+
+    def e2e_c3():
+        s_, i_ = idx.search_terms(qt_host, 100)
+        out_s.copy_(s_, non_blocking=True)
+        out_i.copy_(i_, non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(2):
+        e2e_c3()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_c3()
+    e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
+    ctx = {"idx": idx, "qt": qt, "qt_stop": qt_stop, "n_check": n_check, "n_check_stop": n_check_stop, "kept": kept,
+           "scores": bs, "ids": bi, "k": 100, "n_docs": args.docs, "args": args}
+    line = {"config": "C3", "workload": f"BM25 {args.docs} docs, V={VOCAB}, nnz={idx.nnz}, {args.queries} queries x "
+            f"{args.terms} terms (Zipf ranks 101..V), top-100", "queries_per_s": args.queries / (ms * 1e-3),
+            "ms_per_batch": ms, "posting_bytes_per_batch": post_bytes,
+            "roofline": {"bound": "hbm", "achieved": post_bytes / (ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                         "frac": post_bytes / (ms * 1e-3) / 1e9 / hbm, "peak_source": hbm_src,
+                         "algorithmic_bytes": "8 B x sum of df over the query terms (SURVEY 8d)",
+                         "index_bytes_per_posting": idx.bytes_per_posting() if hasattr(idx, "bytes_per_posting") else 8,
+                         "traffic": bm25_traffic(args.docs, args.queries), "traffic_source": "ncu capture under profiles/ (see profiles/bm25_traffic.json), not this run"},
+            "e2e": {"value": args.queries / (e2e_ms * 1e-3), "unit": "queries/s", "ms_per_batch": e2e_ms,
+                    "h2d_bytes_per_step": int(qt_host.numel() * 4), "d2h_bytes_per_step": args.queries * 100 * 12},
+            "index_bytes": idx.nnz * 8, "index_build_s": build_s, "scores_sorted": sorted_ok,
+            "oracle_check": hooks.c3_check(ctx) if hooks.c3_check and n_check else None,
+            "cpu_baseline": hooks.c3_cpu(ctx) if hooks.c3_cpu and n_check else None}
+    yield line
+
+    if not getattr(args, "skip_stopwords", False):
+        pb = idx.query_posting_bytes(qt_stop)
+        ms_s, (ss, si) = timed(lambda: idx.search_terms(qt_stop, 100), 1, 2)
+        ctx_s = dict(ctx, qt=qt_stop, n_check=n_check_stop, scores=ss, ids=si)
+        yield {"config": "C3-stopwords", "workload": f"as C3 but query terms drawn over ranks 1..V (df up to ~N per term: "
+               f"the two-pass threshold and the crossing-list overflow path at full size)", "queries_per_s": args.queries / (ms_s * 1e-3),
+               "ms_per_batch": ms_s, "posting_bytes_per_batch": pb,
+               "roofline": {"bound": "hbm", "achieved": pb / (ms_s * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                            "frac": pb / (ms_s * 1e-3) / 1e9 / hbm},
+               "oracle_check": hooks.c3_check(ctx_s) if hooks.c3_check and n_check_stop else None}
     if args.skip_c4:
         return
 
@@ -187,17 +250,54 @@ def run(args, dev=None):
         qb, qs = ops.ingest_rows(q32, "cosine")
         vs, vi = ops.topk_search(corpus, cs, qb, qs, 100, workspace=ws)
         s2, i2 = idx.search_terms(qt, 100)
-        return ops.fuse(torch.stack([vi, i2]), None, ops.FUSE_RRF, 10, rank_const=60), vi
+        return ops.fuse(torch.stack([vi, i2]), None, ops.FUSE_RRF, 10, rank_const=60), (vs, vi)
 
-    ms4, ((fi, fs), vi) = timed(hybrid, args.warmup, args.steps)
+    ms4, ((fi, fs), (vs, vi)) = timed(hybrid, args.warmup, args.steps)
     ms_v, _ = timed(lambda: ops.topk_search(corpus, cs, *ops.ingest_rows(q32, "cosine"), 100, workspace=ws), 1, args.steps)
     ms_f, _ = timed(lambda: ops.fuse(torch.stack([vi, bi]), None, ops.FUSE_RRF, 10, rank_const=60), 1, args.steps)
     planted_ok = bool((vi[:h, 0] == src).all().item())
+    # e2e through the public API (sharded.hybrid_search on one rank) with HOST buffers
+    from super_rag_b200.sharded import ShardedBm25Index, ShardedVectorIndex, hybrid_search
+    vec_index = ShardedVectorIndex(corpus, cs, id_base=0)
+    bm_index = ShardedBm25Index(idx)
+    q_host = q32.cpu().pin_memory()
+    o_i = torch.empty(args.queries, 10, dtype=torch.int64).pin_memory()
+    o_s = torch.empty(args.queries, 10, dtype=torch.float64).pin_memory()
+
+    def e2e_c4():
+        i_, s_ = hybrid_search(vec_index, bm_index, q_host, qt_host, 100, 10, rank_const=60)
+        o_i.copy_(i_, non_blocking=True)
+        o_s.copy_(s_, non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(2):
+        e2e_c4()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_c4()
+    e2e4_ms = (time.perf_counter() - t0) / args.steps * 1e3
+    same_as_e2e = bool(torch.equal(o_i.to(dev), fi))
+    ctx4 = dict(ctx, corpus=corpus, row_scale=cs, q32=q32, vec_scores=vs, vec_ids=vi, fused_ids=fi, fused_scores=fs,
+                rank_const=60, k_out=10)
     yield ({"config": "C4", "workload": f"hybrid: vector top-100 ({args.docs}x{args.dim} bf16) + BM25 top-100 -> RRF(60) -> top-10, "
-                      f"{args.queries} queries", "queries_per_s": args.queries / (ms4 * 1e-3), "ms_per_batch": ms4,
-                      "ms_vector_top100": ms_v, "ms_bm25_top100": ms, "ms_fuse": ms_f,
-                      "vector_tflops": 2.0 * args.queries * args.docs * args.dim / (ms_v * 1e-3) / 1e12,
-                      "planted_top1_ok": planted_ok})
+            f"{args.queries} queries", "queries_per_s": args.queries / (ms4 * 1e-3), "ms_per_batch": ms4,
+            "ms_vector_top100": ms_v, "ms_bm25_top100": ms, "ms_fuse": ms_f,
+            "vector_tflops": 2.0 * args.queries * args.docs * args.dim / (ms_v * 1e-3) / 1e12,
+            "e2e": {"value": args.queries / (e2e4_ms * 1e-3), "unit": "queries/s", "ms_per_batch": e2e4_ms,
+                    "h2d_bytes_per_step": int(q_host.numel() * 4 + qt_host.numel() * 4),
+                    "d2h_bytes_per_step": args.queries * 10 * 16, "same_ids_as_device_run": same_as_e2e},
+            "planted_top1_ok": planted_ok,
+            "oracle_check": hooks.c4_check(ctx4) if hooks.c4_check and n_check else None,
+            "cpu_baseline": hooks.c4_cpu(ctx4) if hooks.c4_cpu and n_check else None})
+
+
+def bm25_traffic(n_docs, n_queries):
+    """dram bytes per main-pass launch from the committed ncu capture of this configuration (None if there is none)."""
+    try:
+        with open(os.path.join(os.path.dirname(__file__), "..", "profiles", "bm25_traffic.json")) as f:
+            return json.load(f).get(f"dram_bytes_per_launch_docs{n_docs}_q{n_queries}")
+    except Exception:
+        return None
 
 
 if __name__ == "__main__":
