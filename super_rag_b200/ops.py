@@ -236,9 +236,10 @@ def bm25_build_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: i
         post_doc = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]   # padded: 128-bit loads stay inside
         post_tf = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]
         fill = torch.empty(max(1, vocab * n_sub), dtype=torch.int32, device=dev)
-        _lib.check(lib.srag_bm25_build_fill(_ptr(toks), _ptr(uniq_tf), _ptr(dp), _ptr(doc_uniq), n_docs, vocab,
-                                            _ptr(block_ptr), _ptr(fill), _ptr(post_doc), _ptr(post_tf), st),
-                   "srag_bm25_build_fill")
+        if nnz:   # nothing to fill for a collection whose texts all tokenise to nothing
+            _lib.check(lib.srag_bm25_build_fill(_ptr(toks), _ptr(uniq_tf), _ptr(dp), _ptr(doc_uniq), n_docs, vocab,
+                                                _ptr(block_ptr), _ptr(fill), _ptr(post_doc), _ptr(post_tf), st),
+                       "srag_bm25_build_fill")
     return term_ptr, post_doc, post_tf, dl[:n_docs], df, block_ptr
 
 

@@ -246,7 +246,7 @@ class DeviceCollection:
             arrays = {"rows": self.rows, "row_scale": self.row_scale}
             if self.n:
                 arrays["row_tags"], arrays["row_group"] = self._tags[:self.n], self._group[:self.n]
-            arrays.update({k: torch.from_numpy(v) for k, v in self.docs.to_arrays().items()})
+            arrays.update({k: torch.from_numpy(np.array(v)) for k, v in self.docs.to_arrays().items()})
             shardio.write_shard(path, "vector", meta, arrays, {"tagger": self.tagger.state()})
 
     @classmethod
