@@ -115,8 +115,14 @@ int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int* n_calls);
 /* ---- K2: BM25 -----------------------------------------------------------------------
  * The `fulltext_search` node the reference declares but does not implement
  * (super_rag/nodeflow/runners/merge.py:18-20, super_rag/schema/view_models.py:1043-1047).
- * Index layout (CSR by term): term_ptr int64 [vocab+1]; post_doc int32 [nnz] ascending
- * inside a term (until srag_bm25_bank_order permutes the doc-block slices); post_imp fp32 [nnz]. Numeric contract: oracle/bm25.py docstring.
+ * Index layout (CSR by term). While it is BUILT: term_ptr int64 [vocab+1], post_doc int32 [nnz] ascending inside a
+ * term, post_tf int32 [nnz], block_ptr int64 [vocab, n_sub+1]. As it is SEARCHED (srag_bm25_pack_plan / _fill):
+ *   slice_ptr uint32 [vocab, n_sub+1]  start of every (term, 2048-document sub-block) slice in GROUPS of 4 postings: every
+ *                                      slice starts on a group and is padded to whole groups with zero-impact postings;
+ *   post_off  uint16 [4 * groups]      (doc & 16383) * 4 = byte offset of the document's fp32 accumulator inside the tile
+ *                                      of its 16384-document block (the slice names the block); padding: a trash offset;
+ *   post_imp  fp32   [4 * groups]      impact (> 0; exactly 0 marks padding)
+ * = 6 bytes per posting in HBM. Both arrays are padded by 8 entries. Numeric contract: oracle/bm25.py docstring.
  *
  * srag_bm25_impacts: imp = idf[term] * tf*(k1+1) / (tf + k1*(1-b+b*dl/avgdl)), one IEEE
  * fp32 op per step; the term of posting p is found by bisection in term_ptr.
@@ -129,14 +135,23 @@ int srag_bm25_impacts(const int64_t* term_ptr, int vocab, const int32_t* post_do
 int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* post_doc, int vocab,
                           int64_t n_docs, int block_docs, int64_t* block_ptr, void* stream);
 int srag_bm25_block_docs(void);   /* doc-range width one CTA accumulates in shared memory */
-/* Index-build step after srag_bm25_block_index: permutes the postings INSIDE every (term, doc-block) slice
- * (doc_in/imp_in -> doc_out/imp_out, same offsets, not in place; arrays padded by 4 entries like the inputs)
- * so that the 32 accumulators one warp of the scoring kernel touches per shared-memory access fall on
- * distinct banks where the slice allows it. Every posting of a slice is a distinct document that receives
- * one add per query, so scores are unchanged bit for bit; block_ptr stays valid. After this call post_doc is
- * ascending per (term, block) slice only as a SET, not as a sequence.                                     */
-int srag_bm25_bank_order(const int64_t* block_ptr, int vocab, int64_t n_docs, const int32_t* doc_in,
-                         const float* imp_in, int32_t* doc_out, float* imp_out, void* stream);
+/* Index-build steps after srag_bm25_block_index: canonical postings -> the searched layout.
+ *   srag_bm25_pack_plan: slice_ptr from block_ptr (three small kernels: per-term group counts, a scan over the
+ *     vocabulary, a scan along every term). scratch int64 [2 * vocab + 1] (device); afterwards scratch[2 * vocab] is the
+ *     total number of groups (the caller reads it back to size post_off / post_imp = 4 * groups + 8 entries).
+ *   srag_bm25_pack_fill: writes post_off / post_imp. With permute != 0 the postings INSIDE every slice are laid out so that
+ *     the 32 accumulators one warp of the scoring kernel touches per shared-memory access fall on distinct banks where
+ *     the slice allows it (every posting of a slice is a distinct document that receives one add per query, so scores
+ *     are unchanged bit for bit); permute = 0 keeps ascending documents.                                            */
+int srag_bm25_pack_plan(const int64_t* block_ptr, int vocab, int64_t n_docs, int64_t* scratch, uint32_t* slice_ptr,
+                        void* stream);
+int srag_bm25_pack_fill(const int64_t* block_ptr, const uint32_t* slice_ptr, int vocab, int64_t n_docs,
+                        const int32_t* doc_in, const float* imp_in, uint16_t* off_out, float* imp_out, int permute,
+                        void* stream);
+/* The inverse: doc_out int32 [4 * groups] = document of every stored posting (-1 for padding), term_out (may be NULL) its
+ * term. Not on the search path: tests, canonical postings, shard conversion.                                      */
+int srag_bm25_unpack_docs(const uint32_t* slice_ptr, int vocab, int64_t n_docs, const uint16_t* post_off,
+                          const float* post_imp, int32_t* doc_out, int32_t* term_out, void* stream);
 int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, size_t* bytes);
 /* Index build from tokens without a global sort (the reference has no index build, contract:
  * oracle/bm25.py build_postings). Two calls, because the number of postings is only known after the first:
@@ -156,14 +171,14 @@ int srag_bm25_build_fill(const int32_t* uniq_term, const int32_t* uniq_tf, const
                          uint32_t* fill, int32_t* post_doc, int32_t* post_tf, void* stream);
 /* q_terms int32 [n_queries, max_terms]: unique term ids in ASCENDING order, -1 padded.
  * out_* [n_queries, k]; only documents matching >= 1 term are candidates.               */
-int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,
+int srag_bm25_search(const uint32_t* slice_ptr, const uint16_t* post_off, const float* post_imp,
                      int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries,
                      int max_terms, int k, int64_t id_base, float* out_scores, int64_t* out_ids,
                      void* workspace, size_t workspace_bytes, void* stream);
 /* Same with the metadata pre-filter of srag_topk_search_filtered applied to documents: only admitted
  * documents are scored into the result (doc_tags / doc_group are indexed by the document's position in
  * THIS index, 0 .. n_docs-1; q_tag_mask / q_group per query).                                    */
-int srag_bm25_search_filtered(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,
+int srag_bm25_search_filtered(const uint32_t* slice_ptr, const uint16_t* post_off, const float* post_imp,
                               int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries,
                               int max_terms, int k, int64_t id_base, const uint32_t* doc_tags,
                               const int32_t* doc_group, const uint32_t* q_tag_mask, const int32_t* q_group,

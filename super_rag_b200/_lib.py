@@ -37,7 +37,9 @@ SIGNATURES = {
     "srag_bm25_impacts": [_vp, _i32, _vp, _vp, _i64, _vp, _vp, _f32, _vp, _vp],
     "srag_bm25_block_index": [_vp, _vp, _i32, _i64, _i32, _vp, _vp],
     "srag_bm25_block_docs": [],
-    "srag_bm25_bank_order": [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp],
+    "srag_bm25_pack_plan": [_vp, _i32, _i64, _vp, _vp, _vp],
+    "srag_bm25_pack_fill": [_vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp, _i32, _vp],
+    "srag_bm25_unpack_docs": [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp],
     "srag_bm25_workspace_bytes": [_i64, _i32, _i32, C.POINTER(_sz)],
     "srag_bm25_build_plan": [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "srag_bm25_build_fill": [_vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp],

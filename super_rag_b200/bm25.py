@@ -51,39 +51,60 @@ class Bm25Stats:
 
 
 class Bm25Index:
-    """CSR-by-term postings (int32 doc, fp32 impact) + per-term doc-block offsets, all on one GPU."""
+    """CSR-by-term postings as they are SEARCHED, all on one GPU:
+      slice_ptr  [V, n_sub+1] (uint32 patterns)  start of every (term, 2048-document sub-block) slice, in groups of 4 postings
+      post_off   (uint16 patterns)              byte offset of the document's accumulator inside its 16384-document block's tile
+      post_imp   fp32                           impact; 0 marks the padding that rounds every slice up to whole groups
+    = 6 bytes per posting. term_ptr (int64 [V+1]) keeps the REAL document frequencies (df = diff). The int32 document ids
+    only exist while the index is built; `post_doc` / `canonical_postings` rebuild them on demand (tests, shard conversion)."""
 
-    def __init__(self, term_ptr, post_doc, post_imp, block_ptr, n_docs: int, vocab: int, dl, stats: Bm25Stats,
+    def __init__(self, term_ptr, slice_ptr, post_off, post_imp, n_docs: int, vocab: int, dl, stats: Bm25Stats,
                  id_base: int = 0, bank_ordered: bool = False):
-        self.term_ptr, self.post_doc, self.post_imp, self.block_ptr = term_ptr, post_doc, post_imp, block_ptr
+        self.term_ptr, self.slice_ptr, self.post_off, self.post_imp = term_ptr, slice_ptr, post_off, post_imp
         self.n_docs, self.vocab, self.dl, self.stats, self.id_base = n_docs, vocab, dl, stats, id_base
         self.bank_ordered = bank_ordered
         self._ws = None
         self._ws_event = None
         self._lock = threading.Lock()   # the scoring workspace belongs to the index: one search at a time
 
-    def _bank_order(self) -> None:
-        """Permute every (term, doc-block) slice for conflict-free accumulation (ops.bm25_bank_order). Scores do not
-        depend on the order inside a slice. SRAG_BM25_BANK_ORDER=0 keeps ascending documents (A/B measurements)."""
-        if self.bank_ordered or os.environ.get("SRAG_BM25_BANK_ORDER", "1") == "0":
-            return
-        self.post_doc, self.post_imp = ops.bm25_bank_order(self.block_ptr, self.post_doc, self.post_imp, self.n_docs)
-        self.bank_ordered = True
+    @staticmethod
+    def bytes_per_posting() -> int:
+        return 6
+
+    @property
+    def post_doc(self) -> torch.Tensor:
+        """int32 document id of every STORED posting (-1 = padding), in the stored order."""
+        return ops.bm25_unpack_docs(self.slice_ptr, self.post_off, self.post_imp, self.n_docs)
+
+    @classmethod
+    def _pack(cls, term_ptr, post_doc, post_imp, block_ptr, n_docs, vocab, dl, stats, id_base):
+        """Canonical postings -> the searched layout. SRAG_BM25_BANK_ORDER=0 keeps ascending documents inside every slice
+        (A/B measurements)."""
+        permute = os.environ.get("SRAG_BM25_BANK_ORDER", "1") != "0"
+        slice_ptr, post_off, post_imp = ops.bm25_pack(block_ptr, post_doc, post_imp, n_docs, permute=permute)
+        return cls(term_ptr, slice_ptr, post_off, post_imp, n_docs, vocab, dl, stats, id_base, bank_ordered=permute)
 
     def canonical_postings(self):
-        """(post_doc, post_imp) with ascending documents inside every term — the order the oracle builds."""
-        df = self.term_ptr[1:] - self.term_ptr[:-1]
-        term = torch.repeat_interleave(torch.arange(self.vocab, device=self.device, dtype=torch.int64), df)
-        order = torch.argsort(term * max(1, self.n_docs) + self.post_doc.to(torch.int64))
-        return self.post_doc[order], self.post_imp[order]
+        """(post_doc int32, post_imp fp32) without padding, ascending documents inside every term — the order the oracle
+        builds."""
+        doc, term = ops.bm25_unpack_docs(self.slice_ptr, self.post_off, self.post_imp, self.n_docs, with_terms=True)
+        keep = doc >= 0
+        doc, term, imp = doc[keep], term[keep], self.post_imp[keep]
+        order = torch.argsort(term.to(torch.int64) * max(1, self.n_docs) + doc.to(torch.int64))
+        return doc[order], imp[order]
 
     @property
     def nnz(self) -> int:
-        return int(self.post_doc.numel())
+        """Real postings (padding excluded)."""
+        return int(self.term_ptr[-1].item())
+
+    @property
+    def nnz_stored(self) -> int:
+        return int(self.post_off.numel())
 
     @property
     def device(self):
-        return self.post_doc.device
+        return self.post_off.device
 
     # ---- build -----------------------------------------------------------------------------
     @staticmethod
@@ -105,17 +126,10 @@ class Bm25Index:
             total = float(dl.to(torch.int64).sum().item())
             stats = Bm25Stats(n_docs=n_docs, df=df, avgdl=float(np.float32(total / max(1, n_docs))))
         idf = torch.from_numpy(idf_from_df(stats.df, stats.n_docs)).to(dev)
-        # keep the postings 16-byte aligned and padded so 128-bit loads never leave the buffer
-        nnz = post_doc.numel()
-        pd = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)
-        pd[:nnz] = post_doc
-        post_doc = pd[:nnz]
         imp = ops.bm25_impacts(term_ptr, post_doc, post_tf, idf, dl, stats.avgdl)
         if block_ptr is None:   # the token build produces the sub-block offsets itself
             block_ptr = ops.bm25_block_index(term_ptr, post_doc, n_docs)
-        idx = cls(term_ptr, post_doc, imp, block_ptr, n_docs, vocab, dl, stats, id_base)
-        idx._bank_order()
-        return idx
+        return cls._pack(term_ptr, post_doc, imp, block_ptr, n_docs, vocab, dl, stats, id_base)
 
     @classmethod
     def from_tokens(cls, tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: int, stats: Optional[Bm25Stats] = None,
@@ -125,52 +139,62 @@ class Bm25Index:
 
     # ---- persistence (on-disk shard) ------------------------------------
     def save(self, path: str) -> None:
+        """The searched arrays are written as they are (no rebuild on load)."""
         from . import shardio
         meta = {"n_docs": self.n_docs, "vocab": self.vocab, "id_base": self.id_base, "stats_n_docs": self.stats.n_docs,
-                "avgdl": float(self.stats.avgdl), "bank_ordered": bool(self.bank_ordered), "block_docs": ops.bm25_block_docs()}
+                "avgdl": float(self.stats.avgdl), "bank_ordered": bool(self.bank_ordered), "layout": "slices-v2",
+                "sub_docs": ops.bm25_block_docs(), "abi": 2}
         shardio.write_shard(path, "bm25", meta, {
-            "term_ptr": self.term_ptr, "post_doc": self.post_doc, "post_imp": self.post_imp, "dl": self.dl,
-            "df": torch.from_numpy(np.ascontiguousarray(self.stats.df, dtype=np.int64))})
+            "term_ptr": self.term_ptr, "slice_ptr": self.slice_ptr, "post_off": self.post_off, "post_imp": self.post_imp,
+            "dl": self.dl, "df": torch.from_numpy(np.ascontiguousarray(self.stats.df, dtype=np.int64))})
 
     @classmethod
     def load(cls, path: str, device) -> "Bm25Index":
-        """Impacts are stored, so no statistic is recomputed: scores are bit-identical to the saved index.
-        Only the per-block offsets are rebuilt (they depend on the library's block size)."""
+        """Impacts are stored, so no statistic is recomputed: scores are bit-identical to the saved index. A shard in the
+        searched layout of this library is used as it is; one written by round 1 (int32 documents) is packed again."""
         from . import shardio
         dev = torch.device(device)
         meta, a, _ = shardio.read_shard(path, device=dev, expect_kind="bm25")
-        nnz = a["post_doc"].numel()
-        if a["post_imp"].numel() != nnz or a["term_ptr"].numel() != int(meta["vocab"]) + 1 or \
-                a["dl"].numel() != int(meta["n_docs"]):
+        n_docs, vocab = int(meta["n_docs"]), int(meta["vocab"])
+        if a["term_ptr"].numel() != vocab + 1 or a["dl"].numel() != n_docs:
             raise shardio.ShardError(f"{path}: sections do not match the header")
-        # 16-byte aligned and padded by one group of 4 postings, as from_postings() lays them out
-        pd = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)
-        pi = torch.zeros(nnz + 4, dtype=torch.float32, device=dev)
-        pd[:nnz] = a["post_doc"]
-        pi[:nnz] = a["post_imp"]
         stats = Bm25Stats(n_docs=int(meta["stats_n_docs"]), df=a["df"].cpu().numpy().astype(np.int64),
                           avgdl=float(meta["avgdl"]))
         term_ptr = a["term_ptr"]
-        n_docs, vocab = int(meta["n_docs"]), int(meta["vocab"])
-        ordered = bool(meta.get("bank_ordered", False))
-        idx = cls(term_ptr, pd[:nnz], pi[:nnz], None, n_docs, vocab, a["dl"], stats, int(meta["id_base"]),
-                  bank_ordered=ordered)
-        if ordered and int(meta.get("block_docs", 0)) != ops.bm25_block_docs():
-            # written by a library with another doc-block width: back to ascending documents, then re-ordered below
-            d, w = idx.canonical_postings()
-            pd[:nnz] = d
-            pi[:nnz] = w
-            idx.bank_ordered = False
-        # The offsets are found by bisection on "doc < j * block_docs", which is monotone along a term as long as its
-        # doc-block slices follow one another — true for ascending and for bank-ordered postings of this block width.
-        idx.block_ptr = ops.bm25_block_index(term_ptr, idx.post_doc, n_docs)
-        idx._bank_order()
-        return idx
+        if meta.get("layout") == "slices-v2" and int(meta.get("sub_docs", 0)) == ops.bm25_block_docs():
+            n = a["post_off"].numel()
+            n_sub = max(1, -(-n_docs // ops.bm25_block_docs()))
+            if a["post_imp"].numel() != n or tuple(a["slice_ptr"].shape) != (vocab, n_sub + 1) or n % 4:
+                raise shardio.ShardError(f"{path}: sections do not match the header")
+            po = torch.zeros(n + ops.BM25_PAD, dtype=torch.int16, device=dev)
+            pi = torch.zeros(n + ops.BM25_PAD, dtype=torch.float32, device=dev)
+            po[:n] = a["post_off"]
+            pi[:n] = a["post_imp"]
+            return cls(term_ptr, a["slice_ptr"].contiguous(), po[:n], pi[:n], n_docs, vocab, a["dl"], stats,
+                       int(meta["id_base"]), bank_ordered=bool(meta.get("bank_ordered", False)))
+        if "post_doc" not in a:
+            raise shardio.ShardError(f"{path}: unknown BM25 shard layout {meta.get('layout')!r}")
+        # round-1 shard: int32 documents, ascending or bank-ordered per 2048-document slice. The slice offsets are found
+        # by bisection on "doc < j * sub_docs", monotone along a term either way; slices are then sorted back to ascending
+        # documents (they are sets) and packed.
+        pd, pi = a["post_doc"].contiguous(), a["post_imp"].contiguous()
+        if pi.numel() != pd.numel():
+            raise shardio.ShardError(f"{path}: sections do not match the header")
+        df = term_ptr[1:] - term_ptr[:-1]
+        term = torch.repeat_interleave(torch.arange(vocab, device=dev, dtype=torch.int64), df)
+        order = torch.argsort(term * max(1, n_docs) + pd.to(torch.int64))
+        pd, pi = pd[order].contiguous(), pi[order].contiguous()
+        block_ptr = ops.bm25_block_index(term_ptr, pd, n_docs)
+        return cls._pack(term_ptr, pd, pi, block_ptr, n_docs, vocab, a["dl"], stats, int(meta["id_base"]))
 
     # ---- search ----------------------------------------------------------------------------
     def search_terms(self, q_terms: torch.Tensor, k: int, **filter_kw):
         """q_terms int32 [B,T] (unique ascending, -1 padded) on the index device -> (scores, ids).
         filter_kw: doc_tags / q_tag_mask / doc_group / q_group (ops.bm25_search)."""
+        if self.nnz_stored == 0:    # no postings (every text tokenised to nothing): nothing can match
+            B = q_terms.shape[0]
+            return (torch.full((B, k), float("-inf"), dtype=torch.float32, device=self.device),
+                    torch.full((B, k), -1, dtype=torch.int64, device=self.device))
         if not q_terms.is_cuda:     # host term ids (pinned or not): one small H2D copy
             q_terms = q_terms.to(self.device, non_blocking=True)
         with self._lock:   # ctypes drops the GIL inside srag_*: two searches must not interleave on one workspace
@@ -180,7 +204,7 @@ class Bm25Index:
             stream = torch.cuda.current_stream(self.device)
             if self._ws_event is not None:   # ... nor overlap on it from two streams
                 stream.wait_event(self._ws_event)
-            out = ops.bm25_search(self.block_ptr, self.post_doc, self.post_imp, self.n_docs, q_terms, k,
+            out = ops.bm25_search(self.slice_ptr, self.post_off, self.post_imp, self.n_docs, q_terms, k,
                                   id_base=self.id_base, workspace=self._ws, **filter_kw)
             self._ws_event = torch.cuda.Event()
             self._ws_event.record(stream)
@@ -191,7 +215,8 @@ class Bm25Index:
         return self.search_terms(qt, k, **filter_kw)
 
     def query_posting_bytes(self, q_terms: torch.Tensor) -> int:
-        """Algorithmic bytes of a batch: 8 B per posting of every query term."""
+        """Algorithmic bytes of a batch: 8 B per posting of every query term; the index
+        itself stores 6 B per posting, so the HBM traffic of the scan is below this figure."""
         df = (self.term_ptr[1:] - self.term_ptr[:-1])
         t = q_terms.to(torch.int64)
         m = t >= 0

@@ -1,6 +1,8 @@
 // K2: BM25 scoring over CSR postings. HBM-bound integer/float streaming work — no tensor cores.
 //
-// Postings are CSR by term; block_ptr gives the first posting of every (term, BM25_SUB_DOCS = 2048 documents) slice.
+// Postings are CSR by term: post_off uint16 [nnz] = the document's BYTE offset inside its 16384-document block's fp32
+// accumulator tile ((doc & 16383) * 4; the slice a posting belongs to names the block), post_imp fp32 [nnz] = its impact:
+// 6 bytes per posting in HBM. block_ptr gives the first posting of every (term, BM25_SUB_DOCS = 2048 documents) slice.
 // Query terms are applied in ASCENDING term id; inside a term every posting hits a distinct document, so plain
 // (non-atomic) read-add-write is race-free and the per-document sum order is fixed -> bit-exact with oracle/bm25.py.
 // Selection is two-pass: a SAMPLE pass over the sub-blocks of every 32nd / 16th block reports a few true document scores
@@ -18,7 +20,8 @@
 //                      distinct shared-memory banks (scores unchanged: the order inside a slice is free).
 //   srag_launch_finalize(_ex/_live) (topk_gemm.cu) merges the lists / candidate region of a query.
 //
-// Algorithmic bytes per query = 8 * sum_t df(t)  (int32 doc + fp32 impact per posting).
+// Algorithmic bytes per query = 8 * sum_t df(t)  (int32 doc + fp32 impact per posting); the index itself
+// stores 6 (16-bit offset + fp32 impact), so HBM traffic is below the algorithmic figure.
 // The reference has no BM25 arithmetic; contract: oracle/bm25.py docstring.
 #include <stdlib.h>
 
@@ -58,8 +61,8 @@ struct SlotMeta {  // written by the producer before it issues the slot's copies
     int32_t lo_rel, hi_rel;  // valid postings of the chunk: [lo_rel, hi_rel)
     uint32_t flags;
     float tau;               // sample k-th best score of the query (0 = none)
-    uint32_t pos;            // ring position of the chunk's first posting (multiple of 4)
-    uint32_t n;              // postings copied (multiple of 4)
+    uint32_t pos;            // ring position of the chunk's first posting (multiple of 8)
+    uint32_t n;              // postings copied (multiple of 8)
 };
 
 __device__ __forceinline__ void consumer_sync() { ptx::named_bar_sync(1, BM25_THREADS); }
@@ -74,7 +77,7 @@ struct ProducerState {  // ring bookkeeping, handed between the two producer war
 struct Bm25Smem {
     float acc[BM25_BLOCK_DOCS];
     uint32_t hist[RADIX_BINS];
-    alignas(128) int32_t ring_doc[BM25_RING];
+    alignas(128) uint16_t ring_doc[BM25_RING];   // byte offsets into acc[] (block-relative)
     alignas(128) float ring_imp[BM25_RING];
     SlotMeta meta[BM25_SLOTS];
     uint64_t full[BM25_SLOTS], empty[BM25_SLOTS];
@@ -322,7 +325,8 @@ struct Bm25Filter {  // metadata pre-filter, same rule as K1 (srag_topk_search_f
 
 template <bool FILT>  // FILT: the unfiltered instantiation carries none of the filter code
 __global__ void __launch_bounds__(BM25_CTA_THREADS, BM25_CTAS_PER_SM)
-bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, const int32_t* __restrict__ post_doc,
+bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], groups of 4 postings */,
+                  const uint16_t* __restrict__ post_doc,
                   const float* __restrict__ post_imp, int n_blocks, int n_sub, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
                   const float* __restrict__ tau /* [nq][k] sorted sample scores, phase 1 */,
@@ -375,9 +379,9 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
             hi = 0;
             if (p.ql < nq && t >= 0) {
                 const int s0 = block_of(p.j) * BM25_SUBS;  // the tile = sub-blocks s0 .. s0 + BM25_SUBS - 1
-                const int64_t* bp = block_ptr + (size_t)t * (n_sub + 1);
-                lo = __ldg(bp + s0);
-                hi = __ldg(bp + (s0 + BM25_SUBS < n_sub ? s0 + BM25_SUBS : n_sub));
+                const uint32_t* sp = slice_ptr + (size_t)t * (n_sub + 1);
+                lo = (int64_t)__ldg(sp + s0) << 2;
+                hi = (int64_t)__ldg(sp + (s0 + BM25_SUBS < n_sub ? s0 + BM25_SUBS : n_sub)) << 2;
             }
         };
         // The two producer warps take ALTERNATE items of the CTA's list: planning an item (slice lookup, scans,
@@ -389,6 +393,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
         ProducerState& ps = sm->prod;
         uint32_t slot = 0, tail_slot = 0, tail_par = 0, inflight = 0, pos = 0, free_post = BM25_RING;
         static_assert(BM25_SLOTS == 32, "descriptor slots are addressed with 5-bit arithmetic");
+        static_assert(BM25_BLOCK_DOCS * 4 <= 65536, "byte offsets inside a block's tile must fit 16 bits");
         auto acquire_turn = [&](uint32_t seq) {
             uint32_t spins = 0;
             while (*reinterpret_cast<volatile uint32_t*>(&ps.turn) != seq) {
@@ -450,11 +455,12 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
                     ptrs_at(p0, t, lo, hi);
                 }
                 const int nt = max_terms - j0 < 32 ? max_terms - j0 : 32;
-                // Lane u plans term u: the slice rounded out to groups of 4 postings (the arrays are padded)
-                // and cut into chunks. A term has at most BM25_BLOCK_DOCS postings inside a block.
-                const int64_t a = lo & ~(int64_t)3;
+                // Lane u plans term u: the slice rounded out to groups of 8 postings (16 bytes of 16-bit offsets: the unit
+                // of a bulk copy; the arrays are padded) and cut into chunks. A term has at most BM25_BLOCK_DOCS postings
+                // inside a block.
+                const int64_t a = lo & ~(int64_t)7;
                 const uint32_t hi_off = (uint32_t)(hi - a), lo_off = (uint32_t)(lo - a);
-                const uint32_t len = lo == hi ? 0u : (hi_off + 3u) & ~3u;
+                const uint32_t len = lo == hi ? 0u : (hi_off + 7u) & ~7u;
                 const uint32_t cnt = (len + BM25_CHUNK - 1) / BM25_CHUNK;
                 const uint32_t incl = warp_incl_scan(cnt);
                 const uint32_t total = __shfl_sync(FULL, incl, 31);
@@ -490,7 +496,7 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
                     md.flags = (first_of_item && i == 0) ? SLOT_NEW_ITEM : (term_barrier ? SLOT_NEW_TERM : 0u);
                     md.tau = tau0;
                     md.n = n;
-                    const int32_t* src_d = post_doc + a_u + off;
+                    const uint16_t* src_d = post_doc + a_u + off;
                     const float* src_w = post_imp + a_u + off;
                     if (!have_turn) {  // everything above ran while the other warp was issuing its item
                         acquire_turn(seq);
@@ -511,12 +517,12 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
                             md.pos = my_pos;
                             sm->meta[my_slot] = md;
                             ps.slot_post[my_slot] = n;
-                            ptx::mbar_arrive_expect_tx(bar, n * 8u);
+                            ptx::mbar_arrive_expect_tx(bar, n * 6u);
                             const uint32_t n1 = my_pos + n <= (uint32_t)BM25_RING ? n : BM25_RING - my_pos;  // up to the ring's end
-                            ptx::bulk_load_1d(&sm->ring_doc[my_pos], src_d, n1 * 4u, bar);
+                            ptx::bulk_load_1d(&sm->ring_doc[my_pos], src_d, n1 * 2u, bar);
                             ptx::bulk_load_1d(&sm->ring_imp[my_pos], src_w, n1 * 4u, bar);
                             if (n1 < n) {  // wrapped remainder
-                                ptx::bulk_load_1d(&sm->ring_doc[0], src_d + n1, (n - n1) * 4u, bar);
+                                ptx::bulk_load_1d(&sm->ring_doc[0], src_d + n1, (n - n1) * 2u, bar);
                                 ptx::bulk_load_1d(&sm->ring_imp[0], src_w + n1, (n - n1) * 4u, bar);
                             }
                         }
@@ -668,23 +674,25 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
             consumer_sync();
         }
         const int rel = 4 * (int)threadIdx.x;
-        int4 dd = make_int4(0, 0, 0, 0);
+        uint2 dd = make_uint2(0u, 0u);   // four 16-bit byte offsets into acc[]
         float4 ww = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool active = rel < m.hi_rel && rel + 4 > m.lo_rel;
         if (active) {
             uint32_t idx = m.pos + (uint32_t)rel;
             if (idx >= (uint32_t)BM25_RING) idx -= BM25_RING;
-            dd = *reinterpret_cast<const int4*>(&sm->ring_doc[idx]);
+            dd = *reinterpret_cast<const uint2*>(&sm->ring_doc[idx]);
             ww = *reinterpret_cast<const float4*>(&sm->ring_imp[idx]);
         }
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
         if (active && !(debug & 1)) {
             const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
-            const bool m0 = rel >= m.lo_rel && rel < m.hi_rel, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel;
-            const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel;
-            const int r0 = m0 ? dd.x - doc_base : 0, r1 = m1 ? dd.y - doc_base : 0;
-            const int r2 = m2 ? dd.z - doc_base : 0, r3 = m3 ? dd.w - doc_base : 0;
+            // (slices are padded to whole groups of 4 with zero-impact postings whose offsets only mean something to
+            // bm25_sub_kernel: skipped here — a real impact is > 0)
+            const bool m0 = rel >= m.lo_rel && rel < m.hi_rel && ww.x != 0.f, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel && ww.y != 0.f;
+            const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel && ww.z != 0.f, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel && ww.w != 0.f;
+            const int r0 = m0 ? (int)((dd.x & 0xFFFFu) >> 2) : 0, r1 = m1 ? (int)(dd.x >> 18) : 0;
+            const int r2 = m2 ? (int)((dd.y & 0xFFFFu) >> 2) : 0, r3 = m3 ? (int)(dd.y >> 18) : 0;
             // the four reads are issued together, then the adds, then the writes (one latency, not four)
             const float a0 = sm->acc[r0], a1 = sm->acc[r1], a2 = sm->acc[r2], a3 = sm->acc[r3];
             const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y), n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
@@ -731,27 +739,38 @@ bm25_items_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */
 //   * more crossings in one sub-block than SUB_CAND, or a full region, flags the QUERY; flagged queries are redone
 //     by bm25_items_kernel (exact top-k of every block) after their region is cleared. Massive ties end up there.
 // Per-document sums are formed exactly as in bm25_items_kernel: bit-exact with the oracle.
-constexpr int SUB_WARPS = 27;   // 27 x 8 KB of accumulators + candidate lists = 222 KB: one CTA per SM
+constexpr int SUB_WARPS = 27;   // 27 x (8 KB of accumulators + two trash slots) + candidate lists = 220 KB: one CTA per SM
 constexpr int SUB_CAND = 64;
-#ifndef SRAG_BM25_SUB_DEPTH
-#define SRAG_BM25_SUB_DEPTH 2
-#endif
-constexpr int SUB_DEPTH = SRAG_BM25_SUB_DEPTH;  // rounds (of 128 postings) in flight per warp
 #ifndef SRAG_BM25_SUB_NARROW
 #define SRAG_BM25_SUB_NARROW 32
 #endif
 constexpr uint32_t SUB_NARROW = SRAG_BM25_SUB_NARROW;  // slices up to this long: one posting per lane (0 = never)
-constexpr uint32_t SUB_NARROW_BIT = 0x10u;
+static_assert(SUB_NARROW <= 32, "a narrow round gives one posting to each lane");
+
+// One warp's accumulators with a trash slot on either side. Slices are padded to whole groups of 4 postings; a padding
+// posting carries impact +0.0 and an offset that lands on a trash slot of whichever warp processes it:
+//   sub-block 0 of a block: offset 8192 = the float right AFTER the warp's 2048 accumulators (acc_b = acc)
+//   sub-block m > 0:        offset m * 8192 - 4 = the float right BEFORE them (acc_b = acc - m * 8192 bytes)
+// so padding needs no mask anywhere in the round loop (SUB_TRASH_OFFSET below is what the index build writes).
+struct SubWarpTile {
+    float before[4];
+    float acc[BM25_SUB_DOCS];
+    float after[4];
+};
+__host__ __device__ constexpr uint32_t sub_trash_offset(int sub_in_block) {
+    return sub_in_block == 0 ? (uint32_t)BM25_SUB_DOCS * 4u : (uint32_t)sub_in_block * (BM25_SUB_DOCS * 4u) - 4u;
+}
+static_assert(sub_trash_offset(BM25_SUBS - 1) < 65536u, "trash offsets must fit 16 bits");
 
 struct SubSmem {
-    float acc[SUB_WARPS][BM25_SUB_DOCS];
+    SubWarpTile tile[SUB_WARPS];
     uint16_t cand[SUB_WARPS][SUB_CAND];
     uint32_t cand_count[SUB_WARPS];
 };
 
-__device__ __forceinline__ int32_t ldg_stream_s32(const int32_t* p) {
-    int32_t v;
-    asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(v) : "l"(p));
+__device__ __forceinline__ uint32_t ldg_stream_u16(const uint16_t* p) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
 __device__ __forceinline__ float ldg_stream_f32(const float* p) {
@@ -759,10 +778,9 @@ __device__ __forceinline__ float ldg_stream_f32(const float* p) {
     asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
     return v;
 }
-__device__ __forceinline__ int4 ldg_stream_s32x4(const int32_t* p) {
-    int4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+__device__ __forceinline__ uint2 ldg_stream_u16x4(const uint16_t* p) {
+    uint2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
     return v;
 }
 __device__ __forceinline__ float4 ldg_stream_f32x4(const float* p) {
@@ -772,12 +790,46 @@ __device__ __forceinline__ float4 ldg_stream_f32x4(const float* p) {
     return v;
 }
 
-template <bool FILT>
+// One stage of the round pipeline: the postings a lane holds for one round, loaded SUB_DEPTH - 1 rounds ahead of their
+// use (the loads hit L2: the slices were prefetched an item earlier; two rounds in flight cover that latency, one does
+// not: 12.5 ms against 11.8 ms at C3).
+//   meta: bits 0..7 = postings of the round (1..128), bit 16 NARROW (lane l < count holds posting l: o.x, w.x),
+//         bit 17 = first round of a term; a wide round gives postings 4 l .. 4 l + 3 to lane l (count is a multiple of 4)
+struct SubStage {
+    uint2 o;          // four 16-bit byte offsets (block-relative)
+    float4 w;         // four impacts
+    uint32_t meta;
+};
+constexpr uint32_t STAGE_NARROW = 1u << 16, STAGE_NEW_TERM = 1u << 17;
+#ifndef SRAG_BM25_SUB_DEPTH
+#define SRAG_BM25_SUB_DEPTH 3
+#endif
+constexpr int SUB_DEPTH = SRAG_BM25_SUB_DEPTH;  // stages: SUB_DEPTH - 1 rounds in flight while one is applied
+
+// A document crossed tau: remember its tile offset (rare: ~32 k crossings per query over all its sub-blocks). Out of
+// line, so that the round loop stays small.
+__device__ __noinline__ void sub_record(uint32_t* cand_count, uint16_t* cand, uint32_t off_bytes) {
+    const uint32_t c = atomicAdd(cand_count, 1u);
+    if (c < (uint32_t)SUB_CAND) cand[c] = (uint16_t)off_bytes;
+}
+__device__ __noinline__ void sub_record_filtered(uint32_t* cand_count, uint16_t* cand, uint32_t off_bytes, int32_t blk_doc0,
+                                                 const uint32_t* doc_tags, const int32_t* doc_group, uint32_t f_mask,
+                                                 int32_t f_group) {
+    const int32_t doc = blk_doc0 + (int32_t)(off_bytes >> 2);
+    if (doc_tags && (__ldg(doc_tags + doc) & f_mask) == 0) return;
+    if (f_group >= 0 && __ldg(doc_group + doc) != f_group) return;
+    const uint32_t c = atomicAdd(cand_count, 1u);
+    if (c < (uint32_t)SUB_CAND) cand[c] = (uint16_t)off_bytes;
+}
+
+// SAMPLE = the pass that yields tau (nothing tracked while terms are applied, a scan at the end reports true scores);
+// otherwise the MAIN pass (documents crossing tau are recorded by the add that takes them across).
+template <bool FILT, bool SAMPLE>
 __global__ void __launch_bounds__(32 * SUB_WARPS, 1)
-bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, const int32_t* __restrict__ post_doc,
-                const float* __restrict__ post_imp, int n_blocks, int n_sub, const int32_t* __restrict__ q_terms,
-                int max_terms, int k, int q_offset, int nq, int stride,
-                const float* __restrict__ tau /* [nq][k]; nullptr = SAMPLE pass */,
+bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in groups of 4 postings */,
+                const uint16_t* __restrict__ post_off, const float* __restrict__ post_imp, int n_blocks, int n_sub,
+                const int32_t* __restrict__ q_terms, int max_terms, int k, int q_offset, int nq, int stride,
+                const float* __restrict__ tau /* [nq][k], main pass */,
                 uint64_t* __restrict__ partial /* [nq][n_blocks * k]; sample pass: [nq][nb0 * BM25_SUBS * 32] */,
                 uint32_t* __restrict__ q_count /* [nq], zeroed */, uint32_t* __restrict__ q_flag /* [nq], zeroed */,
                 uint32_t* __restrict__ n_flagged, Bm25Filter flt,
@@ -786,21 +838,23 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
     SubSmem* sm = reinterpret_cast<SubSmem*>(bm25_smem_raw);
     constexpr uint32_t FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    float* acc = sm->acc[w];
+    float* acc = sm->tile[w].acc;
     uint16_t* cand = sm->cand[w];
     uint32_t* cand_count = &sm->cand_count[w];
-    // Two passes share this kernel. SAMPLE pass (tau == nullptr): the sub-blocks of every stride-th block; nothing is
-    // tracked while the terms are applied, and at the end of an item every lane reports the best of the 64 accumulators
-    // it scans (32 true scores per sampled sub-block; the k-th best of a query's reports is tau, a lower bound of its
-    // global k-th score). MAIN pass: ALL sub-blocks, the sampled ones again, with the crossing rule.
-    const bool sample_pass = tau == nullptr;
     const int nb0 = (n_blocks + stride - 1) / stride;
-    const int per_q = (sample_pass ? nb0 : n_blocks) * BM25_SUBS;   // sub-blocks of one query in this pass
-    const long long n_items = (long long)nq * per_q;
+    const int per_q = (SAMPLE ? nb0 : n_blocks) * BM25_SUBS;   // sub-blocks of one query in this pass
     const long long step = (long long)gridDim.x * SUB_WARPS;
     const uint32_t cap = (uint32_t)n_blocks * (uint32_t)k;     // key slots of one query in `partial`
+    // the next item's slices are pulled into L2 by lpt lanes per term (1, 2, 4 ... 32): the longest slice sets the trip count
+    int lpt_log = 0;
+    while (lpt_log < 5 && (max_terms << (lpt_log + 1)) <= 32) ++lpt_log;
+    const int pf_term = lane >> lpt_log, pf_j = lane & ((1 << lpt_log) - 1);
+    if (lane == 0) {  // the trash slots only ever receive +0.0
+        sm->tile[w].before[3] = 0.f;
+        sm->tile[w].after[0] = 0.f;
+    }
 
-    // Items of this warp: first, first + step, ... as (query, j-th phase-1 sub-block); stepping is an add with carry.
+    // Items of this warp: first, first + step, ... as (query, j-th sub-block of the pass); stepping is an add with carry.
     struct Item { int q, j; };
     const int step_q = (int)(step / per_q), step_j = (int)(step % per_q);
     auto advance = [&](Item x) {
@@ -811,20 +865,20 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
     };
     auto sub_of = [&](Item x) -> int {  // sub-block index, -1 past the end of the queries or of the documents
         if (x.q >= nq) return -1;
-        const int sub = sample_pass ? (x.j / BM25_SUBS) * stride * BM25_SUBS + x.j % BM25_SUBS : x.j;
+        const int sub = SAMPLE ? (x.j / BM25_SUBS) * stride * BM25_SUBS + x.j % BM25_SUBS : x.j;
         return sub < n_sub ? sub : -1;
     };
     auto term_of = [&](Item x, int sub, int j0) -> int32_t {
         if (sub < 0 || j0 + lane >= max_terms) return -1;
         return __ldg(q_terms + (size_t)(q_offset + x.q) * max_terms + j0 + lane);
     };
-    auto bounds_of = [&](int sub, int32_t t, int64_t& lo, uint32_t& n) {  // first posting and length of the slice
-        lo = 0;
+    auto bounds_of = [&](int sub, int32_t t, uint32_t& g0, uint32_t& n) {  // first group of 4 and (padded) length of the slice
+        g0 = 0;
         n = 0;
         if (sub >= 0 && t >= 0) {
-            const int64_t* bp = block_ptr + (size_t)t * (n_sub + 1) + sub;
-            lo = __ldg(bp);
-            n = (uint32_t)(__ldg(bp + 1) - lo);
+            const uint32_t* sp = slice_ptr + (size_t)t * (n_sub + 1) + sub;
+            g0 = __ldg(sp);
+            n = (__ldg(sp + 1) - g0) << 2;
         }
     };
     auto flag_query = [&](int q) {
@@ -838,48 +892,61 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
     Item x1 = advance(x0), x2 = advance(x1), x3 = advance(x2);
     int s0 = sub_of(x0), s1 = sub_of(x1), s2 = sub_of(x2), s3 = sub_of(x3);
     int32_t t3 = term_of(x3, s3, 0);
-    int64_t lo, lo1, lo2;
-    uint32_t n0, n1, n2;
-    bounds_of(s0, term_of(x0, s0, 0), lo, n0);
-    bounds_of(s1, term_of(x1, s1, 0), lo1, n1);
-    bounds_of(s2, term_of(x2, s2, 0), lo2, n2);
-    float tau0 = s0 >= 0 && !sample_pass ? __ldg(tau + (size_t)x0.q * k + (k - 1)) : 0.f;
-    float tau1 = s1 >= 0 && !sample_pass ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
+    uint32_t g0, g1, g2;   // slice starts, in groups of 4 postings
+    uint32_t n0, n1, n2;   // slice lengths in postings (multiples of 4)
+    bounds_of(s0, term_of(x0, s0, 0), g0, n0);
+    bounds_of(s1, term_of(x1, s1, 0), g1, n1);
+    bounds_of(s2, term_of(x2, s2, 0), g2, n2);
+    float tau0 = s0 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x0.q * k + (k - 1)) : 0.f;
+    float tau1 = s1 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
 
     for (; x0.q < nq;) {
         if (s0 >= 0) {
             const int q = x0.q;
-            const int32_t doc_base = s0 * BM25_SUB_DOCS;
+            // post_off holds byte offsets inside the 16384-document block's tile; this warp's 2048 accumulators are the
+            // piece of that tile that starts at byte sub_byte0, so acc_b + offset is the accumulator's address
+            const uint32_t sub_byte0 = (uint32_t)(s0 & (BM25_SUBS - 1)) * (BM25_SUB_DOCS * 4u);
+            char* acc_b = reinterpret_cast<char*>(acc) - sub_byte0;
+            const int32_t blk_doc0 = (s0 / BM25_SUBS) * BM25_BLOCK_DOCS;   // document of byte offset 0
             // tau = 0 (the sample matched fewer than k documents): every matched document is a candidate
-            const uint32_t cross_bits = sample_pass ? 0xFFFFFFFFu : tau0 > 0.f ? __float_as_uint(tau0) : 1u;
+            const uint32_t cross_bits = SAMPLE ? 0xFFFFFFFFu : tau0 > 0.f ? __float_as_uint(tau0) : 1u;
             uint32_t f_mask = 0xFFFFFFFFu;
             int32_t f_group = -1;
             if constexpr (FILT) {
                 f_mask = flt.doc_tags ? __ldg(flt.q_tag_mask + q_offset + q) : 0xFFFFFFFFu;
                 f_group = flt.doc_group ? __ldg(flt.q_group + q_offset + q) : -1;
             }
-            if (n1 > 0) {
-                // Pull the NEXT item's slices into L2 now (lane u: term u, one 128-byte line per request): its loads then
-                // see L2 latency instead of HBM latency, and nothing has to be held in registers meanwhile.
-                const char* pd = reinterpret_cast<const char*>(post_doc + lo1);
-                const char* pi = reinterpret_cast<const char*>(post_imp + lo1);
-                const int bytes = (int)n1 * 4 + (int)(reinterpret_cast<uintptr_t>(pd) & 127);
-                pd -= reinterpret_cast<uintptr_t>(pd) & 127;
-                pi -= reinterpret_cast<uintptr_t>(pi) & 127;
-                for (int o = 0; o < bytes; o += 128) {
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pd + o));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pi + o));
+            {
+                // Pull the NEXT item's slices into L2 now (one 128-byte line per request): its loads then see L2 latency
+                // instead of HBM latency, and nothing has to be held in registers meanwhile. Lane group pf_term looks
+                // after term pf_term, its lanes take every (1 << lpt_log)-th line.
+                const uint32_t g_p = __shfl_sync(FULL, g1, pf_term);
+                const uint32_t n_p = __shfl_sync(FULL, n1, pf_term);
+                if (n_p > 0) {
+                    const char* po = reinterpret_cast<const char*>(post_off) + (size_t)g_p * 8u;
+                    const char* pi = reinterpret_cast<const char*>(post_imp) + (size_t)g_p * 16u;
+                    const int bytes_o = (int)n_p * 2 + (int)(reinterpret_cast<uintptr_t>(po) & 127);
+                    const int bytes_i = (int)n_p * 4 + (int)(reinterpret_cast<uintptr_t>(pi) & 127);
+                    po -= reinterpret_cast<uintptr_t>(po) & 127;
+                    pi -= reinterpret_cast<uintptr_t>(pi) & 127;
+                    const int stride_b = 128 << lpt_log;
+                    for (int o = pf_j * 128; o < bytes_i; o += stride_b) {
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pi + o));
+                        if (o < bytes_o) asm volatile("prefetch.global.L2 [%0];" ::"l"(po + o));
+                    }
                 }
             }
             bool zeroed = false;
+            auto record = [&](uint32_t off_bytes) {
+                if constexpr (FILT) sub_record_filtered(cand_count, cand, off_bytes, blk_doc0, flt.doc_tags, flt.doc_group, f_mask, f_group);
+                else sub_record(cand_count, cand, off_bytes);
+            };
             for (int j0 = 0; j0 < max_terms; j0 += 32) {
-                if (j0 > 0) bounds_of(s0, term_of(x0, s0, j0), lo, n0);  // queries with more than 32 terms: fetched in line
-                // Lane u plans term j0 + u: its slice rounded out to aligned groups of 4 postings (the arrays are padded)
-                // and cut into rounds of 128 postings = one 16-byte load per lane and array.
+                if (j0 > 0) bounds_of(s0, term_of(x0, s0, j0), g0, n0);  // queries with more than 32 terms: fetched in line
+                // lane u = term j0 + u: its rounds — one NARROW round for a slice of up to SUB_NARROW postings, else wide
+                // rounds of 128 — and the running total over the terms (ascending term id = lane order)
                 const uint32_t n_l = n0;
-                // a slice of up to SUB_NARROW postings is one NARROW round (one posting per lane), a longer one is cut into
-                // wide rounds of 128 (an aligned group of 4 per lane)
-                const uint32_t cnt = n_l == 0 ? 0u : n_l <= SUB_NARROW ? 1u : (((uint32_t)lo & 3u) + n_l + 127u) >> 7;
+                const uint32_t cnt = n_l == 0 ? 0u : n_l <= SUB_NARROW ? 1u : (n_l + 127u) >> 7;
                 uint32_t incl = cnt;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -894,146 +961,144 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                     for (int i = 0; i < BM25_SUB_DOCS / 128; ++i) a4[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (lane == 0) *cand_count = 0;
                     zeroed = true;
-                    __syncwarp();
                 }
-                // round r of the stream belongs to term u = the first lane whose inclusive round count exceeds r
-                const uint32_t excl = incl - cnt;
-                int4 d[SUB_DEPTH];
-                float4 wv[SUB_DEPTH];
-                uint32_t vm[SUB_DEPTH];  // which of the lane's 4 postings belong to the slice
-                auto load_round = [&](uint32_t r, int4& dd, float4& ww, uint32_t& mask) {
-                    const int u = __popc(__ballot_sync(FULL, incl <= r));
-                    const int64_t lo_u = __shfl_sync(FULL, lo, u);
-                    const uint32_t n_u = __shfl_sync(FULL, n_l, u);
-                    dd = make_int4(0, 0, 0, 0);
-                    ww = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (n_u <= SUB_NARROW) {  // warp-uniform
-                        mask = SUB_NARROW_BIT | ((uint32_t)lane < n_u ? 1u : 0u);
-                        if ((uint32_t)lane < n_u) {
-                            dd.x = ldg_stream_s32(post_doc + lo_u + lane);
-                            ww.x = ldg_stream_f32(post_imp + lo_u + lane);
+                __syncwarp();  // zeroing (and the previous group of terms) done before the first add
+                // The round stream is described 32 rounds at a time, one descriptor per lane: lane i of a chunk finds the
+                // term of round base + i by bisection in the running totals (once per CHUNK, not per round) and works out
+                // where the round's postings start and how many there are; the round loop then only broadcasts two words.
+                for (uint32_t base = 0; base < rounds; base += 32) {
+                    const uint32_t g = base + (uint32_t)lane;
+                    int u = 0;
+#pragma unroll
+                    for (int stepb = 16; stepb > 0; stepb >>= 1) {
+                        const uint32_t v = __shfl_sync(FULL, incl, u + stepb - 1);
+                        if (v <= g) u += stepb;
+                    }
+                    u = u > 31 ? 31 : u;                                   // lanes past the last round (g >= rounds)
+                    const uint32_t incl_u = __shfl_sync(FULL, incl, u), cnt_u = __shfl_sync(FULL, cnt, u);
+                    const uint32_t g0_u = __shfl_sync(FULL, g0, u), n_u = __shfl_sync(FULL, n_l, u);
+                    const uint32_t r_in = g - (incl_u - cnt_u);            // round inside its term
+                    const uint32_t d_grp = g0_u + (r_in << 5);             // first group of 4 postings of the round
+                    const uint32_t left = n_u - (r_in << 7);
+                    uint32_t d_meta = (n_u <= SUB_NARROW ? (n_u | STAGE_NARROW) : (left < 128u ? left : 128u)) |
+                                      (r_in == 0 ? STAGE_NEW_TERM : 0u);
+                    const int n_chunk = (int)(rounds - base < 32u ? rounds - base : 32u);
+
+                    auto fetch = [&](SubStage& st, int r) {   // r: round inside the chunk (warp-uniform)
+                        const uint32_t grp = __shfl_sync(FULL, d_grp, r);
+                        const uint32_t meta = __shfl_sync(FULL, d_meta, r);
+                        st.meta = meta;
+                        const uint32_t count = meta & 0xFFu;
+                        if (meta & STAGE_NARROW) {
+                            if ((uint32_t)lane < count) {
+                                const size_t p = (size_t)grp * 4u + (uint32_t)lane;
+                                st.o.x = ldg_stream_u16(post_off + p);
+                                st.w.x = ldg_stream_f32(post_imp + p);
+                            }
+                        } else if (4u * (uint32_t)lane < count) {
+                            const size_t p = ((size_t)grp + (uint32_t)lane) * 4u;
+                            st.o = ldg_stream_u16x4(post_off + p);
+                            st.w = ldg_stream_f32x4(post_imp + p);
                         }
-                        return;
-                    }
-                    const uint32_t off_u = (uint32_t)lo_u & 3u;  // the slice starts at this element of its first group
-                    const int32_t pos = (int32_t)(((r - __shfl_sync(FULL, excl, u)) << 7) + 4u * (uint32_t)lane);
-                    // elements pos .. pos+3 of the rounded-out slice; the slice proper is [off_u, off_u + n_u)
-                    const int32_t skip = (int32_t)off_u - pos;                // > 0 only in the first group
-                    const int32_t keep = (int32_t)(off_u + n_u) - pos;        // elements up to the slice's end
-                    mask = keep <= 0 ? 0u : (0xFu >> (keep >= 4 ? 0 : 4 - keep));
-                    if (skip > 0) mask &= 0xFu << skip;
-                    if (mask) {
-                        const int64_t p = (lo_u & ~(int64_t)3) + pos;
-                        dd = ldg_stream_s32x4(post_doc + p);
-                        ww = ldg_stream_f32x4(post_imp + p);
-                    }
-                };
-#pragma unroll
-                for (int s_ = 0; s_ < SUB_DEPTH; ++s_) {
-                    vm[s_] = 0;
-                    d[s_] = make_int4(0, 0, 0, 0);
-                    wv[s_] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if ((uint32_t)s_ < rounds) load_round((uint32_t)s_, d[s_], wv[s_], vm[s_]);
-                }
-                for (uint32_t r0 = 0; r0 < rounds; r0 += SUB_DEPTH) {
-#pragma unroll
-                    for (int s_ = 0; s_ < SUB_DEPTH; ++s_) {
-                        if (r0 + s_ < rounds) {  // warp-uniform
-                            const uint32_t mask = vm[s_];
-                            const int4 dd = d[s_];
-                            const float4 ww = wv[s_];
-                            // refill the stage first: the loads must be in flight while this round is applied
-                            if (r0 + s_ + SUB_DEPTH < rounds) load_round(r0 + s_ + SUB_DEPTH, d[s_], wv[s_], vm[s_]);
-                            if (mask & SUB_NARROW_BIT) {  // warp-uniform: one posting per lane
-                                if (mask & 1u) {
-                                    const int rel = dd.x - doc_base;
-                                    const float a0 = acc[rel];
-                                    const float n0 = __fadd_rn(a0, ww.x);
-                                    acc[rel] = n0;
-                                    if (__float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits) {
-                                        bool ok = true;
-                                        if constexpr (FILT) {
-                                            if (flt.doc_tags && (__ldg(flt.doc_tags + dd.x) & f_mask) == 0) ok = false;
-                                            if (f_group >= 0 && __ldg(flt.doc_group + dd.x) != f_group) ok = false;
-                                        }
-                                        if (ok) {
-                                            const uint32_t c = atomicAdd(cand_count, 1u);
-                                            if (c < (uint32_t)SUB_CAND) cand[c] = (uint16_t)rel;
-                                        }
-                                    }
-                                }
-                            } else if (mask) {
-                                const bool m0 = mask & 1u, m1 = mask & 2u, m2 = mask & 4u, m3 = mask & 8u;
-                                const int r0_ = m0 ? dd.x - doc_base : 0, r1_ = m1 ? dd.y - doc_base : 0;
-                                const int r2_ = m2 ? dd.z - doc_base : 0, r3_ = m3 ? dd.w - doc_base : 0;
-                                // the four reads are issued together, then the adds, then the writes
-                                const float a0 = acc[r0_], a1 = acc[r1_], a2 = acc[r2_], a3 = acc[r3_];
-                                const float n0 = __fadd_rn(a0, ww.x), n1 = __fadd_rn(a1, ww.y);
-                                const float n2 = __fadd_rn(a2, ww.z), n3 = __fadd_rn(a3, ww.w);
-                                if (m0) acc[r0_] = n0;
-                                if (m1) acc[r1_] = n1;
-                                if (m2) acc[r2_] = n2;
-                                if (m3) acc[r3_] = n3;
-                                // Impacts are > 0: an accumulator only grows and crosses tau at most once. Cheap test first
-                                // (some new value reaches tau; elements outside the slice may raise a false alarm).
-                                if (__float_as_uint(fmaxf(fmaxf(n0, n1), fmaxf(n2, n3))) >= cross_bits) {
-                                    const int rr[4] = {r0_, r1_, r2_, r3_};
-                                    const bool cc[4] = {
-                                        m0 && __float_as_uint(n0) >= cross_bits && __float_as_uint(a0) < cross_bits,
-                                        m1 && __float_as_uint(n1) >= cross_bits && __float_as_uint(a1) < cross_bits,
-                                        m2 && __float_as_uint(n2) >= cross_bits && __float_as_uint(a2) < cross_bits,
-                                        m3 && __float_as_uint(n3) >= cross_bits && __float_as_uint(a3) < cross_bits};
-#pragma unroll
-                                    for (int e = 0; e < 4; ++e) {
-                                        if (!cc[e]) continue;
-                                        bool ok = true;
-                                        if constexpr (FILT) {
-                                            const int32_t doc = doc_base + rr[e];
-                                            if (flt.doc_tags && (__ldg(flt.doc_tags + doc) & f_mask) == 0) ok = false;
-                                            if (f_group >= 0 && __ldg(flt.doc_group + doc) != f_group) ok = false;
-                                        }
-                                        if (ok) {
-                                            const uint32_t c = atomicAdd(cand_count, 1u);
-                                            if (c < (uint32_t)SUB_CAND) cand[c] = (uint16_t)rr[e];
-                                        }
-                                    }
+                    };
+                    auto apply = [&](const SubStage& st) {
+                        const uint32_t meta = st.meta;
+                        if (meta & STAGE_NEW_TERM) __syncwarp();  // the previous term's writes are visible to every lane
+                        const uint32_t count = meta & 0xFFu;
+                        if (meta & STAGE_NARROW) {      // ---- narrow: one posting per lane
+                            if ((uint32_t)lane < count) {
+                                float* p = reinterpret_cast<float*>(acc_b + st.o.x);
+                                const float a0 = *p;
+                                const float v0 = __fadd_rn(a0, st.w.x);
+                                *p = v0;
+                                if constexpr (!SAMPLE) {
+                                    if (__float_as_uint(v0) >= cross_bits && __float_as_uint(a0) < cross_bits) record(st.o.x);
                                 }
                             }
-                            __syncwarp();  // the next round may belong to the next term and hit the same documents
+                            return;
+                        }
+                        if (4u * (uint32_t)lane < count) {   // ---- wide round: four postings per lane, no masks (padding
+                                                             // postings add +0.0 to a trash slot)
+                            const uint32_t o0 = st.o.x & 0xFFFFu, o1 = st.o.x >> 16, o2 = st.o.y & 0xFFFFu, o3 = st.o.y >> 16;
+                            float* p0 = reinterpret_cast<float*>(acc_b + o0);
+                            float* p1 = reinterpret_cast<float*>(acc_b + o1);
+                            float* p2 = reinterpret_cast<float*>(acc_b + o2);
+                            float* p3 = reinterpret_cast<float*>(acc_b + o3);
+                            // the four reads are issued together, then the adds, then the writes
+                            const float a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
+                            const float v0 = __fadd_rn(a0, st.w.x), v1 = __fadd_rn(a1, st.w.y);
+                            const float v2 = __fadd_rn(a2, st.w.z), v3 = __fadd_rn(a3, st.w.w);
+                            *p0 = v0;
+                            *p1 = v1;
+                            *p2 = v2;
+                            *p3 = v3;
+                            if constexpr (!SAMPLE) {
+                                // Impacts are > 0: an accumulator only grows and crosses tau at most once. Cheap test first.
+                                if (__float_as_uint(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3))) >= cross_bits) {
+                                    if (__float_as_uint(v0) >= cross_bits && __float_as_uint(a0) < cross_bits) record(o0);
+                                    if (__float_as_uint(v1) >= cross_bits && __float_as_uint(a1) < cross_bits) record(o1);
+                                    if (__float_as_uint(v2) >= cross_bits && __float_as_uint(a2) < cross_bits) record(o2);
+                                    if (__float_as_uint(v3) >= cross_bits && __float_as_uint(a3) < cross_bits) record(o3);
+                                }
+                            }
+                        }
+                    };
+                    // SUB_DEPTH stages in rotation, each loaded SUB_DEPTH - 1 rounds before it is applied; the rotation is
+                    // unrolled so that the stages stay in registers and are never copied
+                    SubStage st[SUB_DEPTH];
+#pragma unroll
+                    for (int i = 0; i < SUB_DEPTH; ++i) {
+                        st[i].o = make_uint2(0u, 0u);
+                        st[i].w = make_float4(0.f, 0.f, 0.f, 0.f);
+                        st[i].meta = 0u;
+                    }
+#pragma unroll
+                    for (int i = 0; i < SUB_DEPTH - 1; ++i)
+                        if (i < n_chunk) fetch(st[i], i);
+                    for (int r = 0; r < n_chunk; r += SUB_DEPTH) {
+#pragma unroll
+                        for (int i = 0; i < SUB_DEPTH; ++i) {
+                            if (r + i < n_chunk) {
+                                if (r + i + SUB_DEPTH - 1 < n_chunk) fetch(st[(i + SUB_DEPTH - 1) % SUB_DEPTH], r + i + SUB_DEPTH - 1);
+                                apply(st[i]);
+                            }
                         }
                     }
                 }
             }
-            if (zeroed && sample_pass) {
-                // lane l scans accumulators l, l + 32, ... (conflict-free) and reports its best (ties: lowest document)
-                __syncwarp();
-                uint32_t best = 0, best_rel = 0;
+            if constexpr (SAMPLE) {
+                if (zeroed) {
+                    // lane l scans accumulators l, l + 32, ... (conflict-free) and reports its best (ties: lowest document)
+                    __syncwarp();
+                    const int32_t doc_base = s0 * BM25_SUB_DOCS;
+                    uint32_t best = 0, best_rel = 0;
 #pragma unroll 8
-                for (int i = 0; i < BM25_SUB_DOCS / 32; ++i) {
-                    const uint32_t rel = (uint32_t)(lane + 32 * i);
-                    bool ok = true;
-                    const uint32_t v = __float_as_uint(acc[rel]);
-                    if constexpr (FILT) {
-                        if (v > best) {
-                            const int32_t doc = doc_base + (int32_t)rel;
-                            if (flt.doc_tags && (__ldg(flt.doc_tags + doc) & f_mask) == 0) ok = false;
-                            if (f_group >= 0 && __ldg(flt.doc_group + doc) != f_group) ok = false;
+                    for (int i = 0; i < BM25_SUB_DOCS / 32; ++i) {
+                        const uint32_t rel = (uint32_t)(lane + 32 * i);
+                        bool ok = true;
+                        const uint32_t v = __float_as_uint(acc[rel]);
+                        if constexpr (FILT) {
+                            if (v > best) {
+                                const int32_t doc = doc_base + (int32_t)rel;
+                                if (flt.doc_tags && (__ldg(flt.doc_tags + doc) & f_mask) == 0) ok = false;
+                                if (f_group >= 0 && __ldg(flt.doc_group + doc) != f_group) ok = false;
+                            }
                         }
+                        if (v > best && ok) { best = v; best_rel = rel; }
                     }
-                    if (v > best && ok) { best = v; best_rel = rel; }
+                    const int ssub = (s0 / (stride * BM25_SUBS)) * BM25_SUBS + s0 % BM25_SUBS;  // index among the sampled ones
+                    uint64_t key = best ? srag_pack_key(best, (uint32_t)doc_base + best_rel) : SRAG_KEY_EMPTY;
+                    if (sample_group == 4) {  // the best of four lanes: fewer keys for the tau merge to sort
+                        uint64_t o = __shfl_xor_sync(FULL, key, 1);
+                        key = o > key ? o : key;
+                        o = __shfl_xor_sync(FULL, key, 2);
+                        key = o > key ? o : key;
+                    }
+                    const int per_sub = 32 / sample_group;
+                    if ((lane & (sample_group - 1)) == 0)
+                        partial[((size_t)q * per_q + ssub) * per_sub + lane / sample_group] = key;
+                    __syncwarp();
                 }
-                const int ssub = (s0 / (stride * BM25_SUBS)) * BM25_SUBS + s0 % BM25_SUBS;  // index among the sampled ones
-                uint64_t key = best ? srag_pack_key(best, (uint32_t)doc_base + best_rel) : SRAG_KEY_EMPTY;
-                if (sample_group == 4) {  // the best of four lanes: fewer keys for the tau merge to sort
-                    uint64_t o = __shfl_xor_sync(FULL, key, 1);
-                    key = o > key ? o : key;
-                    o = __shfl_xor_sync(FULL, key, 2);
-                    key = o > key ? o : key;
-                }
-                const int per_sub = 32 / sample_group;
-                if ((lane & (sample_group - 1)) == 0)
-                    partial[((size_t)q * per_q + ssub) * per_sub + lane / sample_group] = key;
-                __syncwarp();
             } else if (zeroed) {
                 __syncwarp();
                 const uint32_t nc = *cand_count;
@@ -1048,8 +1113,9 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
                     } else {
                         uint64_t* out = partial + (size_t)q * cap + base;  // the region fills from the front
                         for (uint32_t i = lane; i < nc; i += 32) {
-                            const uint32_t rel = cand[i];
-                            out[i] = srag_pack_key(__float_as_uint(acc[rel]), (uint32_t)doc_base + rel);
+                            const uint32_t ob = cand[i];
+                            out[i] = srag_pack_key(__float_as_uint(*reinterpret_cast<const float*>(acc_b + ob)),
+                                                   (uint32_t)blk_doc0 + (ob >> 2));
                         }
                     }
                 }
@@ -1065,13 +1131,13 @@ bm25_sub_kernel(const int64_t* __restrict__ block_ptr /* [vocab][n_sub + 1] */, 
         s1 = s2;
         s2 = s3;
         s3 = sub_of(x3);
-        lo = lo1;
+        g0 = g1;
         n0 = n1;
-        lo1 = lo2;
+        g1 = g2;
         n1 = n2;
         tau0 = tau1;
-        bounds_of(s2, t3, lo2, n2);
-        tau1 = s1 >= 0 && !sample_pass ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
+        bounds_of(s2, t3, g2, n2);
+        tau1 = s1 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
         t3 = term_of(x3, s3, 0);
     }
 }
@@ -1126,22 +1192,96 @@ __global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, co
     }
 }
 
-// Bank order (index build). Inside a (term, sub-block) slice every posting is a distinct document and receives exactly
-// one add per query, so the ORDER of a slice's postings is free: sums, and therefore scores, do not depend on it.
-// Both scoring kernels read-add-write acc[doc - doc_base] with lane l holding postings 4l .. 4l+3 of an aligned group of
-// 128 (aligned relative to lo & ~3), i.e. one shared-memory access covers the 32 postings at positions 128g + 4l + e
-// (fixed g, e). With postings in ascending document order their banks (doc & 31) are as good as random: ~3.4
-// wavefronts per access. This kernel permutes each slice so that those 32 postings fall on distinct banks wherever the
-// slice allows it: the postings are laid out "round-robin over banks" (all first-of-their-bank postings in bank order,
-// then all second ones, ...; a window of 32 consecutive entries of full rounds hits every bank once) and that sequence
-// is written to the slice's positions in ACCESS order (g, e, l). The floor is max_b count(b) wavefronts per slice;
-// simulation: 3.2 -> 2.1 wavefronts per access for slices of 100 postings, 3.4 -> 1.6 for 800.
-// One warp per slice, deterministic (stable inside a bank).
+// ---------------------------------------------------------------------------------------------------------
+// Packing (index build): canonical CSR postings (int32 documents ascending inside a term, fp32 impacts, block_ptr int64
+// [vocab][n_sub + 1]) -> the SEARCHED layout:
+//   * every (term, sub-block) slice starts on a group of 4 postings and is padded to whole groups with zero-impact
+//     postings that land on a trash slot (sub_trash_offset), so the scoring kernel loads 8 / 16 aligned bytes per lane
+//     and needs no mask anywhere; slice_ptr uint32 [vocab][n_sub + 1] holds the slice starts in GROUPS (so 2^32 groups =
+//     1.7e10 postings per shard);
+//   * post_off uint16 = byte offset of the document's accumulator inside its 16384-document block's tile;
+//   * BANK ORDER: inside a slice every posting is a distinct document and receives exactly one add per query, so the
+//     ORDER of a slice's postings is free: sums, and therefore scores, do not depend on it. The scoring kernels
+//     read-add-write acc[doc] with lane l holding postings 4l .. 4l+3 of a group of 128, i.e. one shared-memory access
+//     covers the 32 postings at positions 128g + 4l + e (fixed g, e). With postings in ascending document order their
+//     banks (doc & 31) are as good as random: ~3.4 wavefronts per access. The fill kernel lays each slice out "round-robin
+//     over banks" (all first-of-their-bank postings in bank order, then all second ones, ...; a window of 32 consecutive
+//     entries of full rounds hits every bank once) and writes that sequence to the slice's positions in ACCESS order
+//     (g, e, l). The floor is max_b count(b) wavefronts per slice; simulation: 3.2 -> 2.1 wavefronts per access for slices
+//     of 100 postings, 3.4 -> 1.6 for 800. One warp per slice, deterministic (stable inside a bank).
+// ---------------------------------------------------------------------------------------------------------
 constexpr int BANK_ORDER_WARPS = 8;
+
+// groups[t] = sum over the term's slices of ceil(n / 4)
+__global__ void pack_row_sum_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_sub, int64_t* __restrict__ groups) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t t = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < vocab; t += warps) {
+        const int64_t* row = block_ptr + (size_t)t * (n_sub + 1);
+        int64_t s = 0;
+        for (int j = lane; j < n_sub; j += 32) s += (__ldg(row + j + 1) - __ldg(row + j) + 3) >> 2;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+        if (lane == 0) groups[t] = s;
+    }
+}
+
+// term_group[t] = exclusive scan of groups (one CTA; every thread owns a contiguous segment); [vocab] = total
+__global__ void __launch_bounds__(1024) pack_scan_terms_kernel(const int64_t* __restrict__ groups, int vocab,
+                                                               int64_t* __restrict__ term_group) {
+    __shared__ int64_t part[1024];
+    const int per = (vocab + 1023) / 1024;
+    const int lo = threadIdx.x * per, hi = min(vocab, lo + per);
+    int64_t s = 0;
+    for (int i = lo; i < hi; ++i) s += groups[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t run = 0;
+        for (int i = 0; i < 1024; ++i) {
+            const int64_t v = part[i];
+            part[i] = run;
+            run += v;
+        }
+        term_group[vocab] = run;
+    }
+    __syncthreads();
+    int64_t run = part[threadIdx.x];
+    for (int i = lo; i < hi; ++i) {
+        const int64_t v = groups[i];   // (groups and term_group may not alias)
+        term_group[i] = run;
+        run += v;
+    }
+}
+
+// slice_ptr[t][j] = term_group[t] + sum_{j' < j} ceil(n_{t j'} / 4); [t][n_sub] = term_group[t + 1]
+__global__ void pack_row_scan_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_sub,
+                                     const int64_t* __restrict__ term_group, uint32_t* __restrict__ slice_ptr) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t t = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < vocab; t += warps) {
+        const int64_t* row = block_ptr + (size_t)t * (n_sub + 1);
+        uint32_t* out = slice_ptr + (size_t)t * (n_sub + 1);
+        int64_t carry = term_group[t];
+        for (int base = 0; base <= n_sub; base += 32) {
+            const int j = base + lane;
+            const int64_t v = j < n_sub ? (__ldg(row + j + 1) - __ldg(row + j) + 3) >> 2 : 0;
+            int64_t inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int64_t u = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                if (lane >= o) inc += u;
+            }
+            if (j <= n_sub) out[j] = (uint32_t)(carry + inc - v);
+            carry += __shfl_sync(0xFFFFFFFFu, inc, 31);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(32 * BANK_ORDER_WARPS)
-bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_sub,
-                       const int32_t* __restrict__ doc_in, const float* __restrict__ imp_in,
-                       int32_t* __restrict__ doc_out, float* __restrict__ imp_out) {
+bm25_pack_fill_kernel(const int64_t* __restrict__ block_ptr, const uint32_t* __restrict__ slice_ptr, int vocab, int n_sub,
+                      const int32_t* __restrict__ doc_in, const float* __restrict__ imp_in,
+                      uint16_t* __restrict__ off_out, float* __restrict__ imp_out, int permute) {
     __shared__ uint32_t cnt_s[BANK_ORDER_WARPS][32];
     constexpr uint32_t FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -1150,21 +1290,30 @@ bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_s
     const int64_t n_warps = (int64_t)gridDim.x * BANK_ORDER_WARPS;
     for (int64_t s0 = ((int64_t)blockIdx.x * BANK_ORDER_WARPS + w) * 32; s0 < n_slices; s0 += n_warps * 32) {
         // the bounds of 32 consecutive slices, one per lane
-        int64_t lo_l = 0, hi_l = 0;
+        int64_t lo_l = 0, hi_l = 0, dst_l = 0;
+        int sub_l = 0;
         if (s0 + lane < n_slices) {
             const int64_t t = (s0 + lane) / n_sub, j = (s0 + lane) - t * n_sub;
             const int64_t* bp = block_ptr + t * (n_sub + 1) + j;
             lo_l = __ldg(bp);
             hi_l = __ldg(bp + 1);
+            dst_l = (int64_t)__ldg(slice_ptr + t * (n_sub + 1) + j) << 2;
+            sub_l = (int)(j & (BM25_SUBS - 1));
         }
         uint32_t todo = __ballot_sync(FULL, hi_l > lo_l);
         while (todo) {
             const int src = __ffs(todo) - 1;
             todo &= todo - 1;
             const int64_t lo = __shfl_sync(FULL, lo_l, src), hi = __shfl_sync(FULL, hi_l, src);
+            const int64_t a = __shfl_sync(FULL, dst_l, src);   // first position of the padded slice
+            const int sub_in_block = __shfl_sync(FULL, sub_l, src);
             const int n = (int)(hi - lo);
-            const int64_t a = lo & ~(int64_t)3;  // the scoring kernels' groups of 4 / 128 postings are aligned to this
-            const int lo_off = (int)(lo - a), hi_off = lo_off + n;
+            const int n_pad = (n + 3) & ~3;
+            // padding: zero impact, offset = the trash slot of whichever warp scores this sub-block
+            if (lane < n_pad - n) {
+                off_out[a + n + lane] = (uint16_t)sub_trash_offset(sub_in_block);
+                imp_out[a + n + lane] = 0.f;
+            }
             // pass 1: postings per bank (lane b ends up holding the count of bank b)
             cnt[lane] = 0;
             __syncwarp();
@@ -1195,26 +1344,61 @@ bm25_bank_order_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_s
                     sidx += (cb < r ? cb : r) + (((uint32_t)bb < b && cb > r) ? 1u : 0u);
                 }
                 if (valid) {
-                    // the sidx-th position of the slice in access order (group g of 128, element e, lane l)
-                    const int g = ((int)sidx + lo_off) >> 7;
-                    int kk = (int)sidx - (g ? 128 * g - lo_off : 0);
-                    const int sg = g ? 0 : lo_off;
-                    const int tg = hi_off - 128 * g < 128 ? hi_off - 128 * g : 128;
-                    int pos = -1;
+                    int pos = i;   // permute == 0: ascending documents, only packed
+                    if (permute) {
+                        // the sidx-th position of the slice in access order (group g of 128, element e, lane l)
+                        const int g = (int)sidx >> 7;
+                        int kk = (int)sidx - 128 * g;
+                        const int tg = n - 128 * g < 128 ? n - 128 * g : 128;
+                        pos = -1;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const int l0 = (sg - e + 3) >> 2, l1 = (tg - e + 3) >> 2;
-                        const int ne = l1 > l0 ? l1 - l0 : 0;
-                        if (pos < 0) {
-                            if (kk < ne) pos = 128 * g + 4 * (l0 + kk) + e;
-                            else kk -= ne;
+                        for (int e = 0; e < 4; ++e) {
+                            const int ne = (tg - e + 3) >> 2;   // lanes that hold an element e in this group
+                            if (pos < 0) {
+                                if (kk < ne) pos = 128 * g + 4 * kk + e;
+                                else kk -= ne;
+                            }
                         }
                     }
-                    doc_out[a + pos] = d;
+                    off_out[a + pos] = (uint16_t)(((uint32_t)d & (uint32_t)(BM25_BLOCK_DOCS - 1)) << 2);
                     imp_out[a + pos] = im;
                 }
             }
             __syncwarp();
+        }
+    }
+}
+
+// The inverse of the packing: document id of every stored posting (-1 for padding) from (slice, byte offset). One warp
+// per 32 slices; used by tests, `canonical_postings` and shard conversion — never on the search path.
+__global__ void __launch_bounds__(32 * BANK_ORDER_WARPS)
+bm25_unpack_docs_kernel(const uint32_t* __restrict__ slice_ptr, int vocab, int n_sub, const uint16_t* __restrict__ post_off,
+                        const float* __restrict__ post_imp, int32_t* __restrict__ doc_out, int32_t* __restrict__ term_out) {
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t n_slices = (int64_t)vocab * n_sub;
+    const int64_t n_warps = (int64_t)gridDim.x * BANK_ORDER_WARPS;
+    for (int64_t s0 = ((int64_t)blockIdx.x * BANK_ORDER_WARPS + w) * 32; s0 < n_slices; s0 += n_warps * 32) {
+        int64_t lo_l = 0, hi_l = 0;
+        int32_t base_l = 0, term_l = 0;
+        if (s0 + lane < n_slices) {
+            const int64_t t = (s0 + lane) / n_sub, j = (s0 + lane) - t * n_sub;
+            const uint32_t* sp = slice_ptr + t * (n_sub + 1) + j;
+            lo_l = (int64_t)__ldg(sp) << 2;
+            hi_l = (int64_t)__ldg(sp + 1) << 2;
+            base_l = (int32_t)(j / BM25_SUBS) * BM25_BLOCK_DOCS;
+            term_l = (int32_t)t;
+        }
+        uint32_t todo = __ballot_sync(FULL, hi_l > lo_l);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t lo = __shfl_sync(FULL, lo_l, src), hi = __shfl_sync(FULL, hi_l, src);
+            const int32_t base = __shfl_sync(FULL, base_l, src), term = __shfl_sync(FULL, term_l, src);
+            for (int64_t p = lo + lane; p < hi; p += 32) {
+                doc_out[p] = post_imp[p] != 0.f ? base + (int32_t)(post_off[p] >> 2) : -1;
+                if (term_out) term_out[p] = term;
+            }
         }
     }
 }
@@ -1257,18 +1441,55 @@ extern "C" int srag_bm25_block_index(const int64_t* term_ptr, const int32_t* pos
     return SRAG_OK;
 }
 
-extern "C" int srag_bm25_bank_order(const int64_t* block_ptr, int vocab, int64_t n_docs, const int32_t* doc_in,
-                                    const float* imp_in, int32_t* doc_out, float* imp_out, void* stream) {
+static int pack_grid(int64_t n_slices) {
+    const int64_t rounds = (n_slices + 32 * BANK_ORDER_WARPS - 1) / (32 * BANK_ORDER_WARPS);
+    return (int)(rounds < 148 * 64 ? (rounds > 0 ? rounds : 1) : 148 * 64);
+}
+
+extern "C" int srag_bm25_pack_plan(const int64_t* block_ptr, int vocab, int64_t n_docs, int64_t* scratch, uint32_t* slice_ptr,
+                                   void* stream) {
+    SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF, "bad sizes vocab=%d n_docs=%lld", vocab,
+                   (long long)n_docs);
+    SRAG_CHECK_ARG(block_ptr && scratch && slice_ptr, "null pointer argument");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int nb = bm25_subs(n_docs) > 0 ? bm25_subs(n_docs) : 1;
+    int64_t* groups = scratch;                 // [vocab]
+    int64_t* term_group = scratch + vocab;     // [vocab + 1]; term_group[vocab] = total groups
+    int64_t blocks = ((int64_t)vocab + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    pack_row_sum_kernel<<<(int)blocks, 256, 0, st>>>(block_ptr, vocab, nb, groups);
+    SRAG_CUDA(cudaGetLastError());
+    pack_scan_terms_kernel<<<1, 1024, 0, st>>>(groups, vocab, term_group);
+    SRAG_CUDA(cudaGetLastError());
+    pack_row_scan_kernel<<<(int)blocks, 256, 0, st>>>(block_ptr, vocab, nb, term_group, slice_ptr);
+    SRAG_CUDA(cudaGetLastError());
+    return SRAG_OK;
+}
+
+extern "C" int srag_bm25_pack_fill(const int64_t* block_ptr, const uint32_t* slice_ptr, int vocab, int64_t n_docs,
+                                   const int32_t* doc_in, const float* imp_in, uint16_t* off_out, float* imp_out,
+                                   int permute, void* stream) {
     SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF, "bad sizes vocab=%d n_docs=%lld", vocab,
                    (long long)n_docs);
     if (n_docs == 0) return SRAG_OK;
-    SRAG_CHECK_ARG(block_ptr && doc_in && imp_in && doc_out && imp_out, "null pointer argument");
-    SRAG_CHECK_ARG(doc_in != doc_out && imp_in != imp_out, "the permutation is not in place");
+    SRAG_CHECK_ARG(block_ptr && slice_ptr && doc_in && imp_in && off_out && imp_out, "null pointer argument");
+    SRAG_CHECK_ARG(imp_in != imp_out, "packing is not in place");
     const int nb = bm25_subs(n_docs);
-    const int64_t rounds = ((int64_t)vocab * nb + 32 * BANK_ORDER_WARPS - 1) / (32 * BANK_ORDER_WARPS);
-    const int64_t blocks = rounds < 148 * 64 ? rounds : 148 * 64;
-    bm25_bank_order_kernel<<<(int)blocks, 32 * BANK_ORDER_WARPS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        block_ptr, vocab, nb, doc_in, imp_in, doc_out, imp_out);
+    bm25_pack_fill_kernel<<<pack_grid((int64_t)vocab * nb), 32 * BANK_ORDER_WARPS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        block_ptr, slice_ptr, vocab, nb, doc_in, imp_in, off_out, imp_out, permute);
+    SRAG_CUDA(cudaGetLastError());
+    return SRAG_OK;
+}
+
+extern "C" int srag_bm25_unpack_docs(const uint32_t* slice_ptr, int vocab, int64_t n_docs, const uint16_t* post_off,
+                                     const float* post_imp, int32_t* doc_out, int32_t* term_out, void* stream) {
+    SRAG_CHECK_ARG(vocab >= 1 && n_docs >= 0 && n_docs < 0x7FFFFFFF, "bad sizes vocab=%d n_docs=%lld", vocab,
+                   (long long)n_docs);
+    if (n_docs == 0) return SRAG_OK;
+    SRAG_CHECK_ARG(slice_ptr && post_off && post_imp && doc_out, "null pointer argument");
+    const int nb = bm25_subs(n_docs);
+    bm25_unpack_docs_kernel<<<pack_grid((int64_t)vocab * nb), 32 * BANK_ORDER_WARPS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        slice_ptr, vocab, nb, post_off, post_imp, doc_out, term_out);
     SRAG_CUDA(cudaGetLastError());
     return SRAG_OK;
 }
@@ -1304,7 +1525,7 @@ extern "C" int srag_bm25_workspace_bytes(int64_t n_docs, int n_queries, int k, s
     return SRAG_OK;
 }
 
-static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp, int vocab,
+static int bm25_search_impl(const uint32_t* block_ptr, const uint16_t* post_doc, const float* post_imp, int vocab,
                             int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms, int k, int64_t id_base,
                             Bm25Filter flt, float* out_scores, int64_t* out_ids, void* workspace, size_t workspace_bytes,
                             void* stream) {
@@ -1318,7 +1539,7 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
     SRAG_CHECK_ARG(block_ptr && q_terms && out_scores && out_ids && workspace, "null pointer argument");
     SRAG_CHECK_ARG(n_docs == 0 || (post_doc && post_imp), "null postings");
     SRAG_CHECK_ARG(((uintptr_t)post_doc & 15) == 0 && ((uintptr_t)post_imp & 15) == 0 && ((uintptr_t)workspace & 15) == 0,
-                   "postings / workspace must be 16-byte aligned");
+                   "post_off / post_imp / workspace must be 16-byte aligned");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const int nb = bm25_blocks(n_docs) > 0 ? bm25_blocks(n_docs) : 1;
     const int qc = n_queries < BM25_Q_CHUNK ? n_queries : BM25_Q_CHUNK;
@@ -1332,8 +1553,10 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
     {
         int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_items_kernel<false>), (int)sizeof(Bm25Smem));
         if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_items_kernel<true>), (int)sizeof(Bm25Smem));
-        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<false>), (int)sizeof(SubSmem));
-        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<true>), (int)sizeof(SubSmem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<false, false>), (int)sizeof(SubSmem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<false, true>), (int)sizeof(SubSmem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<true, false>), (int)sizeof(SubSmem));
+        if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<true, true>), (int)sizeof(SubSmem));
         if (!rc) rc = srag_current_device_props(&sm_count, nullptr, nullptr);
         if (rc) return rc;
     }
@@ -1368,14 +1591,15 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
             // filled from the front and read up to its fill level, so it needs no zeroing. Queries whose candidates
             // overflow are flagged, their region cleared, and redone by the exact per-block kernel over all blocks.
             auto kern = filtered ? bm25_items_kernel<true> : bm25_items_kernel<false>;
-            auto skern = filtered ? bm25_sub_kernel<true> : bm25_sub_kernel<false>;
+            auto skern_sample = filtered ? bm25_sub_kernel<true, true> : bm25_sub_kernel<false, true>;
+            auto skern = filtered ? bm25_sub_kernel<true, false> : bm25_sub_kernel<false, false>;
             // 8 reports per sampled sub-block when that still leaves plenty more than k of them, else 32
             const int sgroup = (long long)nb0 * BM25_SUBS * 8 >= 8ll * k ? 4 : 1;
             const size_t sample_keys = (size_t)nb0 * (SUB_SAMPLE_KEYS / sgroup);
             SRAG_CUDA(cudaMemsetAsync(sample, 0, (size_t)nq * sample_keys * sizeof(uint64_t), st));
             SRAG_CUDA(cudaMemsetAsync(q_count, 0, bm25_ctr_bytes(qc), st));
             const long long w0 = ((long long)nq * nb0 * BM25_SUBS + SUB_WARPS - 1) / SUB_WARPS;
-            skern<<<(int)(w0 < sm_count ? w0 : sm_count), 32 * SUB_WARPS, sizeof(SubSmem), st>>>(
+            skern_sample<<<(int)(w0 < sm_count ? w0 : sm_count), 32 * SUB_WARPS, sizeof(SubSmem), st>>>(
                 block_ptr, post_doc, post_imp, nb, n_sub, q_terms, max_terms, k, q0, nq, stride, nullptr, sample, q_count,
                 q_flag, n_flagged, flt, sgroup);
             SRAG_CUDA(cudaGetLastError());
@@ -1433,7 +1657,7 @@ static int bm25_search_impl(const int64_t* block_ptr, const int32_t* post_doc, c
     return SRAG_OK;
 }
 
-extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp, int vocab,
+extern "C" int srag_bm25_search(const uint32_t* block_ptr, const uint16_t* post_doc, const float* post_imp, int vocab,
                                 int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms, int k,
                                 int64_t id_base, float* out_scores, int64_t* out_ids, void* workspace,
                                 size_t workspace_bytes, void* stream) {
@@ -1442,7 +1666,7 @@ extern "C" int srag_bm25_search(const int64_t* block_ptr, const int32_t* post_do
                             workspace_bytes, stream);
 }
 
-extern "C" int srag_bm25_search_filtered(const int64_t* block_ptr, const int32_t* post_doc, const float* post_imp,
+extern "C" int srag_bm25_search_filtered(const uint32_t* block_ptr, const uint16_t* post_doc, const float* post_imp,
                                          int vocab, int64_t n_docs, const int32_t* q_terms, int n_queries, int max_terms,
                                          int k, int64_t id_base, const uint32_t* doc_tags, const int32_t* doc_group,
                                          const uint32_t* q_tag_mask, const int32_t* q_group, float* out_scores,

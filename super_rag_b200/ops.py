@@ -243,29 +243,61 @@ def bm25_build_from_tokens(tokens: torch.Tensor, doc_ptr: torch.Tensor, vocab: i
     return term_ptr, post_doc, post_tf, dl[:n_docs], df, block_ptr
 
 
-def bm25_bank_order(block_ptr, post_doc, post_imp, n_docs: int):
-    """Permute the postings inside every (term, doc-block) slice for conflict-free shared-memory accumulation
-    (srag_bm25_bank_order). Returns new (post_doc, post_imp), padded like the inputs; scores are unchanged."""
+BM25_PAD = 8   # entries of padding behind the searched posting arrays (bulk copies and 128-bit loads stay inside)
+
+
+def bm25_pack(block_ptr, post_doc, post_imp, n_docs: int, permute: bool = True):
+    """Canonical postings -> the searched layout (srag_bm25_pack_plan / _fill): every (term, sub-block) slice starts on a
+    group of 4 postings and is padded to whole groups with zero-impact postings, documents become 16-bit tile offsets and
+    (permute) the postings of every slice are laid out for conflict-free shared-memory accumulation.
+    Returns (slice_ptr int32-typed [V, n_sub+1] holding uint32 group indexes, post_off int16-typed (uint16 patterns),
+    post_imp fp32), the two posting arrays padded behind their end; scores are unchanged. One host sync (the padded size)."""
     _need_cuda(block_ptr, post_doc, post_imp)
-    nnz = post_doc.numel()
+    lib = _lib.load()
     dev = post_doc.device
+    vocab = block_ptr.shape[0]
     with torch.cuda.device(dev):
-        pd = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]
-        pi = torch.zeros(nnz + 4, dtype=torch.float32, device=dev)[:nnz]
-        if nnz:
-            _lib.check(_lib.load().srag_bm25_bank_order(_ptr(block_ptr), block_ptr.shape[0], n_docs, _ptr(post_doc),
-                                                        _ptr(post_imp), _ptr(pd), _ptr(pi), _stream(dev)),
-                       "srag_bm25_bank_order")
-    return pd, pi
+        scratch = torch.empty(2 * vocab + 1, dtype=torch.int64, device=dev)
+        slice_ptr = torch.empty(block_ptr.shape, dtype=torch.int32, device=dev)
+        st = _stream(dev)
+        _lib.check(lib.srag_bm25_pack_plan(_ptr(block_ptr), vocab, n_docs, _ptr(scratch), _ptr(slice_ptr), st), "srag_bm25_pack_plan")
+        groups = int(scratch[2 * vocab].item())
+        if groups >= 1 << 32:
+            raise SragError(f"{groups} groups of 4 postings do not fit the 32-bit slice table: shard the index")
+        n_pad = 4 * groups
+        po = torch.zeros(n_pad + BM25_PAD, dtype=torch.int16, device=dev)[:n_pad]
+        pi = torch.zeros(n_pad + BM25_PAD, dtype=torch.float32, device=dev)[:n_pad]
+        if post_doc.numel():
+            _lib.check(lib.srag_bm25_pack_fill(_ptr(block_ptr), _ptr(slice_ptr), vocab, n_docs, _ptr(post_doc), _ptr(post_imp),
+                                               _ptr(po), _ptr(pi), 1 if permute else 0, st), "srag_bm25_pack_fill")
+    return slice_ptr, po, pi
 
 
-def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tensor, k: int, id_base: int = 0,
+def bm25_unpack_docs(slice_ptr, post_off, post_imp, n_docs: int, with_terms: bool = False):
+    """int32 document id of every stored posting (-1 = padding), in the stored order (srag_bm25_unpack_docs); with
+    `with_terms` also the term of every posting. Not on the search path."""
+    _need_cuda(slice_ptr, post_off, post_imp)
+    n = post_off.numel()
+    dev = post_off.device
+    with torch.cuda.device(dev):
+        doc = torch.full((max(n, 1),), -1, dtype=torch.int32, device=dev)[:n]
+        term = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)[:n] if with_terms else None
+        if n:
+            _lib.check(_lib.load().srag_bm25_unpack_docs(_ptr(slice_ptr), slice_ptr.shape[0], n_docs, _ptr(post_off), _ptr(post_imp),
+                                                         _ptr(doc), _ptr(term), _stream(dev)), "srag_bm25_unpack_docs")
+    return (doc, term) if with_terms else doc
+
+
+def bm25_search(slice_ptr, post_off, post_imp, n_docs: int, q_terms: torch.Tensor, k: int, id_base: int = 0,
                 workspace: Optional[torch.Tensor] = None, doc_tags: Optional[torch.Tensor] = None,
                 q_tag_mask: Optional[torch.Tensor] = None, doc_group: Optional[torch.Tensor] = None,
                 q_group: Optional[torch.Tensor] = None):
     """q_terms int32 [B, T]: unique ascending term ids, -1 padded. Optional metadata pre-filter as in
     topk_search (int32 tensors: doc_tags / doc_group [n_docs], q_tag_mask / q_group [B])."""
-    _need_cuda(block_ptr, post_doc, post_imp, q_terms)
+    _need_cuda(slice_ptr, post_off, post_imp, q_terms)
+    if slice_ptr.dtype != torch.int32 or post_off.dtype != torch.int16 or post_imp.dtype != torch.float32 or \
+            post_off.numel() != post_imp.numel():
+        raise SragError("bm25_search wants the searched layout of ops.bm25_pack: slice_ptr (32-bit), post_off (16-bit), post_imp fp32")
     if (doc_tags is None) != (q_tag_mask is None) or (doc_group is None) != (q_group is None):
         raise SragError("doc_tags / q_tag_mask and doc_group / q_group come in pairs")
     for t, n_expect, what in ((doc_tags, n_docs, "doc_tags"), (doc_group, n_docs, "doc_group"),
@@ -277,7 +309,7 @@ def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tenso
     lib = _lib.load()
     B, T = q_terms.shape
     dev = q_terms.device
-    vocab = block_ptr.shape[0]
+    vocab = slice_ptr.shape[0]
     with torch.cuda.device(dev):
         out = C.c_size_t()
         _lib.check(lib.srag_bm25_workspace_bytes(n_docs, B, k, C.byref(out)), "srag_bm25_workspace_bytes")
@@ -287,11 +319,11 @@ def bm25_search(block_ptr, post_doc, post_imp, n_docs: int, q_terms: torch.Tenso
         ids = torch.empty(B, k, dtype=torch.int64, device=dev)
         if doc_tags is not None or doc_group is not None:
             _lib.check(lib.srag_bm25_search_filtered(
-                _ptr(block_ptr), _ptr(post_doc), _ptr(post_imp), vocab, n_docs, _ptr(q_terms.contiguous()), B, T, k,
+                _ptr(slice_ptr), _ptr(post_off), _ptr(post_imp), vocab, n_docs, _ptr(q_terms.contiguous()), B, T, k,
                 id_base, _ptr(doc_tags), _ptr(doc_group), _ptr(q_tag_mask), _ptr(q_group), _ptr(scores), _ptr(ids),
                 _ptr(workspace), workspace.numel(), _stream(dev)), "srag_bm25_search_filtered")
         else:
-            _lib.check(lib.srag_bm25_search(_ptr(block_ptr), _ptr(post_doc), _ptr(post_imp), vocab, n_docs,
+            _lib.check(lib.srag_bm25_search(_ptr(slice_ptr), _ptr(post_off), _ptr(post_imp), vocab, n_docs,
                                             _ptr(q_terms.contiguous()), B, T, k, id_base, _ptr(scores), _ptr(ids),
                                             _ptr(workspace), workspace.numel(), _stream(dev)), "srag_bm25_search")
     return scores, ids

@@ -14,8 +14,8 @@ through one pinned staging buffer, so saving a 20 GB corpus does not need 20 GB 
 
 Kinds written by this package:
   "vector"  rows bf16 [n, dim], row_scale fp32 [n] (NaN = tombstone), doc table (ids / texts / metadata)
-  "bm25"    term_ptr int64 [V+1], post_doc int32 [nnz], post_imp fp32 [nnz], dl int32 [n_docs], df int64 [V]
-            (block_ptr is rebuilt on load: it depends on the library's block size)
+  "bm25"    the searched layout as it sits in HBM: term_ptr int64 [V+1], slice_ptr uint32 [V, n_sub+1], post_off uint16,
+            post_imp fp32 (padded slices), dl int32 [n_docs], df int64 [V]; round-1 shards (post_doc int32) still load
 """
 from __future__ import annotations
 

@@ -194,6 +194,9 @@ def test_bm25_two_phase_with_ties_at_the_threshold():
 
 
 def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
+    """The searched layout: every slice starts on a group of 4 postings, is padded to whole groups with zero-impact
+    postings (trash offsets), holds the same (doc, impact) pairs as the canonical slice, and — bank-ordered — is laid
+    out as oracle/bank_order.py restates it."""
     import torch
     from super_rag_b200 import ops
     from super_rag_b200.bm25 import Bm25Index
@@ -205,33 +208,51 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
     idx = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
     assert not plain.bank_ordered and idx.bank_ordered
     bd = ops.bm25_block_docs()
+    tp, pd, ptf, dl = oracle.build_postings(tokens, doc_ptr, vocab)
+    imp = oracle.bm25_impacts(tp, pd, ptf, dl).view(np.uint32)
     d0, w0 = plain.post_doc.cpu().numpy(), plain.post_imp.cpu().numpy().view(np.uint32)
     d1, w1 = idx.post_doc.cpu().numpy(), idx.post_imp.cpu().numpy().view(np.uint32)
-    bp = idx.block_ptr.cpu().numpy()
-    assert (bp == plain.block_ptr.cpu().numpy()).all()
-    # every slice holds the same (doc, impact) pairs as before, all inside its doc block; the layout itself is the one
-    # oracle/bank_order.py restates (checked on a sample of slices: the restatement is a Python loop)
+    sp = idx.slice_ptr.cpu().numpy().view(np.uint32).astype(np.int64) * 4
+    assert (sp == plain.slice_ptr.cpu().numpy().view(np.uint32).astype(np.int64) * 4).all()
+    assert len(d1) == sp[-1, -1] and len(d1) % 4 == 0
+    # every slice: same pairs as the canonical postings of (term, sub-block), all inside the sub-block, padding = (-1, 0);
+    # the layout itself is the one oracle/bank_order.py restates (checked on a sample of slices: it is a Python loop)
     from oracle import bank_order as bo
     t0 = t1 = 0
     exact = 0
+    n_sub = sp.shape[1] - 1
     for t in range(vocab):
-        for j in range(bp.shape[1] - 1):
-            lo, hi = int(bp[t, j]), int(bp[t, j + 1])
-            if lo == hi:
+        docs_t, imps_t = pd[tp[t]:tp[t + 1]], imp[tp[t]:tp[t + 1]]
+        for j in range(n_sub):
+            lo, hi = int(sp[t, j]), int(sp[t, j + 1])
+            sel = (docs_t // bd) == j
+            a, wa = docs_t[sel], imps_t[sel]
+            n = len(a)
+            assert hi - lo == (n + 3) // 4 * 4, (t, j)
+            if n == 0:
                 continue
-            a, b = d0[lo:hi], d1[lo:hi]
-            assert (b // bd == j).all()
+            b, wb = d1[lo:lo + n], w1[lo:lo + n]
+            assert (d1[lo + n:hi] == -1).all() and (w1[lo + n:hi] == 0).all() and (d0[lo + n:hi] == -1).all()
+            assert (d0[lo:lo + n] == a).all() and (w0[lo:lo + n] == wa).all()          # SRAG_BM25_BANK_ORDER=0: ascending
             o = np.argsort(b, kind="stable")
-            assert (b[o] == a).all() and (w1[lo:hi][o] == w0[lo:hi]).all()
-            if hi - lo >= 64:
-                t0 += bo.access_wavefronts(a, lo)[0]
-                t1 += bo.access_wavefronts(b, lo)[0]
-            if exact < 60 and (hi - lo >= 40 or (hi - lo >= 3 and exact % 3 == 0)):
-                wd, ww = bo.bank_order_slice(a, w0[lo:hi], lo)
-                assert (wd == b).all() and (ww == w1[lo:hi]).all(), (t, j)
+            assert (b[o] == a).all() and (wb[o] == wa).all()
+            if n >= 64:
+                t0 += bo.access_wavefronts(a, 0)[0]
+                t1 += bo.access_wavefronts(b, 0)[0]
+            if exact < 60 and (n >= 40 or (n >= 3 and exact % 3 == 0)):
+                wd, ww = bo.bank_order_slice(a, wa, 0)
+                assert (wd == b).all() and (ww == wb).all(), (t, j)
                 exact += 1
     assert exact >= 30
     assert t1 < 0.8 * t0, (t0, t1)
+    # the raw trash offsets: sub-block 0 of a block -> byte 8192, sub-block m -> m * 8192 - 4
+    off = idx.post_off.cpu().numpy().view(np.uint16)
+    for t in (0, vocab - 1):
+        for j in range(min(n_sub, 12)):
+            lo, hi = int(sp[t, j]), int(sp[t, j + 1])
+            pads = off[lo:hi][w1[lo:hi] == 0]
+            m = j % 8
+            assert (pads == (8192 if m == 0 else m * 8192 - 4)).all()
     # same scores and ids, bit for bit, from both layouts
     rng = np.random.default_rng(5)
     queries = [rng.integers(0, vocab, size=int(rng.integers(1, 9))).tolist() for _ in range(64)]
@@ -240,7 +261,7 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
     assert torch.equal(i0, i1) and torch.equal(s0.view(torch.int32), s1.view(torch.int32))
     # deterministic: a second build gives the same layout
     again = Bm25Index.from_tokens(torch.from_numpy(tokens).cuda(), torch.from_numpy(doc_ptr).cuda(), vocab)
-    assert torch.equal(again.post_doc, idx.post_doc) and torch.equal(again.post_imp.view(torch.int32), idx.post_imp.view(torch.int32))
+    assert torch.equal(again.post_off, idx.post_off) and torch.equal(again.post_imp.view(torch.int32), idx.post_imp.view(torch.int32))
 
 
 def test_bm25_sub_kernel_candidate_paths_and_fallback():

@@ -109,6 +109,18 @@ def test_collection_and_bm25_round_trip_gpu(tmp_path):
     bs1, bi1 = idx2.search(queries, 10)
     assert torch.equal(bi0, bi1) and torch.equal(bs0.view(torch.int32), bs1.view(torch.int32))
     assert idx2.id_base == 40 and idx2.stats.avgdl == idx.stats.avgdl and (idx2.stats.df == idx.stats.df).all()
+    assert torch.equal(idx2.post_off, idx.post_off) and torch.equal(idx2.slice_ptr, idx.slice_ptr)   # used as stored: no rebuild
+    # a shard as round 1 wrote it (int32 documents, unpadded) still loads: it is packed again
+    cd, ci = idx.canonical_postings()
+    pb1 = str(tmp_path / "bm25_r1.shard")
+    shardio.write_shard(pb1, "bm25", {"n_docs": idx.n_docs, "vocab": vocab, "id_base": 40, "stats_n_docs": idx.stats.n_docs,
+                                      "avgdl": float(idx.stats.avgdl), "bank_ordered": False, "block_docs": 2048},
+                        {"term_ptr": idx.term_ptr, "post_doc": cd, "post_imp": ci, "dl": idx.dl,
+                         "df": torch.from_numpy(np.ascontiguousarray(idx.stats.df, dtype=np.int64))})
+    idx3 = Bm25Index.load(pb1, dev)
+    bs3, bi3 = idx3.search(queries, 10)
+    assert torch.equal(bi0, bi3) and torch.equal(bs0.view(torch.int32), bs3.view(torch.int32))
+    assert torch.equal(idx3.post_off, idx.post_off)
 
     enc = fulltext.hash_tokenizer(4096)
     ft = fulltext.FulltextCollection("t_ft_shard", tokenizer=enc, vocab=4096)

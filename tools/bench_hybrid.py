@@ -72,7 +72,7 @@ def build_index(n_docs, dev, keep_terms=None, kept=None):
     term_ptr[1:] = torch.cumsum(df, 0)
     nnz = int(term_ptr[-1].item())
     chunk_base = term_ptr[:-1][None, :] + torch.cumsum(counts, 0) - counts      # [chunk, term] first slot
-    post_doc = torch.zeros(nnz + 4, dtype=torch.int32, device=dev)[:nnz]
+    post_doc = torch.zeros(nnz + 8, dtype=torch.int32, device=dev)[:nnz]
     post_tf = torch.empty(nnz, dtype=torch.int32, device=dev)
     for c in range(n_chunks):
         t, d, tf, _ = gen_chunk(c, n_docs, cdf, dev)
@@ -108,11 +108,14 @@ def make_queries(n_q, terms_per_q, dev, lo_rank=101, seed=4):
 
 
 def torch_restatement(idx, terms, k):
+    if getattr(idx, "_doc_cache", None) is None:       # the searched layout holds 16-bit offsets: unpack the ids once
+        idx._doc_cache = idx.post_doc
+    post_doc = idx._doc_cache
     acc = torch.zeros(idx.n_docs, dtype=torch.float32, device=idx.device)
     hit = torch.zeros(idx.n_docs, dtype=torch.bool, device=idx.device)
     for t in sorted(set(int(x) for x in terms if x >= 0)):
         a, b = int(idx.term_ptr[t].item()), int(idx.term_ptr[t + 1].item())
-        d = idx.post_doc[a:b].to(torch.int64)
+        d = post_doc[a:b].to(torch.int64)
         acc[d] = acc[d] + idx.post_imp[a:b]          # unique docs inside a term: one add per doc, fixed order
         hit[d] = True
     key = torch.where(hit, acc, torch.full_like(acc, -1.0))
@@ -215,7 +218,7 @@ def run(args, dev=None, hooks=None):
                          "traffic": bm25_traffic(args.docs, args.queries), "traffic_source": "ncu capture under profiles/ (see profiles/bm25_traffic.json), not this run"},
             "e2e": {"value": args.queries / (e2e_ms * 1e-3), "unit": "queries/s", "ms_per_batch": e2e_ms,
                     "h2d_bytes_per_step": int(qt_host.numel() * 4), "d2h_bytes_per_step": args.queries * 100 * 12},
-            "index_bytes": idx.nnz * 8, "index_build_s": build_s, "scores_sorted": sorted_ok,
+            "index_bytes": idx.nnz_stored * idx.bytes_per_posting(), "index_padding_postings": idx.nnz_stored - idx.nnz, "index_build_s": build_s, "scores_sorted": sorted_ok,
             "oracle_check": hooks.c3_check(ctx) if hooks.c3_check and n_check else None,
             "cpu_baseline": hooks.c3_cpu(ctx) if hooks.c3_cpu and n_check else None}
     yield line
