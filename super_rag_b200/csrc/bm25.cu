@@ -725,13 +725,17 @@ bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], 
 // bm25_sub_kernel: scoring at WARP granularity (sample pass and main pass). A work item is (query, sub-block of
 // BM25_SUB_DOCS documents); the sub-block's fp32 accumulators are 8 KB of shared memory private to ONE warp, so every add
 // to a document is made by the same warp: terms are applied in ascending order with nothing but __syncwarp() between
-// rounds — no CTA barrier, no producer warps, no descriptor ring. 27 independent warps per SM walk the items
-// round-robin; neighbouring warps take neighbouring sub-blocks, i.e. neighbouring pieces of the same posting lists.
-//   * lane u holds the bounds of query term u inside the sub-block (block_ptr), fetched two items ahead (term ids three
-//     ahead), so no dependent load is waited for; the next item's slices are pulled into L2 a whole item early;
-//   * a round = 128 postings of one term (one 16-byte load per lane and array, L1 no-allocate), or one NARROW round
-//     (one posting per lane) for a slice of up to 32 postings; the rounds of all terms form one stream in ascending-term
-//     order that is loaded SUB_DEPTH rounds ahead of the adds;
+// terms — no CTA barrier, no producer warps. 20 independent warps per SM walk the items round-robin; neighbouring warps
+// take neighbouring sub-blocks, i.e. neighbouring pieces of the same posting lists.
+//   * lane u holds the bounds of query term u inside the sub-block (slice_ptr), fetched two items ahead (term ids three
+//     ahead), so no dependent load is waited for;
+//   * a round = up to 128 postings of one term: 8 bytes of offsets + 16 bytes of impacts per lane. Slices start on a
+//     group of 4 postings and are padded to whole groups (padding adds +0.0 to a trash slot), so a round has no masks;
+//     the rounds of all terms form one stream in ascending-term order. The stream is described 32 rounds at a time —
+//     lane i works out where round i starts and how long it is by bisection in the running totals, ONCE per chunk — and
+//     the round loop only broadcasts two words per round;
+//   * the postings of a round travel global -> shared by cp.async (one group per round) SUB_DEPTH - 1 rounds ahead of the
+//     adds, and cp.async.wait_group gives a true software pipeline (see SubWarpTile for why registers cannot);
 //   * main pass: a document whose accumulator crosses tau is remembered (<= SUB_CAND per item); at the end of the item
 //     its final score goes into the query's candidate region — the query's slice of `partial`, filled from the front
 //     through one atomic counter per query. tau is the k-th best of the scores a 1/stride sample reported, so a query
@@ -739,23 +743,43 @@ bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], 
 //   * more crossings in one sub-block than SUB_CAND, or a full region, flags the QUERY; flagged queries are redone
 //     by bm25_items_kernel (exact top-k of every block) after their region is cleared. Massive ties end up there.
 // Per-document sums are formed exactly as in bm25_items_kernel: bit-exact with the oracle.
-constexpr int SUB_WARPS = 27;   // 27 x (8 KB of accumulators + two trash slots) + candidate lists = 220 KB: one CTA per SM
-constexpr int SUB_CAND = 64;
-#ifndef SRAG_BM25_SUB_NARROW
-#define SRAG_BM25_SUB_NARROW 32
+// History at C3 (ms per batch): 10.85 round 1 (8 B / posting, masked register-staged rounds, 8.35e9 warp instructions) ->
+// 10.97 with 6-byte padded slices and chunked round descriptors (5.84e9 instructions, but every round still waited a full
+// L2 round trip: one scoreboard for all LDGs) -> 9.87 with the cp.async pipeline; stop-word queries 71.9 -> 35.1 ms.
+#ifndef SRAG_BM25_SUB_DEPTH
+#define SRAG_BM25_SUB_DEPTH 4
 #endif
-constexpr uint32_t SUB_NARROW = SRAG_BM25_SUB_NARROW;  // slices up to this long: one posting per lane (0 = never)
-static_assert(SUB_NARROW <= 32, "a narrow round gives one posting to each lane");
+constexpr int SUB_DEPTH = SRAG_BM25_SUB_DEPTH;  // stages of the round pipeline: SUB_DEPTH - 1 rounds in flight while one is applied
+#ifndef SRAG_BM25_SUB_WARPS
+#define SRAG_BM25_SUB_WARPS (SRAG_BM25_SUB_DEPTH <= 2 ? 23 : SRAG_BM25_SUB_DEPTH == 3 ? 21 : 20)
+#endif
+constexpr int SUB_WARPS = SRAG_BM25_SUB_WARPS;   // warps per CTA (one CTA per SM): as many as the shared memory takes
+#ifndef SRAG_BM25_PF
+#define SRAG_BM25_PF 0
+#endif
+// L2 prefetch of a later item's slices: 0 off, 1 the next item, 2 the item after next. Off since the cp.async pipeline
+// covers the latency by itself: C3 9.87 ms without against 10.28 ms with it, the stop-word queries 35.1 ms against 52.1 ms
+// (round 1's register-staged loads needed it: 12.97 ms without, 10.97 ms with).
+constexpr int SUB_PF = SRAG_BM25_PF;
+constexpr int SUB_CAND = 64;
 
-// One warp's accumulators with a trash slot on either side. Slices are padded to whole groups of 4 postings; a padding
-// posting carries impact +0.0 and an offset that lands on a trash slot of whichever warp processes it:
+// One warp's accumulators with a trash slot on either side, and the staging buffers of its round pipeline.
+// Slices are padded to whole groups of 4 postings; a padding posting carries impact +0.0 and an offset that lands on a
+// trash slot of whichever warp processes it:
 //   sub-block 0 of a block: offset 8192 = the float right AFTER the warp's 2048 accumulators (acc_b = acc)
 //   sub-block m > 0:        offset m * 8192 - 4 = the float right BEFORE them (acc_b = acc - m * 8192 bytes)
-// so padding needs no mask anywhere in the round loop (SUB_TRASH_OFFSET below is what the index build writes).
+// so padding needs no mask anywhere in the round loop (sub_trash_offset below is what the index build writes).
+// Staging: a round = up to 128 postings = 8 bytes of offsets + 16 bytes of impacts per lane, copied global -> shared by
+// cp.async (LDGSTS) SUB_DEPTH - 1 rounds before they are applied. The copies of a round are one cp.async GROUP, and
+// cp.async.wait_group waits for "all but the N newest groups": a true software pipeline. (Register-staged loads cannot
+// be pipelined here: ptxas puts the LDGs of every stage on ONE scoreboard, so the first use of round r's data also waits
+// for the loads of rounds r + 1, r + 2 issued after it — measured: depth 2, 3 and 4 all ran at the speed of depth 1.)
 struct SubWarpTile {
     float before[4];
     float acc[BM25_SUB_DOCS];
     float after[4];
+    float4 stage_imp[SUB_DEPTH][32];
+    uint2 stage_off[SUB_DEPTH][32];
 };
 __host__ __device__ constexpr uint32_t sub_trash_offset(int sub_in_block) {
     return sub_in_block == 0 ? (uint32_t)BM25_SUB_DOCS * 4u : (uint32_t)sub_in_block * (BM25_SUB_DOCS * 4u) - 4u;
@@ -768,43 +792,19 @@ struct SubSmem {
     uint32_t cand_count[SUB_WARPS];
 };
 
-__device__ __forceinline__ uint32_t ldg_stream_u16(const uint16_t* p) {
-    uint32_t v;
-    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=r"(v) : "l"(p));
-    return v;
+__device__ __forceinline__ void cp_async_8(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ float ldg_stream_f32(const float* p) {
-    float v;
-    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    return v;
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ uint2 ldg_stream_u16x4(const uint16_t* p) {
-    uint2 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ float4 ldg_stream_f32x4(const float* p) {
-    float4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// One stage of the round pipeline: the postings a lane holds for one round, loaded SUB_DEPTH - 1 rounds ahead of their
-// use (the loads hit L2: the slices were prefetched an item earlier; two rounds in flight cover that latency, one does
-// not: 12.5 ms against 11.8 ms at C3).
-//   meta: bits 0..7 = postings of the round (1..128), bit 16 NARROW (lane l < count holds posting l: o.x, w.x),
-//         bit 17 = first round of a term; a wide round gives postings 4 l .. 4 l + 3 to lane l (count is a multiple of 4)
-struct SubStage {
-    uint2 o;          // four 16-bit byte offsets (block-relative)
-    float4 w;         // four impacts
-    uint32_t meta;
-};
-constexpr uint32_t STAGE_NARROW = 1u << 16, STAGE_NEW_TERM = 1u << 17;
-#ifndef SRAG_BM25_SUB_DEPTH
-#define SRAG_BM25_SUB_DEPTH 3
-#endif
-constexpr int SUB_DEPTH = SRAG_BM25_SUB_DEPTH;  // stages: SUB_DEPTH - 1 rounds in flight while one is applied
+// round descriptor word: bits 0..7 = postings of the round (4 .. 128, a multiple of 4: lane l holds postings 4 l .. 4 l + 3
+// when 4 l < count), bit 17 = first round of a term (a __syncwarp() goes before it)
+constexpr uint32_t STAGE_NEW_TERM = 1u << 17;
 
 // A document crossed tau: remember its tile offset (rare: ~32 k crossings per query over all its sub-blocks). Out of
 // line, so that the round loop stays small.
@@ -838,7 +838,8 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
     SubSmem* sm = reinterpret_cast<SubSmem*>(bm25_smem_raw);
     constexpr uint32_t FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    float* acc = sm->tile[w].acc;
+    SubWarpTile* tile = &sm->tile[w];
+    float* acc = tile->acc;
     uint16_t* cand = sm->cand[w];
     uint32_t* cand_count = &sm->cand_count[w];
     const int nb0 = (n_blocks + stride - 1) / stride;
@@ -872,13 +873,15 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
         if (sub < 0 || j0 + lane >= max_terms) return -1;
         return __ldg(q_terms + (size_t)(q_offset + x.q) * max_terms + j0 + lane);
     };
-    auto bounds_of = [&](int sub, int32_t t, uint32_t& g0, uint32_t& n) {  // first group of 4 and (padded) length of the slice
-        g0 = 0;
-        n = 0;
+    // first and one-past-last group of 4 postings of the slice; kept RAW (the length is only formed where it is used, an
+    // item later: a subtraction right behind the loads would wait for them)
+    auto bounds_of = [&](int sub, int32_t t, uint32_t& g_lo, uint32_t& g_hi) {
+        g_lo = 0;
+        g_hi = 0;
         if (sub >= 0 && t >= 0) {
             const uint32_t* sp = slice_ptr + (size_t)t * (n_sub + 1) + sub;
-            g0 = __ldg(sp);
-            n = (__ldg(sp + 1) - g0) << 2;
+            g_lo = __ldg(sp);
+            g_hi = __ldg(sp + 1);
         }
     };
     auto flag_query = [&](int q) {
@@ -893,10 +896,10 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
     int s0 = sub_of(x0), s1 = sub_of(x1), s2 = sub_of(x2), s3 = sub_of(x3);
     int32_t t3 = term_of(x3, s3, 0);
     uint32_t g0, g1, g2;   // slice starts, in groups of 4 postings
-    uint32_t n0, n1, n2;   // slice lengths in postings (multiples of 4)
-    bounds_of(s0, term_of(x0, s0, 0), g0, n0);
-    bounds_of(s1, term_of(x1, s1, 0), g1, n1);
-    bounds_of(s2, term_of(x2, s2, 0), g2, n2);
+    uint32_t h0, h1, h2;   // slice ends (exclusive), in groups
+    bounds_of(s0, term_of(x0, s0, 0), g0, h0);
+    bounds_of(s1, term_of(x1, s1, 0), g1, h1);
+    bounds_of(s2, term_of(x2, s2, 0), g2, h2);
     float tau0 = s0 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x0.q * k + (k - 1)) : 0.f;
     float tau1 = s1 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
 
@@ -916,12 +919,12 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                 f_mask = flt.doc_tags ? __ldg(flt.q_tag_mask + q_offset + q) : 0xFFFFFFFFu;
                 f_group = flt.doc_group ? __ldg(flt.q_group + q_offset + q) : -1;
             }
-            {
+            if constexpr (SUB_PF > 0) {
                 // Pull the NEXT item's slices into L2 now (one 128-byte line per request): its loads then see L2 latency
                 // instead of HBM latency, and nothing has to be held in registers meanwhile. Lane group pf_term looks
                 // after term pf_term, its lanes take every (1 << lpt_log)-th line.
-                const uint32_t g_p = __shfl_sync(FULL, g1, pf_term);
-                const uint32_t n_p = __shfl_sync(FULL, n1, pf_term);
+                const uint32_t g_p = __shfl_sync(FULL, SUB_PF == 2 ? g2 : g1, pf_term);
+                const uint32_t n_p = (__shfl_sync(FULL, SUB_PF == 2 ? h2 : h1, pf_term) - g_p) << 2;
                 if (n_p > 0) {
                     const char* po = reinterpret_cast<const char*>(post_off) + (size_t)g_p * 8u;
                     const char* pi = reinterpret_cast<const char*>(post_imp) + (size_t)g_p * 16u;
@@ -942,11 +945,11 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                 else sub_record(cand_count, cand, off_bytes);
             };
             for (int j0 = 0; j0 < max_terms; j0 += 32) {
-                if (j0 > 0) bounds_of(s0, term_of(x0, s0, j0), g0, n0);  // queries with more than 32 terms: fetched in line
-                // lane u = term j0 + u: its rounds — one NARROW round for a slice of up to SUB_NARROW postings, else wide
-                // rounds of 128 — and the running total over the terms (ascending term id = lane order)
-                const uint32_t n_l = n0;
-                const uint32_t cnt = n_l == 0 ? 0u : n_l <= SUB_NARROW ? 1u : (n_l + 127u) >> 7;
+                if (j0 > 0) bounds_of(s0, term_of(x0, s0, j0), g0, h0);  // queries with more than 32 terms: fetched in line
+                // lane u = term j0 + u: its rounds of up to 128 postings and the running total over the terms (ascending
+                // term id = lane order)
+                const uint32_t n_l = (h0 - g0) << 2;   // postings of the (padded) slice, a multiple of 4
+                const uint32_t cnt = (n_l + 127u) >> 7;
                 uint32_t incl = cnt;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -980,54 +983,35 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                     const uint32_t r_in = g - (incl_u - cnt_u);            // round inside its term
                     const uint32_t d_grp = g0_u + (r_in << 5);             // first group of 4 postings of the round
                     const uint32_t left = n_u - (r_in << 7);
-                    uint32_t d_meta = (n_u <= SUB_NARROW ? (n_u | STAGE_NARROW) : (left < 128u ? left : 128u)) |
-                                      (r_in == 0 ? STAGE_NEW_TERM : 0u);
+                    const uint32_t d_meta = (left < 128u ? left : 128u) | (r_in == 0 ? STAGE_NEW_TERM : 0u);
                     const int n_chunk = (int)(rounds - base < 32u ? rounds - base : 32u);
 
-                    auto fetch = [&](SubStage& st, int r) {   // r: round inside the chunk (warp-uniform)
+                    // fetch: start the copies of round r (inside the chunk, warp-uniform) into stage r % SUB_DEPTH
+                    auto fetch = [&](int stage, int r, uint32_t& meta_out) {
                         const uint32_t grp = __shfl_sync(FULL, d_grp, r);
                         const uint32_t meta = __shfl_sync(FULL, d_meta, r);
-                        st.meta = meta;
-                        const uint32_t count = meta & 0xFFu;
-                        if (meta & STAGE_NARROW) {
-                            if ((uint32_t)lane < count) {
-                                const size_t p = (size_t)grp * 4u + (uint32_t)lane;
-                                st.o.x = ldg_stream_u16(post_off + p);
-                                st.w.x = ldg_stream_f32(post_imp + p);
-                            }
-                        } else if (4u * (uint32_t)lane < count) {
+                        meta_out = meta;
+                        if (4u * (uint32_t)lane < (meta & 0xFFu)) {
                             const size_t p = ((size_t)grp + (uint32_t)lane) * 4u;
-                            st.o = ldg_stream_u16x4(post_off + p);
-                            st.w = ldg_stream_f32x4(post_imp + p);
+                            cp_async_8(&tile->stage_off[stage][lane], post_off + p);
+                            cp_async_16(&tile->stage_imp[stage][lane], post_imp + p);
                         }
                     };
-                    auto apply = [&](const SubStage& st) {
-                        const uint32_t meta = st.meta;
+                    auto apply = [&](int stage, uint32_t meta) {
                         if (meta & STAGE_NEW_TERM) __syncwarp();  // the previous term's writes are visible to every lane
-                        const uint32_t count = meta & 0xFFu;
-                        if (meta & STAGE_NARROW) {      // ---- narrow: one posting per lane
-                            if ((uint32_t)lane < count) {
-                                float* p = reinterpret_cast<float*>(acc_b + st.o.x);
-                                const float a0 = *p;
-                                const float v0 = __fadd_rn(a0, st.w.x);
-                                *p = v0;
-                                if constexpr (!SAMPLE) {
-                                    if (__float_as_uint(v0) >= cross_bits && __float_as_uint(a0) < cross_bits) record(st.o.x);
-                                }
-                            }
-                            return;
-                        }
-                        if (4u * (uint32_t)lane < count) {   // ---- wide round: four postings per lane, no masks (padding
-                                                             // postings add +0.0 to a trash slot)
-                            const uint32_t o0 = st.o.x & 0xFFFFu, o1 = st.o.x >> 16, o2 = st.o.y & 0xFFFFu, o3 = st.o.y >> 16;
+                        if (4u * (uint32_t)lane < (meta & 0xFFu)) {
+                            // four postings per lane, no masks (padding postings add +0.0 to a trash slot)
+                            const uint2 o = tile->stage_off[stage][lane];
+                            const float4 wv = tile->stage_imp[stage][lane];
+                            const uint32_t o0 = o.x & 0xFFFFu, o1 = o.x >> 16, o2 = o.y & 0xFFFFu, o3 = o.y >> 16;
                             float* p0 = reinterpret_cast<float*>(acc_b + o0);
                             float* p1 = reinterpret_cast<float*>(acc_b + o1);
                             float* p2 = reinterpret_cast<float*>(acc_b + o2);
                             float* p3 = reinterpret_cast<float*>(acc_b + o3);
                             // the four reads are issued together, then the adds, then the writes
                             const float a0 = *p0, a1 = *p1, a2 = *p2, a3 = *p3;
-                            const float v0 = __fadd_rn(a0, st.w.x), v1 = __fadd_rn(a1, st.w.y);
-                            const float v2 = __fadd_rn(a2, st.w.z), v3 = __fadd_rn(a3, st.w.w);
+                            const float v0 = __fadd_rn(a0, wv.x), v1 = __fadd_rn(a1, wv.y);
+                            const float v2 = __fadd_rn(a2, wv.z), v3 = __fadd_rn(a3, wv.w);
                             *p0 = v0;
                             *p1 = v1;
                             *p2 = v2;
@@ -1043,27 +1027,30 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                             }
                         }
                     };
-                    // SUB_DEPTH stages in rotation, each loaded SUB_DEPTH - 1 rounds before it is applied; the rotation is
-                    // unrolled so that the stages stay in registers and are never copied
-                    SubStage st[SUB_DEPTH];
+                    // SUB_DEPTH stages in rotation. Every step commits exactly one cp.async group (an empty one past the
+                    // end of the chunk), so "all but the SUB_DEPTH - 1 newest groups are complete" always means "the round
+                    // about to be applied has landed". A lane only ever reads what it copied itself: no barrier needed.
+                    uint32_t metas[SUB_DEPTH];
 #pragma unroll
-                    for (int i = 0; i < SUB_DEPTH; ++i) {
-                        st[i].o = make_uint2(0u, 0u);
-                        st[i].w = make_float4(0.f, 0.f, 0.f, 0.f);
-                        st[i].meta = 0u;
+                    for (int i = 0; i < SUB_DEPTH; ++i) metas[i] = 0u;
+#pragma unroll
+                    for (int i = 0; i < SUB_DEPTH - 1; ++i) {
+                        if (i < n_chunk) fetch(i, i, metas[i]);
+                        cp_async_commit();
                     }
-#pragma unroll
-                    for (int i = 0; i < SUB_DEPTH - 1; ++i)
-                        if (i < n_chunk) fetch(st[i], i);
                     for (int r = 0; r < n_chunk; r += SUB_DEPTH) {
 #pragma unroll
                         for (int i = 0; i < SUB_DEPTH; ++i) {
                             if (r + i < n_chunk) {
-                                if (r + i + SUB_DEPTH - 1 < n_chunk) fetch(st[(i + SUB_DEPTH - 1) % SUB_DEPTH], r + i + SUB_DEPTH - 1);
-                                apply(st[i]);
+                                const int nxt = (i + SUB_DEPTH - 1) % SUB_DEPTH;
+                                if (r + i + SUB_DEPTH - 1 < n_chunk) fetch(nxt, r + i + SUB_DEPTH - 1, metas[nxt]);
+                                cp_async_commit();
+                                cp_async_wait<SUB_DEPTH - 1>();
+                                apply(i, metas[i]);
                             }
                         }
                     }
+                    cp_async_wait<0>();   // (only empty groups can be left)
                 }
             }
             if constexpr (SAMPLE) {
@@ -1132,11 +1119,11 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
         s2 = s3;
         s3 = sub_of(x3);
         g0 = g1;
-        n0 = n1;
+        h0 = h1;
         g1 = g2;
-        n1 = n2;
+        h1 = h2;
         tau0 = tau1;
-        bounds_of(s2, t3, g2, n2);
+        bounds_of(s2, t3, g2, h2);
         tau1 = s1 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
         t3 = term_of(x3, s3, 0);
     }
