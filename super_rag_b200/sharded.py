@@ -117,6 +117,12 @@ class ShardedVectorIndex:
         self._bufs = {}     # (B, k) -> (send keys [B,k], gathered keys [g,B,k])
         self._graphs = {}   # (B, k) -> (graph, static q_bf16, static q_scale, out scores, out ids)
 
+    def close(self) -> None:
+        """Drop the captured CUDA graphs (they hold NCCL work: destroy_process_group() hangs while one is alive)."""
+        if self._graphs:
+            torch.cuda.synchronize(self.rows.device)
+            self._graphs.clear()
+
     def local_topk(self, q_bf16: torch.Tensor, q_scale: torch.Tensor, k: int, out_keys: Optional[torch.Tensor] = None):
         capturing = torch.cuda.is_current_stream_capturing()
         with self._lock:

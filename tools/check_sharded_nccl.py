@@ -23,6 +23,11 @@ from super_rag_b200.sharded import (ShardedBm25Index, ShardedVectorIndex, exchan
                                     shard_range)
 
 
+def mark(rank, what):
+    if rank == 0:
+        print(f"[check_sharded_nccl] {what}", flush=True)
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
@@ -57,6 +62,9 @@ def main():
     gs3, gi3 = index_g.search_batch(Q, k)
     torch.cuda.synchronize()
     graph_used = index_g.use_graph and len(index_g._graphs) == 1
+    index_g.close()     # captured NCCL work must be gone before destroy_process_group() (it hangs otherwise)
+    del index_g
+    mark(rank, f"vector paths done (graph captured: {graph_used})")
     ok_g = bool(torch.equal(gi1, fi)) and bool(torch.equal(gs1.view(torch.int32), fs.view(torch.int32))) and \
         bool(torch.equal(gi2, fi.flip(0))) and bool(torch.equal(gi3, fi)) and bool(torch.equal(gs3.view(torch.int32), fs.view(torch.int32)))
     ok_v = ok_v and ok_g
@@ -88,6 +96,7 @@ def main():
     torch.cuda.synchronize()
     ok_b = bool(torch.equal(mi, wi)) and bool(torch.equal(ms.view(torch.int32), ws.view(torch.int32)))
 
+    mark(rank, "bm25 shards done")
     # the ShardedBm25Index wrapper and the hybrid (vector + BM25 -> RRF) path == the single-GPU pipeline
     sb = ShardedBm25Index.from_tokens(torch.from_numpy(tokens).to(dev), torch.from_numpy(doc_ptr).to(dev), vocab, n_docs,
                                       stats, rank, world)
@@ -121,6 +130,7 @@ def main():
     torch.cuda.synchronize()
     ok_b = ok_b and bool(torch.equal(bi_, wi_)) and bool(torch.equal(bs_.view(torch.int32), ws_.view(torch.int32)))
 
+    mark(rank, "hybrid and two-pass bm25 shards done")
     flags = torch.tensor([int(ok_v), int(ok_b)], device=dev)
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
