@@ -108,15 +108,17 @@ def make_queries(n_q, terms_per_q, dev, lo_rank=101, seed=4):
 
 
 def torch_restatement(idx, terms, k):
-    if getattr(idx, "_doc_cache", None) is None:       # the searched layout holds 16-bit offsets: unpack the ids once
-        idx._doc_cache = idx.post_doc
-    post_doc = idx._doc_cache
+    """Independent torch scorer over the CANONICAL postings (term_ptr indexes those; the searched arrays are padded and
+    bank-ordered): index_add in ascending term order == the kernel's summation order."""
+    if getattr(idx, "_canon_cache", None) is None:
+        idx._canon_cache = idx.canonical_postings()
+    post_doc, post_imp = idx._canon_cache
     acc = torch.zeros(idx.n_docs, dtype=torch.float32, device=idx.device)
     hit = torch.zeros(idx.n_docs, dtype=torch.bool, device=idx.device)
     for t in sorted(set(int(x) for x in terms if x >= 0)):
         a, b = int(idx.term_ptr[t].item()), int(idx.term_ptr[t + 1].item())
         d = post_doc[a:b].to(torch.int64)
-        acc[d] = acc[d] + idx.post_imp[a:b]          # unique docs inside a term: one add per doc, fixed order
+        acc[d] = acc[d] + post_imp[a:b]              # unique docs inside a term: one add per doc, fixed order
         hit[d] = True
     key = torch.where(hit, acc, torch.full_like(acc, -1.0))
     s, i = torch.sort(key, descending=True, stable=True)   # stable: equal scores keep ascending doc id
