@@ -92,6 +92,23 @@ int srag_topk_search_keys(const void* corpus_bf16, const float* row_scale, int64
                           int64_t id_base, uint64_t* out_keys, float* out_scores, int64_t* out_ids,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same scan for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). It has NO COUNTERPART IN THE REFERENCE.
+ * Identical to the plain search entry point above except that the scratch memory (per-thread heaps, shared
+ * thresholds, pacing counters, the zero-padded query copy) is a file-scope `static __device__` array inside the library of
+ * SRAG_TOPK_STATIC_SCRATCH_BYTES bytes — every GPU that loads the library holds that much until the process exits — so the
+ * call needs no workspace and makes no cudaMalloc / cudaFree / allocating library call (the array's device address is
+ * looked up once per device with cudaGetSymbolAddress). A search whose scratch need (what srag_topk_workspace_bytes
+ * reports) exceeds the array is rejected with SRAG_E_WORKSPACE and a message that names both sizes: 8 MiB covers
+ * n_queries <= 1024 at k <= 10 over any corpus size (5.9 MiB), or k <= 16 at n_queries <= 512; larger k needs the caller-
+ * workspace entry point. ALL calls on a device share the one array and it keeps the last call's contents: every call
+ * clears the part it uses on `stream` before the scan, and two calls that overlap on the GPU (different streams, or
+ * different host threads) RACE — serialise them.                                                                        */
+#define SRAG_TOPK_STATIC_SCRATCH_BYTES (8u << 20)
+int srag_topk_search_static(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                            const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                            int64_t id_base, float* out_scores, int64_t* out_ids, void* stream);
+
 /* Same scan with the metadata pre-filter the reference BUILDS but its connector drops
  * (ContextManager._create_combined_filter, super_rag/context/context.py:74-111;
  * seekdb_connector.py:99-100): row r is eligible for query b iff

@@ -29,6 +29,7 @@ SIGNATURES = {
     "srag_topk_workspace_bytes_ex": [_i64, _i32, _i32, _i32, C.POINTER(_sz)],
     "srag_topk_search": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _sz, _vp],
     "srag_topk_search_keys": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _sz, _vp],
+    "srag_topk_search_static": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp],
     "srag_topk_search_filtered": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                   _sz, _vp],
     "srag_mmr_rerank": [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp, _i32, _i64, _f32, _f32, _vp, _vp, _vp],

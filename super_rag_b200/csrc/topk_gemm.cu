@@ -993,6 +993,54 @@ extern "C" int srag_topk_search_keys(const void* corpus_bf16, const float* row_s
                             nullptr, nullptr, nullptr, out_scores, out_ids, out_keys, workspace, workspace_bytes, stream);
 }
 
+// ---------------------------------------------------------------------------------------
+// srag_topk_search_static: the same scan with its scratch in a file-scope device array, for callers that may not
+// allocate (include/srag_b200.h). In host code `g_topk_static_scratch` is only a host-side stand-in for the symbol: its
+// DEVICE address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_topk_static_scratch[SRAG_TOPK_STATIC_SCRATCH_BYTES];
+
+static int topk_static_scratch_ptr(void** out) {
+    constexpr int MAX_DEVICES = 64;
+    static std::mutex mu;
+    static void* ptrs[MAX_DEVICES] = {};
+    int dev = 0;
+    SRAG_CUDA(cudaGetDevice(&dev));
+    SRAG_CHECK_ARG(dev >= 0 && dev < MAX_DEVICES, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        SRAG_CUDA(cudaGetSymbolAddress(&p, g_topk_static_scratch));
+        SRAG_CHECK_ARG(p != nullptr && ((uintptr_t)p & 255) == 0, "static scratch has no usable device address");
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return SRAG_OK;
+}
+
+extern "C" int srag_topk_search_static(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
+                                       const void* queries_bf16, const float* q_scale, int n_queries, int k,
+                                       int64_t id_base, float* out_scores, int64_t* out_ids, void* stream) {
+    SRAG_CHECK_ARG(out_scores && out_ids, "null pointer argument");
+    size_t need = 0;
+    int rc = srag_topk_workspace_bytes(n_rows, n_queries, k, &need);   // validates n_queries / k / n_rows as well
+    if (rc) return rc;
+    if (need > (size_t)SRAG_TOPK_STATIC_SCRATCH_BYTES) {
+        srag_set_error("srag_topk_search_static: n_queries=%d k=%d needs %zu bytes of scratch, the static array holds %zu "
+                       "(SRAG_TOPK_STATIC_SCRATCH_BYTES); use srag_topk_search with a caller workspace",
+                       n_queries, k, need, (size_t)SRAG_TOPK_STATIC_SCRATCH_BYTES);
+        return SRAG_E_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    rc = topk_static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    // the impl clears (cudaMemsetAsync on `stream`) the heaps, thresholds and counters it uses before the scan, so the last
+    // call's contents never leak into this one; the padded query copy is used when it still fits behind them
+    return topk_search_impl(corpus_bf16, row_scale, n_rows, dim, queries_bf16, q_scale, n_queries, k, id_base, nullptr,
+                            nullptr, nullptr, nullptr, out_scores, out_ids, nullptr, scratch,
+                            (size_t)SRAG_TOPK_STATIC_SCRATCH_BYTES, stream);
+}
+
 extern "C" int srag_topk_search_filtered(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
                                          const void* queries_bf16, const float* q_scale, int n_queries, int k,
                                          int64_t id_base, const uint32_t* row_tags, const int32_t* row_group,

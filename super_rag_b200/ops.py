@@ -154,6 +154,32 @@ def topk_search(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Te
     return scores, ids
 
 
+TOPK_STATIC_SCRATCH_BYTES = 8 << 20
+
+
+def topk_search_static(corpus: torch.Tensor, row_scale: torch.Tensor, queries: torch.Tensor, q_scale: torch.Tensor, k: int,
+                       out_scores: torch.Tensor, out_ids: torch.Tensor, id_base: int = 0) -> None:
+    """srag_topk_search_static: the exact top-k scan with the library's own static device scratch (8 MiB) — no workspace,
+    no device allocation anywhere in the call (this wrapper allocates nothing either: the caller passes the outputs).
+    No counterpart in the reference. Calls on one device share the scratch:
+    do not overlap them on the GPU. Raises SragError when the search needs more scratch than the array holds."""
+    _need_cuda(corpus, row_scale, queries, q_scale, out_scores, out_ids)
+    if corpus.dtype != torch.bfloat16 or queries.dtype != torch.bfloat16:
+        raise SragError("corpus and queries must be bfloat16 (use ingest_rows)")
+    B, D = queries.shape
+    if out_scores.dtype != torch.float32 or out_ids.dtype != torch.int64 or tuple(out_scores.shape) != (B, k) or \
+            tuple(out_ids.shape) != (B, k) or not out_scores.is_contiguous() or not out_ids.is_contiguous():
+        raise SragError("out_scores fp32 [B, k] and out_ids int64 [B, k], contiguous")
+    N = corpus.shape[0]
+    if N and corpus.shape[1] != D:
+        raise SragError(f"dimension mismatch: corpus {tuple(corpus.shape)} vs queries {tuple(queries.shape)}")
+    dev = queries.device
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().srag_topk_search_static(_ptr(corpus), _ptr(row_scale), N, D, _ptr(queries), _ptr(q_scale), B, k,
+                                                       id_base, _ptr(out_scores), _ptr(out_ids), _stream(dev)),
+                   "srag_topk_search_static")
+
+
 def prof_enable(on: bool):
     _lib.check(_lib.load().srag_prof_enable(1 if on else 0), "srag_prof_enable")
 
