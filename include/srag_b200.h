@@ -134,11 +134,11 @@ int srag_prof_read(double* main_ms_sum, double* finalize_ms_sum, int* n_calls);
  * (super_rag/nodeflow/runners/merge.py:18-20, super_rag/schema/view_models.py:1043-1047).
  * Index layout (CSR by term). While it is BUILT: term_ptr int64 [vocab+1], post_doc int32 [nnz] ascending inside a
  * term, post_tf int32 [nnz], block_ptr int64 [vocab, n_sub+1]. As it is SEARCHED (srag_bm25_pack_plan / _fill):
- *   slice_ptr uint32 [vocab, n_sub+1]  start of every (term, 2048-document sub-block) slice in GROUPS of 4 postings: every
+ *   slice_ptr uint32 [vocab, n_sub+1]  start of every (term, 2048-document sub-block) slice in GROUPS of 8 postings: every
  *                                      slice starts on a group and is padded to whole groups with zero-impact postings;
- *   post_off  uint16 [4 * groups]      (doc & 16383) * 4 = byte offset of the document's fp32 accumulator inside the tile
+ *   post_off  uint16 [8 * groups]      (doc & 16383) * 4 = byte offset of the document's fp32 accumulator inside the tile
  *                                      of its 16384-document block (the slice names the block); padding: a trash offset;
- *   post_imp  fp32   [4 * groups]      impact (> 0; exactly 0 marks padding)
+ *   post_imp  fp32   [8 * groups]      impact (> 0; exactly 0 marks padding)
  * = 6 bytes per posting in HBM. Both arrays are padded by 8 entries. Numeric contract: oracle/bm25.py docstring.
  *
  * srag_bm25_impacts: imp = idf[term] * tf*(k1+1) / (tf + k1*(1-b+b*dl/avgdl)), one IEEE
@@ -155,7 +155,7 @@ int srag_bm25_block_docs(void);   /* doc-range width one CTA accumulates in shar
 /* Index-build steps after srag_bm25_block_index: canonical postings -> the searched layout.
  *   srag_bm25_pack_plan: slice_ptr from block_ptr (three small kernels: per-term group counts, a scan over the
  *     vocabulary, a scan along every term). scratch int64 [2 * vocab + 1] (device); afterwards scratch[2 * vocab] is the
- *     total number of groups (the caller reads it back to size post_off / post_imp = 4 * groups + 8 entries).
+ *     total number of groups (the caller reads it back to size post_off / post_imp = 8 * groups + 8 entries).
  *   srag_bm25_pack_fill: writes post_off / post_imp. With permute != 0 the postings INSIDE every slice are laid out so that
  *     the 32 accumulators one warp of the scoring kernel touches per shared-memory access fall on distinct banks where
  *     the slice allows it (every posting of a slice is a distinct document that receives one add per query, so scores
@@ -165,7 +165,7 @@ int srag_bm25_pack_plan(const int64_t* block_ptr, int vocab, int64_t n_docs, int
 int srag_bm25_pack_fill(const int64_t* block_ptr, const uint32_t* slice_ptr, int vocab, int64_t n_docs,
                         const int32_t* doc_in, const float* imp_in, uint16_t* off_out, float* imp_out, int permute,
                         void* stream);
-/* The inverse: doc_out int32 [4 * groups] = document of every stored posting (-1 for padding), term_out (may be NULL) its
+/* The inverse: doc_out int32 [8 * groups] = document of every stored posting (-1 for padding), term_out (may be NULL) its
  * term. Not on the search path: tests, canonical postings, shard conversion.                                      */
 int srag_bm25_unpack_docs(const uint32_t* slice_ptr, int vocab, int64_t n_docs, const uint16_t* post_off,
                           const float* post_imp, int32_t* doc_out, int32_t* term_out, void* stream);

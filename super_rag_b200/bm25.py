@@ -52,7 +52,7 @@ class Bm25Stats:
 
 class Bm25Index:
     """CSR-by-term postings as they are SEARCHED, all on one GPU:
-      slice_ptr  [V, n_sub+1] (uint32 patterns)  start of every (term, 2048-document sub-block) slice, in groups of 4 postings
+      slice_ptr  [V, n_sub+1] (uint32 patterns)  start of every (term, 2048-document sub-block) slice, in groups of 8 postings
       post_off   (uint16 patterns)              byte offset of the document's accumulator inside its 16384-document block's tile
       post_imp   fp32                           impact; 0 marks the padding that rounds every slice up to whole groups
     = 6 bytes per posting. term_ptr (int64 [V+1]) keeps the REAL document frequencies (df = diff). The int32 document ids
@@ -142,7 +142,7 @@ class Bm25Index:
         """The searched arrays are written as they are (no rebuild on load)."""
         from . import shardio
         meta = {"n_docs": self.n_docs, "vocab": self.vocab, "id_base": self.id_base, "stats_n_docs": self.stats.n_docs,
-                "avgdl": float(self.stats.avgdl), "bank_ordered": bool(self.bank_ordered), "layout": "slices-v2",
+                "avgdl": float(self.stats.avgdl), "bank_ordered": bool(self.bank_ordered), "layout": "slices-v3",
                 "sub_docs": ops.bm25_block_docs(), "abi": 2}
         shardio.write_shard(path, "bm25", meta, {
             "term_ptr": self.term_ptr, "slice_ptr": self.slice_ptr, "post_off": self.post_off, "post_imp": self.post_imp,
@@ -161,10 +161,10 @@ class Bm25Index:
         stats = Bm25Stats(n_docs=int(meta["stats_n_docs"]), df=a["df"].cpu().numpy().astype(np.int64),
                           avgdl=float(meta["avgdl"]))
         term_ptr = a["term_ptr"]
-        if meta.get("layout") == "slices-v2" and int(meta.get("sub_docs", 0)) == ops.bm25_block_docs():
+        if meta.get("layout") == "slices-v3" and int(meta.get("sub_docs", 0)) == ops.bm25_block_docs():
             n = a["post_off"].numel()
             n_sub = max(1, -(-n_docs // ops.bm25_block_docs()))
-            if a["post_imp"].numel() != n or tuple(a["slice_ptr"].shape) != (vocab, n_sub + 1) or n % 4:
+            if a["post_imp"].numel() != n or tuple(a["slice_ptr"].shape) != (vocab, n_sub + 1) or n % 8:
                 raise shardio.ShardError(f"{path}: sections do not match the header")
             po = torch.zeros(n + ops.BM25_PAD, dtype=torch.int16, device=dev)
             pi = torch.zeros(n + ops.BM25_PAD, dtype=torch.float32, device=dev)

@@ -39,6 +39,10 @@ constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 ac
 // Index granularity: block_ptr holds one offset per (term, BM25_SUB_DOCS documents). A tile of bm25_items_kernel is
 // BM25_SUBS consecutive sub-blocks; bm25_sub_kernel gives one sub-block to one warp.
 constexpr int BM25_SUB_DOCS = 2048;
+// Slices of the searched layout start on, and are padded to, whole GROUPS of BM25_GROUP postings (16 bytes of 16-bit
+// offsets, 32 bytes of impacts: the unit of a bulk copy); slice_ptr counts groups.
+constexpr int BM25_GROUP = 8;
+constexpr int BM25_GROUP_LOG = 3;
 constexpr int BM25_SUBS = BM25_BLOCK_DOCS / BM25_SUB_DOCS;
 constexpr int BM25_THREADS = 32 * SRAG_BM25_WARPS;  // consumer threads
 constexpr int RADIX_BINS = 2048;
@@ -325,7 +329,7 @@ struct Bm25Filter {  // metadata pre-filter, same rule as K1 (srag_topk_search_f
 
 template <bool FILT>  // FILT: the unfiltered instantiation carries none of the filter code
 __global__ void __launch_bounds__(BM25_CTA_THREADS, BM25_CTAS_PER_SM)
-bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], groups of 4 postings */,
+bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], groups of 8 postings */,
                   const uint16_t* __restrict__ post_doc,
                   const float* __restrict__ post_imp, int n_blocks, int n_sub, const int32_t* __restrict__ q_terms,
                   int max_terms, int k, int q_offset, int nq, int phase, int stride,
@@ -380,8 +384,8 @@ bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], 
             if (p.ql < nq && t >= 0) {
                 const int s0 = block_of(p.j) * BM25_SUBS;  // the tile = sub-blocks s0 .. s0 + BM25_SUBS - 1
                 const uint32_t* sp = slice_ptr + (size_t)t * (n_sub + 1);
-                lo = (int64_t)__ldg(sp + s0) << 2;
-                hi = (int64_t)__ldg(sp + (s0 + BM25_SUBS < n_sub ? s0 + BM25_SUBS : n_sub)) << 2;
+                lo = (int64_t)__ldg(sp + s0) << BM25_GROUP_LOG;
+                hi = (int64_t)__ldg(sp + (s0 + BM25_SUBS < n_sub ? s0 + BM25_SUBS : n_sub)) << BM25_GROUP_LOG;
             }
         };
         // The two producer warps take ALTERNATE items of the CTA's list: planning an item (slice lookup, scans,
@@ -687,7 +691,7 @@ bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], 
         if (lane == 0) ptx::mbar_arrive(&sm->empty[slot]);  // the slot's data is in registers: hand it back
         if (active && !(debug & 1)) {
             const int32_t doc_base = cur_blk * BM25_BLOCK_DOCS;
-            // (slices are padded to whole groups of 4 with zero-impact postings whose offsets only mean something to
+            // (slices are padded to whole groups of 8 with zero-impact postings whose offsets only mean something to
             // bm25_sub_kernel: skipped here — a real impact is > 0)
             const bool m0 = rel >= m.lo_rel && rel < m.hi_rel && ww.x != 0.f, m1 = rel + 1 >= m.lo_rel && rel + 1 < m.hi_rel && ww.y != 0.f;
             const bool m2 = rel + 2 >= m.lo_rel && rel + 2 < m.hi_rel && ww.z != 0.f, m3 = rel + 3 >= m.lo_rel && rel + 3 < m.hi_rel && ww.w != 0.f;
@@ -730,7 +734,7 @@ bm25_items_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], 
 //   * lane u holds the bounds of query term u inside the sub-block (slice_ptr), fetched two items ahead (term ids three
 //     ahead), so no dependent load is waited for;
 //   * a round = up to 128 postings of one term: 8 bytes of offsets + 16 bytes of impacts per lane. Slices start on a
-//     group of 4 postings and are padded to whole groups (padding adds +0.0 to a trash slot), so a round has no masks;
+//     group of 8 postings and are padded to whole groups (padding adds +0.0 to a trash slot), so a round has no masks;
 //     the rounds of all terms form one stream in ascending-term order. The stream is described 32 rounds at a time —
 //     lane i works out where round i starts and how long it is by bisection in the running totals, ONCE per chunk — and
 //     the round loop only broadcasts two words per round;
@@ -762,9 +766,19 @@ constexpr int SUB_WARPS = SRAG_BM25_SUB_WARPS;   // warps per CTA (one CTA per S
 // (round 1's register-staged loads needed it: 12.97 ms without, 10.97 ms with).
 constexpr int SUB_PF = SRAG_BM25_PF;
 constexpr int SUB_CAND = 64;
+#ifndef SRAG_BM25_STAGE_TMA
+#define SRAG_BM25_STAGE_TMA 0
+#endif
+// How a round's postings travel global -> shared: 0 (default) = cp.async (LDGSTS) per lane with wait_group; 1 = two 1-D
+// bulk copies (cp.async.bulk, TMA) issued by one lane and tracked by an mbarrier per stage. The kernel's busiest unit is
+// the SM's LSU data pipe (ncu, C3: 70 % of its wavefront slots — per 128-posting round ~11.7 accumulator reads + writes at
+// the bank-conflict floor max_b count(b), ~4.2 stage reads, ~6 LDGSTS writes, ~5.2 zeroing); bulk copies bypass it for
+// the writes (Mem Busy 76 % -> 55 %), but 256 / 512-byte copies are too small for the TMA path and the one-lane issue
+// block + try_wait loop add instructions: C3 12.3 ms against 9.86 ms with LDGSTS. Kept selectable for A/B runs.
+constexpr bool SUB_STAGE_TMA = SRAG_BM25_STAGE_TMA != 0;
 
 // One warp's accumulators with a trash slot on either side, and the staging buffers of its round pipeline.
-// Slices are padded to whole groups of 4 postings; a padding posting carries impact +0.0 and an offset that lands on a
+// Slices are padded to whole groups of 8 postings; a padding posting carries impact +0.0 and an offset that lands on a
 // trash slot of whichever warp processes it:
 //   sub-block 0 of a block: offset 8192 = the float right AFTER the warp's 2048 accumulators (acc_b = acc)
 //   sub-block m > 0:        offset m * 8192 - 4 = the float right BEFORE them (acc_b = acc - m * 8192 bytes)
@@ -778,8 +792,9 @@ struct SubWarpTile {
     float before[4];
     float acc[BM25_SUB_DOCS];
     float after[4];
-    float4 stage_imp[SUB_DEPTH][32];
-    uint2 stage_off[SUB_DEPTH][32];
+    alignas(16) float4 stage_imp[SUB_DEPTH][32];
+    alignas(16) uint2 stage_off[SUB_DEPTH][32];
+    alignas(8) uint64_t stage_bar[SUB_DEPTH];   // TMA staging: one mbarrier per stage (count 1 + transaction bytes)
 };
 __host__ __device__ constexpr uint32_t sub_trash_offset(int sub_in_block) {
     return sub_in_block == 0 ? (uint32_t)BM25_SUB_DOCS * 4u : (uint32_t)sub_in_block * (BM25_SUB_DOCS * 4u) - 4u;
@@ -826,7 +841,7 @@ __device__ __noinline__ void sub_record_filtered(uint32_t* cand_count, uint16_t*
 // otherwise the MAIN pass (documents crossing tau are recorded by the add that takes them across).
 template <bool FILT, bool SAMPLE>
 __global__ void __launch_bounds__(32 * SUB_WARPS, 1)
-bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in groups of 4 postings */,
+bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in groups of 8 postings */,
                 const uint16_t* __restrict__ post_off, const float* __restrict__ post_imp, int n_blocks, int n_sub,
                 const int32_t* __restrict__ q_terms, int max_terms, int k, int q_offset, int nq, int stride,
                 const float* __restrict__ tau /* [nq][k], main pass */,
@@ -853,7 +868,14 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
     if (lane == 0) {  // the trash slots only ever receive +0.0
         sm->tile[w].before[3] = 0.f;
         sm->tile[w].after[0] = 0.f;
+        if constexpr (SUB_STAGE_TMA) {
+#pragma unroll
+            for (int i = 0; i < SUB_DEPTH; ++i) ptx::mbar_init(&sm->tile[w].stage_bar[i], 1);
+            ptx::fence_mbar_init();
+        }
     }
+    __syncwarp();
+    uint32_t stage_phase = 0;   // TMA staging: bit i = parity the next wait on stage i expects
 
     // Items of this warp: first, first + step, ... as (query, j-th sub-block of the pass); stepping is an add with carry.
     struct Item { int q, j; };
@@ -873,7 +895,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
         if (sub < 0 || j0 + lane >= max_terms) return -1;
         return __ldg(q_terms + (size_t)(q_offset + x.q) * max_terms + j0 + lane);
     };
-    // first and one-past-last group of 4 postings of the slice; kept RAW (the length is only formed where it is used, an
+    // first and one-past-last group of 8 postings of the slice; kept RAW (the length is only formed where it is used, an
     // item later: a subtraction right behind the loads would wait for them)
     auto bounds_of = [&](int sub, int32_t t, uint32_t& g_lo, uint32_t& g_hi) {
         g_lo = 0;
@@ -895,7 +917,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
     Item x1 = advance(x0), x2 = advance(x1), x3 = advance(x2);
     int s0 = sub_of(x0), s1 = sub_of(x1), s2 = sub_of(x2), s3 = sub_of(x3);
     int32_t t3 = term_of(x3, s3, 0);
-    uint32_t g0, g1, g2;   // slice starts, in groups of 4 postings
+    uint32_t g0, g1, g2;   // slice starts, in groups of 8 postings
     uint32_t h0, h1, h2;   // slice ends (exclusive), in groups
     bounds_of(s0, term_of(x0, s0, 0), g0, h0);
     bounds_of(s1, term_of(x1, s1, 0), g1, h1);
@@ -924,10 +946,10 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                 // instead of HBM latency, and nothing has to be held in registers meanwhile. Lane group pf_term looks
                 // after term pf_term, its lanes take every (1 << lpt_log)-th line.
                 const uint32_t g_p = __shfl_sync(FULL, SUB_PF == 2 ? g2 : g1, pf_term);
-                const uint32_t n_p = (__shfl_sync(FULL, SUB_PF == 2 ? h2 : h1, pf_term) - g_p) << 2;
+                const uint32_t n_p = (__shfl_sync(FULL, SUB_PF == 2 ? h2 : h1, pf_term) - g_p) << BM25_GROUP_LOG;
                 if (n_p > 0) {
-                    const char* po = reinterpret_cast<const char*>(post_off) + (size_t)g_p * 8u;
-                    const char* pi = reinterpret_cast<const char*>(post_imp) + (size_t)g_p * 16u;
+                    const char* po = reinterpret_cast<const char*>(post_off) + (size_t)g_p * (BM25_GROUP * 2u);
+                    const char* pi = reinterpret_cast<const char*>(post_imp) + (size_t)g_p * (BM25_GROUP * 4u);
                     const int bytes_o = (int)n_p * 2 + (int)(reinterpret_cast<uintptr_t>(po) & 127);
                     const int bytes_i = (int)n_p * 4 + (int)(reinterpret_cast<uintptr_t>(pi) & 127);
                     po -= reinterpret_cast<uintptr_t>(po) & 127;
@@ -948,7 +970,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                 if (j0 > 0) bounds_of(s0, term_of(x0, s0, j0), g0, h0);  // queries with more than 32 terms: fetched in line
                 // lane u = term j0 + u: its rounds of up to 128 postings and the running total over the terms (ascending
                 // term id = lane order)
-                const uint32_t n_l = (h0 - g0) << 2;   // postings of the (padded) slice, a multiple of 4
+                const uint32_t n_l = (h0 - g0) << BM25_GROUP_LOG;   // postings of the (padded) slice, a multiple of 8
                 const uint32_t cnt = (n_l + 127u) >> 7;
                 uint32_t incl = cnt;
 #pragma unroll
@@ -981,7 +1003,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                     const uint32_t incl_u = __shfl_sync(FULL, incl, u), cnt_u = __shfl_sync(FULL, cnt, u);
                     const uint32_t g0_u = __shfl_sync(FULL, g0, u), n_u = __shfl_sync(FULL, n_l, u);
                     const uint32_t r_in = g - (incl_u - cnt_u);            // round inside its term
-                    const uint32_t d_grp = g0_u + (r_in << 5);             // first group of 4 postings of the round
+                    const uint32_t d_grp = g0_u + (r_in << (7 - BM25_GROUP_LOG));   // first group of 8 postings of the round
                     const uint32_t left = n_u - (r_in << 7);
                     const uint32_t d_meta = (left < 128u ? left : 128u) | (r_in == 0 ? STAGE_NEW_TERM : 0u);
                     const int n_chunk = (int)(rounds - base < 32u ? rounds - base : 32u);
@@ -991,13 +1013,28 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                         const uint32_t grp = __shfl_sync(FULL, d_grp, r);
                         const uint32_t meta = __shfl_sync(FULL, d_meta, r);
                         meta_out = meta;
-                        if (4u * (uint32_t)lane < (meta & 0xFFu)) {
-                            const size_t p = ((size_t)grp + (uint32_t)lane) * 4u;
+                        if constexpr (SUB_STAGE_TMA) {
+                            // every lane has read this stage's previous contents (apply() of SUB_DEPTH - 1 rounds ago)
+                            __syncwarp();
+                            if (lane == 0) {
+                                const uint32_t count = meta & 0xFFu;   // a multiple of 8: 16 / 32-byte granules
+                                const size_t p = (size_t)grp * BM25_GROUP;
+                                uint64_t* bar = &tile->stage_bar[stage];
+                                ptx::mbar_arrive_expect_tx(bar, count * 6u);
+                                ptx::bulk_load_1d(&tile->stage_off[stage][0], post_off + p, count * 2u, bar);
+                                ptx::bulk_load_1d(&tile->stage_imp[stage][0], post_imp + p, count * 4u, bar);
+                            }
+                        } else if (4u * (uint32_t)lane < (meta & 0xFFu)) {
+                            const size_t p = (size_t)grp * BM25_GROUP + (uint32_t)lane * 4u;
                             cp_async_8(&tile->stage_off[stage][lane], post_off + p);
                             cp_async_16(&tile->stage_imp[stage][lane], post_imp + p);
                         }
                     };
                     auto apply = [&](int stage, uint32_t meta) {
+                        if constexpr (SUB_STAGE_TMA) {
+                            ptx::mbar_wait_lean(&tile->stage_bar[stage], (stage_phase >> stage) & 1u);
+                            stage_phase ^= 1u << stage;
+                        }
                         if (meta & STAGE_NEW_TERM) __syncwarp();  // the previous term's writes are visible to every lane
                         if (4u * (uint32_t)lane < (meta & 0xFFu)) {
                             // four postings per lane, no masks (padding postings add +0.0 to a trash slot)
@@ -1036,7 +1073,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
 #pragma unroll
                     for (int i = 0; i < SUB_DEPTH - 1; ++i) {
                         if (i < n_chunk) fetch(i, i, metas[i]);
-                        cp_async_commit();
+                        if constexpr (!SUB_STAGE_TMA) cp_async_commit();
                     }
                     for (int r = 0; r < n_chunk; r += SUB_DEPTH) {
 #pragma unroll
@@ -1044,13 +1081,15 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                             if (r + i < n_chunk) {
                                 const int nxt = (i + SUB_DEPTH - 1) % SUB_DEPTH;
                                 if (r + i + SUB_DEPTH - 1 < n_chunk) fetch(nxt, r + i + SUB_DEPTH - 1, metas[nxt]);
-                                cp_async_commit();
-                                cp_async_wait<SUB_DEPTH - 1>();
+                                if constexpr (!SUB_STAGE_TMA) {
+                                    cp_async_commit();
+                                    cp_async_wait<SUB_DEPTH - 1>();
+                                }
                                 apply(i, metas[i]);
                             }
                         }
                     }
-                    cp_async_wait<0>();   // (only empty groups can be left)
+                    if constexpr (!SUB_STAGE_TMA) cp_async_wait<0>();   // (only empty groups can be left)
                 }
             }
             if constexpr (SAMPLE) {
@@ -1182,7 +1221,7 @@ __global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, co
 // ---------------------------------------------------------------------------------------------------------
 // Packing (index build): canonical CSR postings (int32 documents ascending inside a term, fp32 impacts, block_ptr int64
 // [vocab][n_sub + 1]) -> the SEARCHED layout:
-//   * every (term, sub-block) slice starts on a group of 4 postings and is padded to whole groups with zero-impact
+//   * every (term, sub-block) slice starts on a group of 8 postings and is padded to whole groups with zero-impact
 //     postings that land on a trash slot (sub_trash_offset), so the scoring kernel loads 8 / 16 aligned bytes per lane
 //     and needs no mask anywhere; slice_ptr uint32 [vocab][n_sub + 1] holds the slice starts in GROUPS (so 2^32 groups =
 //     1.7e10 postings per shard);
@@ -1199,14 +1238,14 @@ __global__ void bm25_block_index_kernel(const int64_t* __restrict__ term_ptr, co
 // ---------------------------------------------------------------------------------------------------------
 constexpr int BANK_ORDER_WARPS = 8;
 
-// groups[t] = sum over the term's slices of ceil(n / 4)
+// groups[t] = sum over the term's slices of ceil(n / 8)
 __global__ void pack_row_sum_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_sub, int64_t* __restrict__ groups) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
     for (int64_t t = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < vocab; t += warps) {
         const int64_t* row = block_ptr + (size_t)t * (n_sub + 1);
         int64_t s = 0;
-        for (int j = lane; j < n_sub; j += 32) s += (__ldg(row + j + 1) - __ldg(row + j) + 3) >> 2;
+        for (int j = lane; j < n_sub; j += 32) s += (__ldg(row + j + 1) - __ldg(row + j) + (BM25_GROUP - 1)) >> BM25_GROUP_LOG;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
         if (lane == 0) groups[t] = s;
@@ -1241,7 +1280,7 @@ __global__ void __launch_bounds__(1024) pack_scan_terms_kernel(const int64_t* __
     }
 }
 
-// slice_ptr[t][j] = term_group[t] + sum_{j' < j} ceil(n_{t j'} / 4); [t][n_sub] = term_group[t + 1]
+// slice_ptr[t][j] = term_group[t] + sum_{j' < j} ceil(n_{t j'} / 8); [t][n_sub] = term_group[t + 1]
 __global__ void pack_row_scan_kernel(const int64_t* __restrict__ block_ptr, int vocab, int n_sub,
                                      const int64_t* __restrict__ term_group, uint32_t* __restrict__ slice_ptr) {
     const int lane = threadIdx.x & 31;
@@ -1252,7 +1291,7 @@ __global__ void pack_row_scan_kernel(const int64_t* __restrict__ block_ptr, int 
         int64_t carry = term_group[t];
         for (int base = 0; base <= n_sub; base += 32) {
             const int j = base + lane;
-            const int64_t v = j < n_sub ? (__ldg(row + j + 1) - __ldg(row + j) + 3) >> 2 : 0;
+            const int64_t v = j < n_sub ? (__ldg(row + j + 1) - __ldg(row + j) + (BM25_GROUP - 1)) >> BM25_GROUP_LOG : 0;
             int64_t inc = v;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -1284,7 +1323,7 @@ bm25_pack_fill_kernel(const int64_t* __restrict__ block_ptr, const uint32_t* __r
             const int64_t* bp = block_ptr + t * (n_sub + 1) + j;
             lo_l = __ldg(bp);
             hi_l = __ldg(bp + 1);
-            dst_l = (int64_t)__ldg(slice_ptr + t * (n_sub + 1) + j) << 2;
+            dst_l = (int64_t)__ldg(slice_ptr + t * (n_sub + 1) + j) << BM25_GROUP_LOG;
             sub_l = (int)(j & (BM25_SUBS - 1));
         }
         uint32_t todo = __ballot_sync(FULL, hi_l > lo_l);
@@ -1295,7 +1334,7 @@ bm25_pack_fill_kernel(const int64_t* __restrict__ block_ptr, const uint32_t* __r
             const int64_t a = __shfl_sync(FULL, dst_l, src);   // first position of the padded slice
             const int sub_in_block = __shfl_sync(FULL, sub_l, src);
             const int n = (int)(hi - lo);
-            const int n_pad = (n + 3) & ~3;
+            const int n_pad = (n + BM25_GROUP - 1) & ~(BM25_GROUP - 1);
             // padding: zero impact, offset = the trash slot of whichever warp scores this sub-block
             if (lane < n_pad - n) {
                 off_out[a + n + lane] = (uint16_t)sub_trash_offset(sub_in_block);
@@ -1371,8 +1410,8 @@ bm25_unpack_docs_kernel(const uint32_t* __restrict__ slice_ptr, int vocab, int n
         if (s0 + lane < n_slices) {
             const int64_t t = (s0 + lane) / n_sub, j = (s0 + lane) - t * n_sub;
             const uint32_t* sp = slice_ptr + t * (n_sub + 1) + j;
-            lo_l = (int64_t)__ldg(sp) << 2;
-            hi_l = (int64_t)__ldg(sp + 1) << 2;
+            lo_l = (int64_t)__ldg(sp) << BM25_GROUP_LOG;
+            hi_l = (int64_t)__ldg(sp + 1) << BM25_GROUP_LOG;
             base_l = (int32_t)(j / BM25_SUBS) * BM25_BLOCK_DOCS;
             term_l = (int32_t)t;
         }

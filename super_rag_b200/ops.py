@@ -274,7 +274,7 @@ BM25_PAD = 8   # entries of padding behind the searched posting arrays (bulk cop
 
 def bm25_pack(block_ptr, post_doc, post_imp, n_docs: int, permute: bool = True):
     """Canonical postings -> the searched layout (srag_bm25_pack_plan / _fill): every (term, sub-block) slice starts on a
-    group of 4 postings and is padded to whole groups with zero-impact postings, documents become 16-bit tile offsets and
+    group of 8 postings and is padded to whole groups with zero-impact postings, documents become 16-bit tile offsets and
     (permute) the postings of every slice are laid out for conflict-free shared-memory accumulation.
     Returns (slice_ptr int32-typed [V, n_sub+1] holding uint32 group indexes, post_off int16-typed (uint16 patterns),
     post_imp fp32), the two posting arrays padded behind their end; scores are unchanged. One host sync (the padded size)."""
@@ -289,8 +289,8 @@ def bm25_pack(block_ptr, post_doc, post_imp, n_docs: int, permute: bool = True):
         _lib.check(lib.srag_bm25_pack_plan(_ptr(block_ptr), vocab, n_docs, _ptr(scratch), _ptr(slice_ptr), st), "srag_bm25_pack_plan")
         groups = int(scratch[2 * vocab].item())
         if groups >= 1 << 32:
-            raise SragError(f"{groups} groups of 4 postings do not fit the 32-bit slice table: shard the index")
-        n_pad = 4 * groups
+            raise SragError(f"{groups} groups of 8 postings do not fit the 32-bit slice table: shard the index")
+        n_pad = 8 * groups
         po = torch.zeros(n_pad + BM25_PAD, dtype=torch.int16, device=dev)[:n_pad]
         pi = torch.zeros(n_pad + BM25_PAD, dtype=torch.float32, device=dev)[:n_pad]
         if post_doc.numel():

@@ -194,7 +194,7 @@ def test_bm25_two_phase_with_ties_at_the_threshold():
 
 
 def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
-    """The searched layout: every slice starts on a group of 4 postings, is padded to whole groups with zero-impact
+    """The searched layout: every slice starts on a group of 8 postings, is padded to whole groups with zero-impact
     postings (trash offsets), holds the same (doc, impact) pairs as the canonical slice, and — bank-ordered — is laid
     out as oracle/bank_order.py restates it."""
     import torch
@@ -212,9 +212,9 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
     imp = oracle.bm25_impacts(tp, pd, ptf, dl).view(np.uint32)
     d0, w0 = plain.post_doc.cpu().numpy(), plain.post_imp.cpu().numpy().view(np.uint32)
     d1, w1 = idx.post_doc.cpu().numpy(), idx.post_imp.cpu().numpy().view(np.uint32)
-    sp = idx.slice_ptr.cpu().numpy().view(np.uint32).astype(np.int64) * 4
-    assert (sp == plain.slice_ptr.cpu().numpy().view(np.uint32).astype(np.int64) * 4).all()
-    assert len(d1) == sp[-1, -1] and len(d1) % 4 == 0
+    sp = idx.slice_ptr.cpu().numpy().view(np.uint32).astype(np.int64) * 8
+    assert (sp == plain.slice_ptr.cpu().numpy().view(np.uint32).astype(np.int64) * 8).all()
+    assert len(d1) == sp[-1, -1] and len(d1) % 8 == 0
     # every slice: same pairs as the canonical postings of (term, sub-block), all inside the sub-block, padding = (-1, 0);
     # the layout itself is the one oracle/bank_order.py restates (checked on a sample of slices: it is a Python loop)
     from oracle import bank_order as bo
@@ -228,7 +228,7 @@ def test_bm25_bank_order_is_a_slice_permutation_and_cuts_conflicts(monkeypatch):
             sel = (docs_t // bd) == j
             a, wa = docs_t[sel], imps_t[sel]
             n = len(a)
-            assert hi - lo == (n + 3) // 4 * 4, (t, j)
+            assert hi - lo == (n + 7) // 8 * 8, (t, j)
             if n == 0:
                 continue
             b, wb = d1[lo:lo + n], w1[lo:lo + n]
