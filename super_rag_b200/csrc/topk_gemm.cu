@@ -89,6 +89,7 @@ struct TopkParams {
     int share_j;      // j = ceil(k / lists), 1..8; 0 = threshold sharing off
     int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
     int window;       // tiles the leader may run ahead of the slowest follower
+    int warm;         // warm-up tiles per list (0 = off): see "Warm-up" in the epilogue
     int debug;        // SRAG_TOPK_DEBUG perf-dissection bits (results are WRONG when set): 2 no MMA, 4 no epilogue work
     // metadata pre-filter (all null = off): a row is eligible for query q iff
     //   (row_tags == null  || (row_tags[row] & q_tag_mask[q]) != 0) &&
@@ -137,10 +138,41 @@ __device__ __noinline__ float heap_replace_root(uint64_t* heap, int k, uint32_t 
 }
 
 
+// While a list holds fewer than k keys it is only APPENDED to (slot count + 3: one store, no loads; the finalize kernel
+// reads every slot whatever its order). When the k-th key arrives the slots are turned into the heap above in place,
+// bottom-up, once. With threshold sharing most lists never fill (~j ln(n/j) pushes against k slots), so their pushes
+// never pay a sift. Returns the threshold (the root's score).
+__device__ __noinline__ float heap_build(uint64_t* heap, int k) {
+    for (int start = (k - 2) >> 2; start >= 0; --start) {
+        const uint64_t key = heap[start + 3];
+        int i = start;
+        for (;;) {
+            const int c0 = 4 * i + 1;
+            if (c0 >= k) break;
+            const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(heap + c0 + 3);
+            const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(heap + c0 + 5);
+            uint64_t kc = a.x;
+            int c = c0;
+            if (c0 + 1 < k && a.y < kc) { kc = a.y; c = c0 + 1; }
+            if (c0 + 2 < k && b.x < kc) { kc = b.x; c = c0 + 2; }
+            if (c0 + 3 < k && b.y < kc) { kc = b.y; c = c0 + 3; }
+            if (kc >= key) break;
+            heap[i + 3] = kc;
+            i = c;
+        }
+        heap[i + 3] = key;
+    }
+    const uint64_t root = heap[3];
+    return root == SRAG_KEY_EMPTY ? -INFINITY : __uint_as_float(srag_key_score_bits(root));
+}
+
 // ---------------------------------------------------------------------------------------
 // main kernel
 // ---------------------------------------------------------------------------------------
-template <int G, bool RQ, int EW, bool FILT = false>  // FILT: metadata pre-filter compiled into the push path
+// FILT: metadata pre-filter compiled into the push path. WARM: the warm-up pass (large k) compiled in — a template
+// parameter because merely carrying the run-time `warm` logic cost the HBM-bound plans 15-25 % (B = 128, k = 10: 3.7 ->
+// 4.8 ms on one box), like the run-time filter flag did in round 1.
+template <int G, bool RQ, int EW, bool FILT = false, bool WARM = false>
 __global__ void __launch_bounds__(64 + 32 * EW, 1)
 topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                  const TopkParams p) {
@@ -157,6 +189,12 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int num_kb = (p.dim + BLOCK_K - 1) / BLOCK_K;
     const int num_c_tiles = (int)((p.n_rows + BLOCK_N - 1) / BLOCK_N);
     const int q_row = (q_tile * G + (int)cta_rank) * BLOCK_M;  // first query of this CTA
+    // The unit's tile sequence: its first `warm` tiles once for the warm-up (epilogue: thresholds only), then ALL its
+    // tiles slab, slab + S, ... Producer, MMA issuer and epilogue walk the same sequence.
+    const int n_my = num_c_tiles > slab ? (num_c_tiles - slab + p.num_slabs - 1) / p.num_slabs : 0;
+    const int warm = WARM ? (p.warm < n_my ? p.warm : n_my) : 0;
+    const int n_iter = n_my + warm;
+    auto tile_of = [&](int it_) { return slab + (it_ < warm ? it_ : it_ - warm) * p.num_slabs; };
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* qres = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -218,8 +256,8 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         // follower. A hint only: waits are bounded, correctness never depends on them.
         volatile int* prog = p.progress ? p.progress + ((size_t)slab * 2 + cta_rank) * PROG_SLOTS : nullptr;
         const bool paced = prog != nullptr && p.num_q_tiles > 1 && p.num_q_tiles <= PROG_SLOTS;
-        int it = 0;
-        for (int c = slab; c < num_c_tiles; c += p.num_slabs, ++it) {
+        for (int it = 0; it < n_iter; ++it) {
+            const int c = tile_of(it);
             const int c_row = c * BLOCK_N + (int)cta_rank * C::B_ROWS;
             if (paced) {
                 uint32_t spins = 0;
@@ -274,8 +312,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const uint32_t ring_lo = (ptx::smem_u32(ring) & 0x3FFFFu) >> 4;
             const uint32_t qres_lo = (ptx::smem_u32(qres) & 0x3FFFFu) >> 4;
             uint32_t stage = 0, phase = 0;
-            int it = 0;
-            for (int c = slab; c < num_c_tiles; c += p.num_slabs, ++it) {
+            for (int it = 0; it < n_iter; ++it) {
                 const int buf = it & 1;
                 const uint32_t use = (uint32_t)(it >> 1);
                 ptx::mbar_wait(&tail->tmem_empty[buf], (use & 1) ^ 1);
@@ -376,6 +413,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int i = 0; i < 8; ++i) topj[i] = -INFINITY;
         float thr_own = -INFINITY, thr_shared = -INFINITY;
         uint32_t published = 0;
+        int heap_cnt = 0;   // WARM kernels: keys appended so far; == k: the list is a heap
         float thr = valid_q ? -INFINITY : INFINITY;
         // metadata pre-filter: checked only for the few scores that beat the running threshold
         constexpr bool filtered = FILT;  // a template parameter: the unfiltered kernel carries none of this
@@ -406,10 +444,19 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
         };
 
+        // Warm-up (k >= 32 with threshold sharing). With an empty heap every early row is a push, and a push at k = 100 is a
+        // sift of dependent L2 round trips: ~330 of a thread's ~370 pushes fell into its first four tiles, before the
+        // first shared threshold existed, and stalled the MMA pipe through tmem_empty (18.6 ms per batch at k = 100 against
+        // 15.7 ms at k = 10). So the first `warm` tiles are scanned TWICE: the first time only the j best scores are kept in
+        // registers (topj) and published; then every list waits (bounded) for the others' j-th best, and the real scan
+        // starts over from the first tile with T = min over lists already in place: ~j pushes for those tiles instead of
+        // ~k ln(rows / k). T is valid for the same reason as ever: it counts j DISTINCT rows per list (topj is cleared
+        // before the rescan, `published` only ever rises), so >= k rows overall score >= T.
+        bool warm_mode = WARM && warm > 0;
         float nxt[SPL];
-        if (slab < num_c_tiles) load_scales(slab, nxt);
-        int it = 0;
-        for (int c = slab; c < num_c_tiles; c += p.num_slabs, ++it) {
+        if (n_iter > 0) load_scales(tile_of(0), nxt);
+        for (int it = 0; it < n_iter; ++it) {
+            const int c = tile_of(it);
             const int buf = it & 1;
             const uint32_t use = (uint32_t)(it >> 1);
             __syncwarp();
@@ -431,13 +478,27 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 s_lo_l = fminf(s_lo_l, __shfl_xor_sync(0xFFFFFFFFu, s_lo_l, o));
             }
             __syncwarp();
-            if (c + p.num_slabs < num_c_tiles) load_scales(c + p.num_slabs, nxt);
+            if (it + 1 < n_iter) load_scales(tile_of(it + 1), nxt);
 
-            if (p.share_j > 0 && valid_q && (it & 3) == 0) {  // refresh the shared bound every 4th tile
-                uint32_t lo = 0xFFFFFFFFu;
-                const volatile uint32_t* gp = p.gthr + qx;
+            if (WARM && warm_mode && it == warm) {  // the warm-up is over: the real scan starts with an empty heap and empty topj
+                warm_mode = false;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) topj[i] = -INFINITY;
+                if (valid_q) thr = -INFINITY;
+            }
+            if (p.share_j > 0 && valid_q && !warm_mode && ((it - warm) & 3) == 0) {  // refresh the shared bound every 4th tile
+                // right after the warm-up: wait (bounded — a hint, never a correctness condition) until every list of
+                // this query has published
+                uint32_t spins = (warm > 0 && it == warm) ? 2048u : 1u;
+                uint32_t lo;
+                for (;;) {
+                    lo = 0xFFFFFFFFu;
+                    const volatile uint32_t* gp = p.gthr + qx;
 #pragma unroll 6
-                for (int l = 0; l < num_lists; ++l) lo = min(lo, gp[(size_t)l * p.n_queries]);
+                    for (int l = 0; l < num_lists; ++l) lo = min(lo, gp[(size_t)l * p.n_queries]);
+                    if (lo > 0x00800001u || --spins == 0u) break;
+                    __nanosleep(128);
+                }
                 if (lo > 0x00800001u) {  // every list has published something above -inf
                     thr_shared = __uint_as_float(srag_f32_from_orderable(lo - 2u));
                     thr = fmaxf(thr_own, thr_shared);
@@ -501,13 +562,33 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                                 if (sv[q * 8 + e] > thr && (!filtered || eligible(r0 + q * 8 + e)))
                                 {
                                     float v = sv[q * 8 + e];
-                                    thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
-                                    thr = fmaxf(thr_own, thr_shared);
+                                    if (!WARM || !warm_mode) {
+                                        if constexpr (WARM) {
+                                            // (only in the warm-up instantiations: in the plain kernels the extra branch and
+                                            // call site at each of the 64 unrolled push sites cost the HBM-bound plans 25 %
+                                            // — B = 128, k = 10: 3.9 -> 4.9 ms — for no gain at small k)
+                                            if (heap_cnt < p.k) {   // not full yet: append (the threshold stays where it is)
+                                                heap[heap_cnt + 3] = srag_pack_key(__float_as_uint(v), r0 + q * 8 + e);
+                                                if (++heap_cnt == p.k) thr_own = heap_build(heap, p.k);
+                                            } else {
+                                                thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
+                                            }
+                                        } else {
+                                            thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
+                                        }
+                                        thr = fmaxf(thr_own, thr_shared);
+                                    }
 #pragma unroll
                                     for (int i = 0; i < 8; ++i) {  // keep the 8 best scores sorted (descending)
                                         const float hi = fmaxf(topj[i], v);
                                         v = fminf(topj[i], v);
                                         topj[i] = hi;
+                                    }
+                                    if (WARM && warm_mode) {  // warm-up: only the j best matter; the filter is the j-th best so far
+                                        float tj = topj[0];
+#pragma unroll
+                                        for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
+                                        thr = tj;
                                     }
                                 }
                             }
@@ -603,7 +684,7 @@ topk_finalize_kernel(const uint64_t* __restrict__ partial, size_t src_stride, in
         const long long t = (long long)live_base + live_count[q];
         total = t < total_max ? (int)t : total_max;
     }
-    if (total > chunk || live_count) {
+    {
         // Sparse lists (K2 with a sample threshold leaves most block lists empty): compact the non-empty keys
         // in ONE pass; when they all fit, sort one small power of two instead of total/chunk passes.
         for (int i = threadIdx.x; i < P; i += blockDim.x) fin_keys[i] = SRAG_KEY_EMPTY;
@@ -796,11 +877,11 @@ int prof_claim() {
     return g_prof.n++;
 }
 
-template <int G, bool RQ, int EW, bool FILT = false>
+template <int G, bool RQ, int EW, bool FILT = false, bool WARM = false>
 int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, const TopkParams& prm,
                 cudaStream_t st) {
     {
-        const int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&topk_gemm_kernel<G, RQ, EW, FILT>),
+        const int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&topk_gemm_kernel<G, RQ, EW, FILT, WARM>),
                                             (int)smem_bytes<G, RQ>());
         if (rc) return rc;
     }
@@ -816,7 +897,7 @@ int launch_main(const Plan& pl, const CUtensorMap& tq, const CUtensorMap& tc, co
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    SRAG_CUDA(cudaLaunchKernelEx(&cfg, topk_gemm_kernel<G, RQ, EW, FILT>, tq, tc, prm));
+    SRAG_CUDA(cudaLaunchKernelEx(&cfg, topk_gemm_kernel<G, RQ, EW, FILT, WARM>, tq, tc, prm));
     return SRAG_OK;
 }
 
@@ -913,6 +994,9 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
         prm.share_j = (env_int("SRAG_TOPK_SHARE", 1) != 0 && lists >= 2 && worth && j <= 8) ? j : 0;
     }
     prm.window = pl.window;
+    // warm-up tiles (see the epilogue): only where a push is expensive (large k) and a shared threshold exists
+    prm.warm = (prm.share_j > 0 && k >= 32 && !rq && ew == 4) ? env_int("SRAG_TOPK_WARM", 8) : 0;
+    if (prm.warm < 0) prm.warm = 0;
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
     prm.row_tags = n_rows > 0 ? row_tags : nullptr;
     prm.row_group = n_rows > 0 ? row_group : nullptr;
@@ -949,15 +1033,21 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
                 srag_set_error("the metadata filter is not available with SRAG_TOPK_RQ / SRAG_TOPK_EPI_WARPS overrides");
                 return SRAG_E_INVALID;
             }
-            rc = pl.cta_group == 2 ? launch_main<2, false, 4, true>(pl, tq, tc, prm, st)
-                                   : launch_main<1, false, 4, true>(pl, tq, tc, prm, st);
+            if (prm.warm > 0)
+                rc = pl.cta_group == 2 ? launch_main<2, false, 4, true, true>(pl, tq, tc, prm, st)
+                                       : launch_main<1, false, 4, true, true>(pl, tq, tc, prm, st);
+            else
+                rc = pl.cta_group == 2 ? launch_main<2, false, 4, true>(pl, tq, tc, prm, st)
+                                       : launch_main<1, false, 4, true>(pl, tq, tc, prm, st);
         } else
         switch (sel) {
-            case 0: rc = launch_main<1, false, 4>(pl, tq, tc, prm, st); break;
+            case 0: rc = prm.warm > 0 ? launch_main<1, false, 4, false, true>(pl, tq, tc, prm, st)
+                                      : launch_main<1, false, 4>(pl, tq, tc, prm, st); break;
             case 1: rc = launch_main<1, false, 8>(pl, tq, tc, prm, st); break;
             case 2: rc = launch_main<1, true, 4>(pl, tq, tc, prm, st); break;
             case 3: rc = launch_main<1, true, 8>(pl, tq, tc, prm, st); break;
-            case 4: rc = launch_main<2, false, 4>(pl, tq, tc, prm, st); break;
+            case 4: rc = prm.warm > 0 ? launch_main<2, false, 4, false, true>(pl, tq, tc, prm, st)
+                                      : launch_main<2, false, 4>(pl, tq, tc, prm, st); break;
             case 5: rc = launch_main<2, false, 8>(pl, tq, tc, prm, st); break;
             case 6: rc = launch_main<2, true, 4>(pl, tq, tc, prm, st); break;
             default: rc = launch_main<2, true, 8>(pl, tq, tc, prm, st); break;
