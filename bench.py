@@ -469,6 +469,12 @@ def run_ours(args):
     ms_step = ms_total / args.steps
     value = B / (ms_step * 1e-3)
     graph_step = bool(getattr(index, "use_graph", False) and index._graphs)
+    exchange_kind = None
+    if world > 1:
+        exchange_kind = ("8-byte keys from the finalize kernel -> ONE kernel: P2P stores into every rank's symmetric buffer over "
+                         "NVLink + flags + merge (no collective call)" if getattr(index, "p2p", None) is not None else
+                         "8-byte keys from the finalize kernel -> NCCL all_gather -> merge_keys" if index.use_keys else
+                         "two int64 planes -> NCCL all_gather -> merge_candidates")
     if n_prof == 0:
         # the step ran as a CUDA graph replay (the library's timing events are not part of the graph): time the dominant
         # kernel on a few eager steps right after the timed region instead
@@ -537,8 +543,7 @@ def run_ours(args):
                                        f"{B} queries/step, top-{k}, exact cosine (fp32 accumulate)",
                            "rows_per_gpu": n_local, "l2": "inputs larger than L2 (corpus shard "
                            f"{2.0 * n_local * DIM / 1e9:.2f} GB vs 126 MB L2), no flush needed",
-                           "planted_top1_ok": ok, "exchange": "8-byte keys from the finalize kernel -> all_gather -> merge_keys"
-                           if world > 1 and index.use_keys else None, "cuda_graph_step": graph_step},
+                           "planted_top1_ok": ok, "exchange": exchange_kind, "cuda_graph_step": graph_step},
                 "roofline": roof,
                 "e2e": {"value": B / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": B * DIM * 4,
                         "d2h_bytes_per_step": B * k * 12, "ms_per_step": e2e_s * 1e3},

@@ -240,6 +240,18 @@ int srag_mmr_rerank(const void* corpus_bf16, const float* row_scale, int64_t n_r
  * all-gather leaves them; 8 bytes per candidate on the wire instead of 12.                                   */
 int srag_merge_keys(const uint64_t* keys, int n_shards, int n_queries, int kk, int k, float* out_scores,
                     int64_t* out_ids, void* stream);
+/* The exchange AND the merge in one kernel over peer memory (NVLink / NVSwitch P2P stores; no collective call, SURVEY
+ * §5 "peer-to-peer ... is a legitimate alternative to measure against NCCL"). Every rank owns a buffer of the SAME layout
+ * that every peer can address (torch symmetric memory / cudaIpc):
+ *     keys uint64 [2][world][cap_keys] followed anywhere by flags uint32 [world][cap_q], zero-initialised once.
+ * peer_keys_host / peer_flags_host: HOST arrays of `world` device addresses (as uint64) — this process's mapping of every
+ * rank's key / flag region, index = rank. Step `epoch` = 1, 2, 3, ... (the same value on every rank, one step at a
+ * time per buffer): each CTA first stores its queries' keys (local_keys uint64 [n_queries, k], as written by
+ * srag_topk_search_keys) into slot [epoch & 1][rank] of every rank and then raises flag [rank][q] = epoch there; then
+ * it waits for the `world` flags of each of its queries and merges world * k keys (<= 2048) into out_* [n_queries, k].   */
+int srag_exchange_merge_p2p(const uint64_t* local_keys, const uint64_t* peer_keys_host, const uint64_t* peer_flags_host,
+                            int world, int rank, int n_queries, int k, uint32_t epoch, size_t cap_keys, int cap_q,
+                            float* out_scores, int64_t* out_ids, void* stream);
 /* (score, id) -> exchange key, for candidate lists that were not produced by srag_topk_search_keys (BM25 shards).
  * ids must be < 2^32 - 1; *err_flag (device int, may be NULL) is set to 1 otherwise. id < 0 -> empty key.        */
 int srag_pack_keys(const float* scores, const int64_t* ids, int64_t n, uint64_t* keys, int* err_flag, void* stream);

@@ -51,6 +51,7 @@ SIGNATURES = {
     "srag_merge_candidates": [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
     "srag_merge_keys": [_vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
     "srag_pack_keys": [_vp, _vp, _i64, _vp, _vp, _vp],
+    "srag_exchange_merge_p2p": [_vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_uint32, _sz, _i32, _vp, _vp, _vp],
 }
 _RESTYPE = {"srag_last_error": C.c_char_p}
 

@@ -274,3 +274,105 @@ extern "C" int srag_pack_keys(const float* scores, const int64_t* ids, int64_t n
     SRAG_CUDA(cudaGetLastError());
     return SRAG_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// K4x: candidate exchange + merge in ONE kernel over peer memory (NVLink / NVSwitch P2P stores), no collective call.
+// Every rank owns a symmetric buffer (same layout on every rank, mapped into every peer):
+//     keys  uint64 [2 parities][world][cap_keys]      flags uint32 [world][cap_q]
+// Step `epoch` (1, 2, ... the same on every rank): phase 1 — each CTA stores its queries' k exchange keys into slot
+// [epoch & 1][my rank] of EVERY rank's buffer (its own included), fences system-wide, then sets flag [my rank][q] = epoch
+// on every rank; phase 2 — for each of its queries the CTA waits until all `world` flags of the query have reached
+// `epoch`, reads the world * k keys (bypassing L1) and merges them like srag_merge_keys. Pushes never wait for anything,
+// so no set of resident CTAs can deadlock another rank. Keys are double-buffered by parity: a rank cannot start step
+// e + 2 (which reuses the parity of e) before every rank has pushed e + 1, i.e. finished merging e.
+// ---------------------------------------------------------------------------------------
+namespace {
+
+constexpr int P2P_MAX_WORLD = 8;
+struct P2pPeers {
+    uint64_t* keys[P2P_MAX_WORLD];
+    uint32_t* flags[P2P_MAX_WORLD];
+};
+
+__global__ void __launch_bounds__(FUSE_THREADS)
+exchange_merge_p2p_kernel(const uint64_t* __restrict__ local_keys, P2pPeers peers, int world, int rank, int n_queries, int k,
+                          uint32_t epoch, size_t cap_keys, int cap_q, float* __restrict__ out_scores,
+                          int64_t* __restrict__ out_ids) {
+    __shared__ uint64_t s_key[FUSE_MAX_N];
+    const size_t par_off = (size_t)(epoch & 1u) * world * cap_keys;
+    // ---- phase 1: push this CTA's queries to every rank ----
+    for (int q = blockIdx.x; q < n_queries; q += gridDim.x) {
+        for (int e = threadIdx.x; e < world * k; e += blockDim.x) {
+            const int dst = e / k, j = e - dst * k;
+            peers.keys[dst][par_off + (size_t)rank * cap_keys + (size_t)q * k + j] = local_keys[(size_t)q * k + j];
+        }
+        __threadfence_system();   // every thread: its stores are visible system-wide before the flags below
+        __syncthreads();
+        if (threadIdx.x < world)
+            *reinterpret_cast<volatile uint32_t*>(peers.flags[threadIdx.x] + (size_t)rank * cap_q + q) = epoch;
+    }
+    // ---- phase 2: wait for every rank's keys of a query, merge ----
+    const volatile uint32_t* my_flags = peers.flags[rank];
+    const uint64_t* my_keys = peers.keys[rank] + par_off;
+    const int n = world * k;
+    const int P = pow2_at_least(n);
+    for (int q = blockIdx.x; q < n_queries; q += gridDim.x) {
+        if (threadIdx.x < world) {
+            uint32_t spins = 0;
+            // flags only ever rise (a peer one step ahead writes epoch + 1); bounded: a lost peer traps instead of hanging
+            while ((int32_t)(my_flags[(size_t)threadIdx.x * cap_q + q] - epoch) < 0) {
+                __nanosleep(64);
+                if (++spins > (1u << 24)) __trap();
+            }
+            __threadfence_system();
+        }
+        __syncthreads();
+        for (int e = threadIdx.x; e < P; e += blockDim.x) {
+            uint64_t key = SRAG_KEY_EMPTY;
+            if (e < n) {
+                const int g = e / k, i = e - g * k;
+                key = __ldcv(my_keys + (size_t)g * cap_keys + (size_t)q * k + i);   // written by a peer: not through L1
+            }
+            s_key[e] = key;
+        }
+        __syncthreads();
+        block_bitonic(P, [&](int i, int j) { return s_key[i] > s_key[j]; },
+                      [&](int i, int j) { const uint64_t a = s_key[i]; s_key[i] = s_key[j]; s_key[j] = a; });
+        for (int j = threadIdx.x; j < k; j += blockDim.x) {
+            const uint64_t key = j < P ? s_key[j] : SRAG_KEY_EMPTY;
+            const bool ok = key != SRAG_KEY_EMPTY;
+            out_ids[(size_t)q * k + j] = ok ? (int64_t)srag_key_idx(key) : -1;
+            out_scores[(size_t)q * k + j] = ok ? __uint_as_float(srag_key_score_bits(key)) : -INFINITY;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+extern "C" int srag_exchange_merge_p2p(const uint64_t* local_keys, const uint64_t* peer_keys_host,
+                                       const uint64_t* peer_flags_host, int world, int rank, int n_queries, int k,
+                                       uint32_t epoch, size_t cap_keys, int cap_q, float* out_scores, int64_t* out_ids,
+                                       void* stream) {
+    SRAG_CHECK_ARG(world >= 1 && world <= P2P_MAX_WORLD && rank >= 0 && rank < world, "bad world=%d rank=%d", world, rank);
+    SRAG_CHECK_ARG(n_queries >= 0 && k >= 1 && world * k <= FUSE_MAX_N, "bad sizes n_queries=%d k=%d", n_queries, k);
+    SRAG_CHECK_ARG(epoch >= 1 && n_queries <= cap_q && (size_t)n_queries * k <= cap_keys,
+                   "epoch must be >= 1 and the batch must fit the symmetric buffer (cap_q=%d cap_keys=%zu)", cap_q, cap_keys);
+    if (n_queries == 0) return SRAG_OK;
+    SRAG_CHECK_ARG(local_keys && peer_keys_host && peer_flags_host && out_scores && out_ids, "null pointer argument");
+    P2pPeers peers;
+    for (int r = 0; r < P2P_MAX_WORLD; ++r) {
+        peers.keys[r] = r < world ? reinterpret_cast<uint64_t*>(peer_keys_host[r]) : nullptr;
+        peers.flags[r] = r < world ? reinterpret_cast<uint32_t*>(peer_flags_host[r]) : nullptr;
+        SRAG_CHECK_ARG(r >= world || (peers.keys[r] && peers.flags[r]), "null peer pointer for rank %d", r);
+    }
+    int sms = 0;
+    const int rc = srag_current_device_props(&sms, nullptr, nullptr);
+    if (rc) return rc;
+    const int resident = sms * 4;   // every CTA pushes before it waits, so the grid size is a throughput choice only
+    const int grid = n_queries < resident ? n_queries : resident;
+    exchange_merge_p2p_kernel<<<grid, FUSE_THREADS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        local_keys, peers, world, rank, n_queries, k, epoch, cap_keys, cap_q, out_scores, out_ids);
+    SRAG_CUDA(cudaGetLastError());
+    return SRAG_OK;
+}

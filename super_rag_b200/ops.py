@@ -442,3 +442,22 @@ def pack_keys(scores: torch.Tensor, ids: torch.Tensor, out: Optional[torch.Tenso
         _lib.check(_lib.load().srag_pack_keys(_ptr(scores.contiguous()), _ptr(ids.contiguous()), ids.numel(), _ptr(keys),
                                               _ptr(None), _stream(dev)), "srag_pack_keys")
     return keys
+
+
+def exchange_merge_p2p(local_keys: torch.Tensor, peer_key_ptrs, peer_flag_ptrs, world: int, rank: int, k: int, epoch: int,
+                       cap_keys: int, cap_q: int, out_scores: Optional[torch.Tensor] = None,
+                       out_ids: Optional[torch.Tensor] = None):
+    """srag_exchange_merge_p2p: push this rank's exchange keys [B, k] into every rank's symmetric buffer over NVLink, wait
+    for the others', merge -> (scores [B,k], ids [B,k]). peer_*_ptrs: ctypes uint64 arrays of `world` device addresses."""
+    _need_cuda(local_keys)
+    if local_keys.dtype != torch.int64 or local_keys.ndim != 2 or local_keys.shape[1] != k or not local_keys.is_contiguous():
+        raise SragError("local_keys must be a contiguous int64 [B, k] tensor")
+    B = local_keys.shape[0]
+    dev = local_keys.device
+    with torch.cuda.device(dev):
+        os_ = out_scores if out_scores is not None else torch.empty(B, k, dtype=torch.float32, device=dev)
+        oi = out_ids if out_ids is not None else torch.empty(B, k, dtype=torch.int64, device=dev)
+        _lib.check(_lib.load().srag_exchange_merge_p2p(_ptr(local_keys), peer_key_ptrs, peer_flag_ptrs, world, rank, B, k,
+                                                       epoch, cap_keys, cap_q, _ptr(os_), _ptr(oi), _stream(dev)),
+                   "srag_exchange_merge_p2p")
+    return os_, oi

@@ -80,6 +80,41 @@ def exchange_candidates(scores: torch.Tensor, ids: torch.Tensor, group=None) -> 
     return gathered[:, 0].to(torch.int32).contiguous().view(torch.float32), gathered[:, 1].contiguous()
 
 
+class P2pExchange:
+    """The symmetric buffer behind `ops.exchange_merge_p2p`: keys uint64 [2][world][cap_keys] + flags uint32 [world][cap_q]
+    in ONE torch symmetric-memory allocation per rank, rendezvoused over the process group so that every rank can store
+    into every other rank's copy through NVLink. One instance per (index, group); steps are numbered by `epoch`."""
+
+    CAP_Q = 1024           # queries per step (ops.MAX_QUERIES_PER_CALL)
+    CAP_K = 128            # SRAG_MAX_TOPK
+
+    def __init__(self, device: torch.device, group=None):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.cap_q, self.cap_keys = self.CAP_Q, self.CAP_Q * self.CAP_K
+        key_bytes = 2 * self.world * self.cap_keys * 8
+        flag_bytes = self.world * self.cap_q * 4
+        self.buf = symm.empty(key_bytes + flag_bytes, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        pg = group if group is not None else dist.group.WORLD
+        self.handle = symm.rendezvous(self.buf, pg)
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.key_ptrs = (C.c_uint64 * self.world)(*ptrs)
+        self.flag_ptrs = (C.c_uint64 * self.world)(*[p + key_bytes for p in ptrs])
+        self.epoch = 0
+        dist.barrier(group)   # every rank has zeroed its flags before anyone's first step
+
+    def step(self, ops, local_keys: torch.Tensor, k: int):
+        if local_keys.shape[0] > self.cap_q or k > self.CAP_K:
+            raise ValueError(f"batch {tuple(local_keys.shape)} exceeds the exchange buffer ({self.cap_q} x {self.CAP_K})")
+        self.epoch += 1
+        return ops.exchange_merge_p2p(local_keys, self.key_ptrs, self.flag_ptrs, self.world, self.rank, k, self.epoch,
+                                      self.cap_keys, self.cap_q)
+
+
 class ShardedVectorIndex:
     """This rank's shard of a row-sharded corpus plus the exchange + merge step.
 
@@ -114,6 +149,21 @@ class ShardedVectorIndex:
             fits = bool(flag.item())
         self.use_keys = fits
         self.use_graph = self.world > 1 and fits and os.environ.get("SRAG_SHARDED_GRAPH", "0") == "1"
+        # SRAG_SHARDED_P2P=1: exchange + merge in one kernel over peer memory instead of the NCCL all-gather (every rank
+        # must set it alike); a failed set-up (no symmetric memory / no P2P access) falls back to NCCL on ALL ranks
+        self.p2p: Optional[P2pExchange] = None
+        if self.world > 1 and fits and os.environ.get("SRAG_SHARDED_P2P", "0") == "1":
+            ok = 1
+            try:
+                self.p2p = P2pExchange(self.rows.device, group)
+            except Exception:
+                ok = 0
+            flag = torch.tensor([ok], dtype=torch.int32, device=self.rows.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if not bool(flag.item()):
+                self.p2p = None
+            if self.p2p is not None:
+                self.use_graph = False   # the step number is a kernel argument
         self._bufs = {}     # (B, k) -> (send keys [B,k], gathered keys [g,B,k])
         self._graphs = {}   # (B, k) -> (graph, static q_bf16, static q_scale, out scores, out ids)
 
@@ -153,6 +203,8 @@ class ShardedVectorIndex:
             self._bufs[(B, k)] = bufs
         send, recv = bufs
         self.local_topk(q_bf16, q_scale, k, out_keys=send)
+        if self.p2p is not None:
+            return self.p2p.step(self.ops, send, k)
         gather_keys(send, self.group, out=recv)
         return self.ops.merge_keys(recv, k)
 

@@ -68,6 +68,20 @@ def main():
     ok_g = bool(torch.equal(gi1, fi)) and bool(torch.equal(gs1.view(torch.int32), fs.view(torch.int32))) and \
         bool(torch.equal(gi2, fi.flip(0))) and bool(torch.equal(gi3, fi)) and bool(torch.equal(gs3.view(torch.int32), fs.view(torch.int32)))
     ok_v = ok_v and ok_g
+    # the one-kernel exchange over peer memory (SRAG_SHARDED_P2P=1): three steps (both parities, a second batch shape)
+    os.environ["SRAG_SHARDED_P2P"] = "1"
+    index_p = ShardedVectorIndex(cb[lo:hi].contiguous(), cs[lo:hi].contiguous(), id_base=lo)
+    os.environ.pop("SRAG_SHARDED_P2P")
+    p2p_used = index_p.p2p is not None
+    if p2p_used:
+        for rep in range(3):
+            ps, pi = index_p.search_batch(Q, k)
+            ok_v = ok_v and bool(torch.equal(pi, fi)) and bool(torch.equal(ps.view(torch.int32), fs.view(torch.int32)))
+        ps, pi = index_p.search_batch(Q[:77], 5)
+        ws5, wi5 = ops.topk_search(cb, cs, *ops.ingest_rows(Q[:77], "cosine"), 5)
+        torch.cuda.synchronize()
+        ok_v = ok_v and bool(torch.equal(pi, wi5)) and bool(torch.equal(ps.view(torch.int32), ws5.view(torch.int32)))
+    mark(rank, f"p2p exchange done (used: {p2p_used})")
     # ids beyond the 32-bit key range take the two-plane exchange: same answers
     big = ShardedVectorIndex(cb[lo:hi].contiguous(), cs[lo:hi].contiguous(), id_base=lo + (1 << 33))
     assert not big.use_keys
@@ -135,7 +149,7 @@ def main():
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(f"world={world} vector_sharded_equals_single={bool(flags[0].item())} "
-              f"bm25_and_hybrid_sharded_equals_single={bool(flags[1].item())} cuda_graph_step={graph_used}", flush=True)
+              f"bm25_and_hybrid_sharded_equals_single={bool(flags[1].item())} cuda_graph_step={graph_used} p2p_exchange={p2p_used}", flush=True)
         if flags[0].item() and flags[1].item():
             print("PARITY OK", flush=True)
     dist.destroy_process_group()
