@@ -995,7 +995,7 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
     }
     prm.window = pl.window;
     // warm-up tiles (see the epilogue): only where a push is expensive (large k) and a shared threshold exists
-    prm.warm = (prm.share_j > 0 && k >= 32 && !rq && ew == 4) ? env_int("SRAG_TOPK_WARM", 8) : 0;
+    prm.warm = (prm.share_j > 0 && k >= env_int("SRAG_TOPK_WARM_MIN_K", 32) && !rq && ew == 4) ? env_int("SRAG_TOPK_WARM", 8) : 0;
     if (prm.warm < 0) prm.warm = 0;
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
     prm.row_tags = n_rows > 0 ? row_tags : nullptr;
