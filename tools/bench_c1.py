@@ -43,6 +43,45 @@ def c1_data(n=100_000, d=1024, nq=1000):
     return C, Q, src
 
 
+def time_reference_api(C, Q, metas, sub, k):
+    """The UNMODIFIED reference path on the host cores: ContextManager.query (context/context.py:14-48) ->
+    SeekDBVectorStoreConnector.search (seekdb_connector.py:98-115) -> the pyseekdb stub's exact-cosine query, one call per
+    query. Needs /root/reference; no GPU. -> (ids [len(sub), k], result fields)."""
+    import logging
+    n, d = C.shape
+    seek, ContextManager, _ = ref_stub.load_reference_connector()
+    ref_stub.STATE.collections.pop("bench_c1_ref", None)
+    cm = ContextManager("bench_c1_ref", embedding_model=None, vectordb_type="seekdb",
+                        vectordb_ctx={"collection": "bench_c1_ref", "vector_size": d})
+    assert type(cm.adaptor.connector).__module__ == "super_rag.vectorstore.seekdb_connector"
+    coll = ref_stub.STATE.collections.setdefault("bench_c1_ref", ref_stub.StubCollection("bench_c1_ref", ref_stub.STATE))
+    coll.add([f"id{r}" for r in range(n)], embeddings=C, metadatas=metas, documents=[None] * n)
+    logging.getLogger("super_rag.vectorstore.seekdb_connector").setLevel(logging.WARNING)
+    cm.query("q", topk=k, vector=Q[sub[0]].tolist())
+    t0 = time.perf_counter()
+    ref_res = [cm.query("q", score_threshold=0.5, topk=k, vector=Q[j].tolist(), index_types=["vector"]) for j in sub]
+    ref_s = (time.perf_counter() - t0) / len(sub)
+    ref_ids = np.array([[r.metadata["row"] for r in x] for x in ref_res])
+    ref_stub.STATE.collections.pop("bench_c1_ref", None)
+    return ref_ids, {"ref_api_cpu_qps": 1.0 / ref_s, "ref_api_cpu_ms_per_query": 1e3 * ref_s,
+                     "ref_api_cpu": f"unmodified ContextManager.query -> SeekDBVectorStoreConnector.search over the pyseekdb stub "
+                                    f"(exact fp32 cosine, numpy on {os.cpu_count()} host cpus), {len(sub)} queries"}
+
+
+def run_reference_only(cpu_queries=200):
+    """CPU-only: the reference-API leg of C1 in the build container (where /root/reference lives), checked against the
+    oracle instead of the GPU."""
+    n, d, nq, k = 100_000, 1024, 1000, 5
+    C, Q, src = c1_data(n, d, nq)
+    sub = list(range(nq - cpu_queries, nq))
+    ref_ids, line = time_reference_api(C, Q, [{"row": r} for r in range(n)], sub, k)
+    want_s, want_i = oracle.exact_topk(C, Q[sub], k, "cosine")
+    line.update({"config": "C1 (reference API leg only, no GPU in this container)", "cpu_cores": os.cpu_count(),
+                 "ref_api_vs_oracle_identical_id_lists": float((ref_ids == want_i).all(axis=1).mean()),
+                 "planted_top1_ok": bool((ref_ids[:, 0] == src[-cpu_queries:]).all())})
+    return line
+
+
 def run(dev=None, cpu_queries=200):
     n, d, nq, k = 100_000, 1024, 1000, 5
     C, Q, src = c1_data(n, d, nq)
@@ -98,26 +137,9 @@ def run(dev=None, cpu_queries=200):
     # ---- the CPU side: the reference's own connector over the stub, one call per query -------------------------
     sub = list(range(nq - cpu_queries, nq))
     if ref_stub.reference_available():
-        seek, ContextManager, _ = ref_stub.load_reference_connector()
-        ref_stub.STATE.collections.pop("bench_c1_ref", None)
-        cm = ContextManager("bench_c1_ref", embedding_model=None, vectordb_type="seekdb",
-                            vectordb_ctx={"collection": "bench_c1_ref", "vector_size": d})
-        assert type(cm.adaptor.connector).__module__ == "super_rag.vectorstore.seekdb_connector"
-        coll = ref_stub.STATE.collections.setdefault("bench_c1_ref", ref_stub.StubCollection("bench_c1_ref", ref_stub.STATE))
-        coll.add([f"id{r}" for r in range(n)], embeddings=C, metadatas=metas, documents=[None] * n)
-        import logging
-        logging.getLogger("super_rag.vectorstore.seekdb_connector").setLevel(logging.WARNING)
-        cm.query("q", topk=k, vector=Q[sub[0]].tolist())
-        t0 = time.perf_counter()
-        ref_res = [cm.query("q", score_threshold=0.5, topk=k, vector=Q[j].tolist(), index_types=["vector"]) for j in sub]
-        ref_s = (time.perf_counter() - t0) / len(sub)
-        ref_ids = np.array([[r.metadata["row"] for r in x] for x in ref_res])
-        agree = float((ref_ids == ids_single[sub]).all(axis=1).mean())
-        line.update({"ref_api_cpu_qps": 1.0 / ref_s, "ref_api_cpu_ms_per_query": 1e3 * ref_s,
-                     "ref_api_cpu": f"unmodified ContextManager.query -> SeekDBVectorStoreConnector.search over the pyseekdb stub "
-                                    f"(exact fp32 cosine, numpy on {os.cpu_count()} host cpus), {len(sub)} queries",
-                     "ref_api_vs_gpu_identical_id_lists": agree})
-        ref_stub.STATE.collections.pop("bench_c1_ref", None)
+        ref_ids, ref_line = time_reference_api(C, Q, metas, sub, k)
+        ref_line["ref_api_vs_gpu_identical_id_lists"] = float((ref_ids == ids_single[sub]).all(axis=1).mean())
+        line.update(ref_line)
     else:
         coll = ref_stub.StubCollection("direct", ref_stub.STATE)
         coll.add([f"id{r}" for r in range(n)], embeddings=C, metadatas=metas, documents=[None] * n)
@@ -135,4 +157,4 @@ def run(dev=None, cpu_queries=200):
 
 
 if __name__ == "__main__":
-    print(json.dumps(run()), flush=True)
+    print(json.dumps(run_reference_only() if "--reference-only" in sys.argv else run()), flush=True)
