@@ -13,6 +13,8 @@
 // over shared-memory tiles (m <= 256, D ~ 1024: 67 MFLOP per query at most — CUDA cores, no tensor cores;
 // the tile never exists in memory, only its row maxima do). 1/|c_i| is the row multiplier K0 stored at
 // ingest, folded into the tile as it is staged.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -175,6 +177,209 @@ mmr_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict__ r
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Tensor-core variant (round 2; m > 32). The Gram matrix is the one contraction of the path that ran on CUDA cores
+// (3.7 ms per 1024 queries at m = 256). Here one CTA per query computes it with tcgen05.mma, accumulators in TMEM:
+//   * the candidates' raw bf16 rows are gathered by id, 64 dimensions (128 bytes) at a time, straight into the K-major
+//     128-byte-swizzled shared-memory layout the MMA reads (what TMA would write: 16-byte chunk c of row r at
+//     r * 128 + ((c ^ (r & 7)) << 4)); two stages, so the gather of k-block kb + 1 overlaps the MMAs of kb;
+//   * A = candidate rows [128 h, 128 h + 128) (M = 128, h = 0 / 1), B = all candidate rows (N = 128 or 256): D_h[i][j] =
+//     c_i . c_j for the unscaled rows, fp32, in TMEM columns [h N, h N + N);
+//   * epilogue: a thread owns one row (TMEM lane), reads it 32 columns at a time and keeps max_j D_ij s_j over the valid
+//     j != i; times s_i (>= 0) that is max_j S_ij. Products of bf16 values are exact in fp32, so the only rounding is the
+//     accumulation — closer to the float64 reference than the scaled-fp32 tiles of the CUDA-core kernel.
+// Relevance, scoring and the sort are the code above.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int MMRT_THREADS = 256;
+constexpr int MMRT_KB = 64;                       // dimensions per k-block: one 128-byte swizzle row
+constexpr int MMRT_STAGE_BYTES = MMR_MAX * 128;   // 256 rows x 128 B
+
+__global__ void __launch_bounds__(MMRT_THREADS)
+mmr_tc_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict__ row_scale, int64_t n_rows, int dim,
+              const __nv_bfloat16* __restrict__ queries, const float* __restrict__ q_scale,
+              const int64_t* __restrict__ cand_ids, int m, int64_t id_base, float lambda, float min_score,
+              int64_t* __restrict__ out_ids, float* __restrict__ out_scores) {
+    extern __shared__ uint8_t mmr_smem_raw[];
+    uint8_t* stage_base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(mmr_smem_raw) + 1023) & ~(uintptr_t)1023);
+    __shared__ int64_t s_row[MMR_MAX];
+    __shared__ float s_scale[MMR_MAX];
+    __shared__ float s_rel[MMR_MAX];
+    __shared__ float s_rowmax[MMR_MAX];
+    __shared__ uint64_t s_key[MMR_MAX];
+    __shared__ uint64_t mma_done[2];
+    __shared__ uint32_t tmem_slot;
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t* ids = cand_ids + (size_t)q * m;
+    const int halves = m > 128 ? 2 : 1;
+    const int N = m > 128 ? 256 : 128;
+    const uint32_t tmem_cols = (uint32_t)(halves * N);   // 128 or 512: a power of two >= 32
+
+    for (int i = tid; i < MMR_MAX; i += MMRT_THREADS) {
+        int64_t row = -1;
+        float sc = 0.f;
+        if (i < m) {
+            const int64_t id = ids[i];
+            if (id >= id_base && id - id_base < n_rows) {
+                row = id - id_base;
+                sc = __ldg(row_scale + row);
+                if (!(sc == sc)) row = -1;  // NaN multiplier = deleted row
+            }
+        }
+        s_row[i] = row;
+        s_scale[i] = row >= 0 ? sc : 0.f;
+        s_rel[i] = 0.f;
+        s_rowmax[i] = 0.f;
+    }
+    if (tid == 0) {
+        ptx::mbar_init(&mma_done[0], 1);
+        ptx::mbar_init(&mma_done[1], 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 0) {
+        ptx::tmem_alloc<1>(&tmem_slot, tmem_cols);
+        ptx::tmem_relinquish<1>();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    // relevance q . c_i: one warp per candidate, 8 dimensions per lane and step
+    const __nv_bfloat16* qv = queries + (size_t)q * dim;
+    for (int i = warp; i < m; i += MMRT_THREADS / 32) {
+        const int64_t row = s_row[i];
+        if (row < 0) continue;
+        const __nv_bfloat16* cv = corpus + (size_t)row * dim;
+        float acc = 0.f;
+        for (int d = 8 * lane; d < dim; d += 256) {
+            float a[8], b[8];
+            bf16x8_to_f32(__ldg(reinterpret_cast<const uint4*>(qv + d)), 1.0f, a);
+            bf16x8_to_f32(__ldg(reinterpret_cast<const uint4*>(cv + d)), 1.0f, b);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc = fmaf(a[e], b[e], acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+        if (lane == 0) s_rel[i] = acc * __ldg(q_scale + q) * s_scale[i];
+    }
+
+    // ---- Gram matrix on the tensor cores ----
+    const int num_kb = (dim + MMRT_KB - 1) / MMRT_KB;
+    const int rows_pad = halves * 128 > N ? halves * 128 : N;   // rows staged per k-block (128 or 256)
+    const uint32_t idesc = ptx::umma_idesc_bf16(128, (uint32_t)N);
+    constexpr uint32_t KSTEP = (16 * 2) >> 4;                   // descriptor units per UMMA_K = 16 bf16
+    for (int kb = 0; kb < num_kb; ++kb) {
+        const int st = kb & 1;
+        uint8_t* dst = stage_base + st * MMRT_STAGE_BYTES;
+        if (kb >= 2) ptx::mbar_wait(&mma_done[st], (uint32_t)(((kb >> 1) - 1) & 1));   // the MMAs of k-block kb - 2 have read it
+        // every thread moves 16-byte chunks: chunk c of candidate row r -> swizzled position
+        for (int e0 = tid; e0 < rows_pad * 8; e0 += MMRT_THREADS * 4) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * MMRT_THREADS;
+                v[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (e < rows_pad * 8) {
+                    const int r = e >> 3, c = e & 7;
+                    const int d = kb * MMRT_KB + c * 8;
+                    const int64_t row = r < m ? s_row[r] : -1;
+                    if (row >= 0 && d < dim) v[u] = __ldg(reinterpret_cast<const uint4*>(corpus + (size_t)row * dim + d));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * MMRT_THREADS;
+                if (e < rows_pad * 8) {
+                    const int r = e >> 3, c = e & 7;
+                    *reinterpret_cast<uint4*>(dst + r * 128 + ((c ^ (r & 7)) << 4)) = v[u];
+                }
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
+        __syncthreads();
+        if (warp == 0) {
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+                const uint64_t b_desc = ptx::umma_desc_k128(ptx::smem_u32(dst));
+                for (int h = 0; h < halves; ++h) {
+                    const uint64_t a_desc = ptx::umma_desc_k128(ptx::smem_u32(dst + h * 128 * 128));
+#pragma unroll
+                    for (int k = 0; k < MMRT_KB / 16; ++k)
+                        ptx::umma_bf16<1>(tmem_base + (uint32_t)(h * N), a_desc + k * KSTEP, b_desc + k * KSTEP, idesc,
+                                          (uint32_t)((kb | k) != 0));
+                }
+                ptx::umma_commit<1>(&mma_done[st]);
+            }
+            __syncwarp();
+        }
+    }
+    // all MMAs retired: the last commit covers every earlier one
+    {
+        const int last = num_kb - 1;
+        ptx::mbar_wait(&mma_done[last & 1], (uint32_t)((last >> 1) & 1));
+        ptx::tc_fence_after();
+    }
+    // epilogue: thread = row (TMEM lane) of half `warp >> 2`, lane quadrant `warp & 3`
+    {
+        const int h = warp >> 2, quad = warp & 3;
+        if (h < halves) {
+            const int i = h * 128 + quad * 32 + lane;
+            const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(h * N);
+            float mx = 0.f;
+            for (int ch = 0; ch < N / 32; ++ch) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(t_addr + (uint32_t)(ch * 32), v);
+                ptx::tmem_ld_wait_dep(v);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int col = ch * 32 + j;
+                    if (col < m && col != i && s_row[col] >= 0) mx = fmaxf(mx, __uint_as_float(v[j]) * s_scale[col]);
+                }
+            }
+            if (i < m && s_row[i] >= 0) s_rowmax[i] = fmaxf(0.f, mx * s_scale[i]);
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<1>(tmem_base, tmem_cols);
+    }
+
+    // scores -> sortable keys (score desc, candidate position asc = the reference's stable sort)
+    for (int i = tid; i < MMR_MAX; i += MMRT_THREADS) {
+        uint64_t key = SRAG_KEY_EMPTY;
+        if (i < m && s_row[i] >= 0) {
+            const float s = lambda * s_rel[i] + (lambda - 1.0f) * s_rowmax[i];
+            if (s >= min_score) key = srag_pack_key(__float_as_uint(s), (uint32_t)i);
+        }
+        s_key[i] = key;
+    }
+    __syncthreads();
+    for (int size = 2; size <= MMR_MAX; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = tid; t < MMR_MAX / 2; t += MMRT_THREADS) {
+                const int i = 2 * t - (t & (stride - 1)), j = i + stride;
+                const bool desc = (i & size) == 0;
+                const uint64_t x = s_key[i], y = s_key[j];
+                if ((x < y) == desc) { s_key[i] = y; s_key[j] = x; }
+            }
+            __syncthreads();
+        }
+    for (int j = tid; j < m; j += MMRT_THREADS) {
+        const uint64_t key = s_key[j];
+        int64_t id = -1;
+        float s = -INFINITY;
+        if (key != SRAG_KEY_EMPTY) {
+            id = ids[srag_key_idx(key)];
+            s = __uint_as_float(srag_key_score_bits(key));
+        }
+        out_ids[(size_t)q * m + j] = id;
+        out_scores[(size_t)q * m + j] = s;
+    }
+}
+
 }  // namespace
 
 extern "C" int srag_mmr_rerank(const void* corpus_bf16, const float* row_scale, int64_t n_rows, int dim,
@@ -190,6 +395,16 @@ extern "C" int srag_mmr_rerank(const void* corpus_bf16, const float* row_scale, 
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const __nv_bfloat16* c = reinterpret_cast<const __nv_bfloat16*>(corpus_bf16);
     const __nv_bfloat16* qv = reinterpret_cast<const __nv_bfloat16*>(queries_bf16);
+    static const bool use_tc = [] { const char* e = getenv("SRAG_MMR_TC"); return !(e && e[0] == '0'); }();
+    if (m > 32 && use_tc) {   // tensor-core Gram matrix (SRAG_MMR_TC=0: the CUDA-core kernel, for A/B runs)
+        const int smem = 2 * MMRT_STAGE_BYTES + 1024;
+        const int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&mmr_tc_kernel), smem);
+        if (rc) return rc;
+        mmr_tc_kernel<<<n_queries, MMRT_THREADS, smem, st>>>(c, row_scale, n_rows, dim, qv, q_scale, cand_ids, m, id_base,
+                                                             mmr_lambda, min_score, out_ids, out_scores);
+        SRAG_CUDA(cudaGetLastError());
+        return SRAG_OK;
+    }
     if (m <= 32)
         mmr_kernel<2><<<n_queries, MMR_THREADS, 0, st>>>(c, row_scale, n_rows, dim, qv, q_scale, cand_ids, m, id_base,
                                                          mmr_lambda, min_score, out_ids, out_scores);
