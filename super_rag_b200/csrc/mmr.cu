@@ -193,7 +193,12 @@ mmr_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict__ r
 // ---------------------------------------------------------------------------------------------------------
 constexpr int MMRT_THREADS = 256;
 constexpr int MMRT_KB = 64;                       // dimensions per k-block: one 128-byte swizzle row
-constexpr int MMRT_STAGE_BYTES = MMR_MAX * 128;   // 256 rows x 128 B
+constexpr int MMRT_STAGES = 4;                    // k-blocks in flight (cp.async groups)
+
+__device__ __forceinline__ void mmr_cp_async_16(uint32_t smem_dst, const void* gsrc, uint32_t src_bytes) {
+    // src_bytes = 16 copies, 0 zero-fills the 16 bytes (the source address must still be valid)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(gsrc), "r"(src_bytes) : "memory");
+}
 
 __global__ void __launch_bounds__(MMRT_THREADS)
 mmr_tc_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict__ row_scale, int64_t n_rows, int dim,
@@ -207,13 +212,17 @@ mmr_tc_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict_
     __shared__ float s_rel[MMR_MAX];
     __shared__ float s_rowmax[MMR_MAX];
     __shared__ uint64_t s_key[MMR_MAX];
-    __shared__ uint64_t mma_done[2];
+    __shared__ uint64_t mma_done[MMRT_STAGES];
     __shared__ uint32_t tmem_slot;
     const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t* ids = cand_ids + (size_t)q * m;
     const int halves = m > 128 ? 2 : 1;
     const int N = m > 128 ? 256 : 128;
+    const int rows_pad = N;                               // rows staged per k-block
+    const int stage_bytes = rows_pad * 128;
+    const int num_kb = (dim + MMRT_KB - 1) / MMRT_KB;
     const uint32_t tmem_cols = (uint32_t)(halves * N);   // 128 or 512: a power of two >= 32
+    uint8_t* q_s = stage_base + MMRT_STAGES * stage_bytes;   // the query, raw bf16, zero-padded to num_kb * 64 dimensions
 
     for (int i = tid; i < MMR_MAX; i += MMRT_THREADS) {
         int64_t row = -1;
@@ -231,9 +240,14 @@ mmr_tc_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict_
         s_rel[i] = 0.f;
         s_rowmax[i] = 0.f;
     }
+    for (int c = tid; c < num_kb * 8; c += MMRT_THREADS) {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (c * 8 < dim) v = __ldg(reinterpret_cast<const uint4*>(queries + (size_t)q * dim + c * 8));
+        *reinterpret_cast<uint4*>(q_s + c * 16) = v;
+    }
     if (tid == 0) {
-        ptx::mbar_init(&mma_done[0], 1);
-        ptx::mbar_init(&mma_done[1], 1);
+#pragma unroll
+        for (int s = 0; s < MMRT_STAGES; ++s) ptx::mbar_init(&mma_done[s], 1);
         ptx::fence_mbar_init();
     }
     if (warp == 0) {
@@ -245,65 +259,39 @@ mmr_tc_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict_
     ptx::tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
 
-    // relevance q . c_i: one warp per candidate, 8 dimensions per lane and step
-    const __nv_bfloat16* qv = queries + (size_t)q * dim;
-    for (int i = warp; i < m; i += MMRT_THREADS / 32) {
-        const int64_t row = s_row[i];
-        if (row < 0) continue;
-        const __nv_bfloat16* cv = corpus + (size_t)row * dim;
-        float acc = 0.f;
-        for (int d = 8 * lane; d < dim; d += 256) {
-            float a[8], b[8];
-            bf16x8_to_f32(__ldg(reinterpret_cast<const uint4*>(qv + d)), 1.0f, a);
-            bf16x8_to_f32(__ldg(reinterpret_cast<const uint4*>(cv + d)), 1.0f, b);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) acc = fmaf(a[e], b[e], acc);
+    // ---- Gram matrix on the tensor cores, relevance from the same staged tiles ----
+    // cp.async group g = k-block g (an empty group past the end), MMRT_STAGES - 1 k-blocks ahead of the MMAs.
+    const uint32_t stage_u32 = ptx::smem_u32(stage_base);
+    auto issue = [&](int kb) {
+        const uint32_t dst = stage_u32 + (uint32_t)((kb % MMRT_STAGES) * stage_bytes);
+        for (int e = tid; e < rows_pad * 8; e += MMRT_THREADS) {
+            const int r = e >> 3, c = e & 7;
+            const int d = kb * MMRT_KB + c * 8;
+            const int64_t row = r < m ? s_row[r] : -1;
+            const bool ok = row >= 0 && d < dim;
+            mmr_cp_async_16(dst + (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)), ok ? corpus + (size_t)row * dim + d : corpus,
+                            ok ? 16u : 0u);
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
-        if (lane == 0) s_rel[i] = acc * __ldg(q_scale + q) * s_scale[i];
+    };
+    for (int kb = 0; kb < MMRT_STAGES - 1; ++kb) {
+        if (kb < num_kb) issue(kb);
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
-
-    // ---- Gram matrix on the tensor cores ----
-    const int num_kb = (dim + MMRT_KB - 1) / MMRT_KB;
-    const int rows_pad = halves * 128 > N ? halves * 128 : N;   // rows staged per k-block (128 or 256)
     const uint32_t idesc = ptx::umma_idesc_bf16(128, (uint32_t)N);
     constexpr uint32_t KSTEP = (16 * 2) >> 4;                   // descriptor units per UMMA_K = 16 bf16
+    float rel_acc = 0.f;                                        // thread tid: q . (raw row tid)
     for (int kb = 0; kb < num_kb; ++kb) {
-        const int st = kb & 1;
-        uint8_t* dst = stage_base + st * MMRT_STAGE_BYTES;
-        if (kb >= 2) ptx::mbar_wait(&mma_done[st], (uint32_t)(((kb >> 1) - 1) & 1));   // the MMAs of k-block kb - 2 have read it
-        // every thread moves 16-byte chunks: chunk c of candidate row r -> swizzled position
-        for (int e0 = tid; e0 < rows_pad * 8; e0 += MMRT_THREADS * 4) {
-            uint4 v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int e = e0 + u * MMRT_THREADS;
-                v[u] = make_uint4(0u, 0u, 0u, 0u);
-                if (e < rows_pad * 8) {
-                    const int r = e >> 3, c = e & 7;
-                    const int d = kb * MMRT_KB + c * 8;
-                    const int64_t row = r < m ? s_row[r] : -1;
-                    if (row >= 0 && d < dim) v[u] = __ldg(reinterpret_cast<const uint4*>(corpus + (size_t)row * dim + d));
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int e = e0 + u * MMRT_THREADS;
-                if (e < rows_pad * 8) {
-                    const int r = e >> 3, c = e & 7;
-                    *reinterpret_cast<uint4*>(dst + r * 128 + ((c ^ (r & 7)) << 4)) = v[u];
-                }
-            }
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
-        __syncthreads();
+        const int st = kb % MMRT_STAGES;
+        uint8_t* tile = stage_base + st * stage_bytes;
+        asm volatile("cp.async.wait_group %0;" ::"n"(MMRT_STAGES - 2) : "memory");   // this thread's part of k-block kb landed
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
+        __syncthreads();                                        // ... everyone's part; and relevance(kb - 1) is over
         if (warp == 0) {
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
-                const uint64_t b_desc = ptx::umma_desc_k128(ptx::smem_u32(dst));
+                const uint64_t b_desc = ptx::umma_desc_k128(ptx::smem_u32(tile));
                 for (int h = 0; h < halves; ++h) {
-                    const uint64_t a_desc = ptx::umma_desc_k128(ptx::smem_u32(dst + h * 128 * 128));
+                    const uint64_t a_desc = ptx::umma_desc_k128(ptx::smem_u32(tile + h * 128 * 128));
 #pragma unroll
                     for (int k = 0; k < MMRT_KB / 16; ++k)
                         ptx::umma_bf16<1>(tmem_base + (uint32_t)(h * N), a_desc + k * KSTEP, b_desc + k * KSTEP, idesc,
@@ -313,11 +301,33 @@ mmr_tc_kernel(const __nv_bfloat16* __restrict__ corpus, const float* __restrict_
             }
             __syncwarp();
         }
+        // refill the stage k-block kb - 1 used (its MMAs must have read it; its relevance pass ended before the barrier)
+        const int nxt = kb + MMRT_STAGES - 1;
+        if (nxt < num_kb) {
+            if (kb >= 1) ptx::mbar_wait(&mma_done[(kb - 1) % MMRT_STAGES], (uint32_t)(((kb - 1) / MMRT_STAGES) & 1));
+            issue(nxt);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        // relevance: thread = candidate row; the swizzle makes the 16-byte reads of 8 neighbouring rows conflict-free
+        if (tid < rows_pad) {
+            const uint8_t* rowp = tile + tid * 128;
+            const uint8_t* qp = q_s + kb * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float a[8], b[8];
+                bf16x8_to_f32(*reinterpret_cast<const uint4*>(rowp + ((c ^ (tid & 7)) << 4)), 1.0f, a);
+                bf16x8_to_f32(*reinterpret_cast<const uint4*>(qp + c * 16), 1.0f, b);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) rel_acc = fmaf(a[e], b[e], rel_acc);
+            }
+        }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (tid < m && s_row[tid] >= 0) s_rel[tid] = rel_acc * __ldg(q_scale + q) * s_scale[tid];
     // all MMAs retired: the last commit covers every earlier one
     {
         const int last = num_kb - 1;
-        ptx::mbar_wait(&mma_done[last & 1], (uint32_t)((last >> 1) & 1));
+        ptx::mbar_wait(&mma_done[last % MMRT_STAGES], (uint32_t)((last / MMRT_STAGES) & 1));
         ptx::tc_fence_after();
     }
     // epilogue: thread = row (TMEM lane) of half `warp >> 2`, lane quadrant `warp & 3`
@@ -396,8 +406,9 @@ extern "C" int srag_mmr_rerank(const void* corpus_bf16, const float* row_scale, 
     const __nv_bfloat16* c = reinterpret_cast<const __nv_bfloat16*>(corpus_bf16);
     const __nv_bfloat16* qv = reinterpret_cast<const __nv_bfloat16*>(queries_bf16);
     static const bool use_tc = [] { const char* e = getenv("SRAG_MMR_TC"); return !(e && e[0] == '0'); }();
-    if (m > 32 && use_tc) {   // tensor-core Gram matrix (SRAG_MMR_TC=0: the CUDA-core kernel, for A/B runs)
-        const int smem = 2 * MMRT_STAGE_BYTES + 1024;
+    const int smem = MMRT_STAGES * (m > 128 ? 256 : 128) * 128 + ((dim + MMRT_KB - 1) / MMRT_KB) * 128 + 1024;
+    // tensor-core Gram matrix (SRAG_MMR_TC=0, or a dim whose staged query does not fit: the CUDA-core kernel)
+    if (m > 32 && use_tc && smem <= 220 * 1024) {
         const int rc = srag_func_smem_optin(reinterpret_cast<const void*>(&mmr_tc_kernel), smem);
         if (rc) return rc;
         mmr_tc_kernel<<<n_queries, MMRT_THREADS, smem, st>>>(c, row_scale, n_rows, dim, qv, q_scale, cand_ids, m, id_base,

@@ -83,3 +83,32 @@ def test_mmr_gathered_candidates_vs_oracle():
             kept_pos = np.nonzero(keep)[0]
             assert int((gi[b] >= 0).sum()) == int(keep.sum())
             _check(gi[b], gs[b], kept_pos[order], scores, ids[b] + id_base * (ids[b] >= 0))
+
+
+@pytest.mark.parametrize("d", [200, 64, 1536])
+def test_mmr_tensor_core_path_ragged_dims_and_sizes(d):
+    """The tcgen05 Gram kernel stages 64 dimensions per k-block: a dim that is not a multiple of 64 (zero-filled tail), one
+    k-block only, more k-blocks than stages; m at both sides of the 128-row split and of the CUDA-core cut (m <= 32)."""
+    import torch
+    from super_rag_b200 import ops
+    rng = np.random.default_rng(d)
+    dev = torch.device("cuda:0")
+    n = 3000
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    C[10:30] = C[10] + 0.3 * rng.standard_normal((20, d)).astype(np.float32)
+    cb, cs = ops.ingest_rows(torch.from_numpy(C).to(dev), "cosine")
+    C_r = oracle.bf16_round(C)
+    for m, B in [(33, 5), (128, 4), (130, 3), (255, 2), (256, 2)]:
+        Q = rng.standard_normal((B, d)).astype(np.float32)
+        qb, qs = ops.ingest_rows(torch.from_numpy(Q).to(dev), "cosine")
+        Q_r = oracle.bf16_round(Q)
+        ids = np.stack([rng.choice(n, m, replace=False) for _ in range(B)]).astype(np.int64)
+        ids[:, m - 1] = 10 + np.arange(B)             # cluster members at the ends of the list
+        ids[:, 0] = 20 + np.arange(B)
+        gi, gs = ops.mmr_rerank(cb, cs, qb, qs, torch.from_numpy(ids).to(dev), 0.6, -2.0)
+        gi, gs = gi.cpu().numpy(), gs.cpu().numpy()
+        for b in range(B):
+            qn = Q_r[b].astype(np.float64) / np.linalg.norm(Q_r[b].astype(np.float64))
+            order, scores = oracle.mmr_rerank(qn, C_r[ids[b]], 0.6, -2.0)
+            assert int((gi[b] >= 0).sum()) == m
+            _check(gi[b], gs[b], order, scores, ids[b])
