@@ -86,7 +86,11 @@ struct TopkParams {
     int num_slabs;    // S
     uint64_t* partial;  // [n_queries][S * EW/4][heap_stride(k)] per-thread 4-ary min-heaps of sortable keys, pre-zeroed (= empty)
     uint32_t* gthr;   // [S * EW/4][n_queries] j-th best score of every list (orderable bits), pre-zeroed
-    int share_j;      // j = ceil(k / lists), 1..8; 0 = threshold sharing off
+    int share_j;      // every list publishes its j-th best score, 1..8; 0 = threshold sharing off
+    int share_need;   // the shared bound is the share_need-th largest published value, share_need = ceil(k / j) <= 16
+    int share_period; // the bound is re-read every tile for the first share_early tiles, then every share_period-th
+    int share_early;
+    int prescan;      // 1: tile 0 is read twice from TMEM — maxima first, pushes once the shared bound exists
     int* progress;    // [S][2 ranks][PROG_SLOTS] tiles fully issued per q-tile unit, pre-zeroed; null = no pacing
     int window;       // tiles the leader may run ahead of the slowest follower
     int warm;         // warm-up tiles per list (0 = off): see "Warm-up" in the epilogue
@@ -399,11 +403,13 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         float* sc = tail->scale + ew * CPW;
         const float nanf_ = __uint_as_float(0x7FC00000u);
         const int col0 = half * CPW;
-        // Threshold sharing. The query is scanned by L = S * H lists (one per unit and column slice). Each
-        // list publishes its j-th best score, j = ceil(k / L). Every list then holds >= j rows scoring
-        // >= T = min over lists of those, i.e. >= k rows overall score >= T, so a row of the global
-        // top-k scores >= T and is never dropped by "> thr" with thr = max(own k-th best, T - 2 ulp).
-        // Cuts heap pushes per thread from ~k ln(n/k) to ~j ln(n/j).
+        // Threshold sharing. The query is scanned by L = S * H lists (one per unit and column slice) over disjoint rows.
+        // Each list publishes its j-th best score. T = the n-th largest published value, n = ceil(k / j): at least n
+        // lists hold >= j rows scoring >= T, i.e. >= k rows overall score >= T, so a row of the global top-k scores >= T
+        // and is never dropped by "> thr" with thr = max(own k-th best, T - 2 ulp). (Round 1 used the MIN over all lists
+        // with j = ceil(k / L): the same argument with n = L, but held down by the unluckiest list and undefined until
+        // every list had published. With j = 1, n = k the bound after one tile is already ~ the k-th best of everything
+        // scanned so far by anyone.) Cuts heap pushes per thread from ~k ln(n/k) to a handful.
         const bool valid_q = q_global < p.n_queries;
         const int qx = min(q_global, p.n_queries - 1);
         const int num_lists = p.num_slabs * H;
@@ -455,6 +461,109 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         bool warm_mode = WARM && warm > 0;
         float nxt[SPL];
         if (n_iter > 0) load_scales(tile_of(0), nxt);
+
+        // share_need-th largest published value of this query's lists (orderable bits; <= 0x00800001 = not there yet)
+        // and how many lists have published at all
+        auto shared_bound = [&](int& n_pub) -> uint32_t {
+            uint32_t best[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) best[i] = 0u;
+            const volatile uint32_t* gp = p.gthr + qx;
+            int cnt = 0;
+#pragma unroll 2
+            for (int l = 0; l < num_lists; ++l) {
+                uint32_t v = gp[(size_t)l * p.n_queries];
+                cnt += v > 0x00800001u;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {  // keep the 16 largest sorted (descending)
+                    const uint32_t hi = max(best[i], v);
+                    v = min(best[i], v);
+                    best[i] = hi;
+                }
+            }
+            uint32_t r = best[0];
+#pragma unroll
+            for (int i = 1; i < 16; ++i) r = (i < p.share_need) ? best[i] : r;
+            n_pub = cnt;
+            return r;
+        };
+        auto publish = [&]() {
+            float tj = topj[0];
+#pragma unroll
+            for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
+            if (tj > -INFINITY) {
+                const uint32_t o = srag_f32_orderable(__float_as_uint(tj));
+                if (o > published) {  // single writer per slot: a plain (volatile) store
+                    *reinterpret_cast<volatile uint32_t*>(p.gthr + (size_t)my_list * p.n_queries + qx) = o;
+                    published = o;
+                }
+            }
+        };
+
+        // Cold start. With empty heaps and no bound every early score is a push, and because the 32 lanes of a warp
+        // (32 queries) push at different columns, a warp pays a sift's dependent L2 round trips at nearly EVERY column of
+        // its first tiles: one tile per unit took 0.41 ms against 0.03 ms in steady state — a fixed ~0.25 ms per search,
+        // 12 % of a 1.25 M-row shard's scan (the N = 8 strong-scaling point). So tile 0 is read from TMEM TWICE (the
+        // accumulator is simply not released in between; the MMAs of tile 1 run into the other buffer meanwhile): first
+        // only the j best scores are kept in registers and published; every list then waits (bounded — a hint, never a
+        // correctness condition) for the others and takes T as above; then the normal pass over tile 0 pushes only what
+        // beats T (~k rows per QUERY, not per thread). topj is cleared in between, `published` only ever rises, so the
+        // j rows a published value stands for are distinct rows of this list.
+        if (p.prescan && p.share_j > 0 && n_iter > 0) {
+            __syncwarp();
+            if constexpr (SPL == 2) {
+                *reinterpret_cast<float2*>(sc + lane * 2) = make_float2(nxt[0], nxt[1]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < SPL; i += 4)
+                    *reinterpret_cast<float4*>(sc + lane * SPL + i) = make_float4(nxt[i], nxt[i + 1], nxt[i + 2], nxt[i + 3]);
+            }
+            __syncwarp();
+            ptx::mbar_wait(&tail->tmem_full[0], 0);
+            ptx::tc_fence_after();
+            const uint32_t t_addr0 = lane_addr + (uint32_t)col0;
+            const uint32_t row_base0 = (uint32_t)tile_of(0) * BLOCK_N + (uint32_t)col0;
+            float tj = valid_q ? -INFINITY : INFINITY;
+#pragma unroll 1
+            for (int ch = 0; ch < CHUNKS; ++ch) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(t_addr0 + (uint32_t)ch * 32u, v);
+                ptx::tmem_ld_wait_dep(v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    float x = __uint_as_float(v[e]) * sc[ch * 32 + e];   // the product the main pass computes (NaN never passes)
+                    if (x > tj && (!filtered || eligible(row_base0 + (uint32_t)(ch * 32 + e)))) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float hi = fmaxf(topj[i], x);
+                            x = fminf(topj[i], x);
+                            topj[i] = hi;
+                        }
+                        tj = topj[0];
+#pragma unroll
+                        for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
+                    }
+                }
+            }
+            if (valid_q) {
+                publish();
+                const int lists_with_rows = (num_c_tiles < p.num_slabs ? num_c_tiles : p.num_slabs) * H;
+                uint32_t spins = 512u, b;
+                for (;;) {
+                    int n_pub;
+                    b = shared_bound(n_pub);
+                    if (n_pub >= lists_with_rows || --spins == 0u) break;
+                    __nanosleep(64);
+                }
+                if (b > 0x00800001u) {
+                    thr_shared = __uint_as_float(srag_f32_from_orderable(b - 2u));
+                    thr = fmaxf(thr_own, thr_shared);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) topj[i] = -INFINITY;
+            __syncwarp();
+        }
         for (int it = 0; it < n_iter; ++it) {
             const int c = tile_of(it);
             const int buf = it & 1;
@@ -486,21 +595,21 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 for (int i = 0; i < 8; ++i) topj[i] = -INFINITY;
                 if (valid_q) thr = -INFINITY;
             }
-            if (p.share_j > 0 && valid_q && !warm_mode && ((it - warm) & 3) == 0) {  // refresh the shared bound every 4th tile
-                // right after the warm-up: wait (bounded — a hint, never a correctness condition) until every list of
+            // refresh the shared bound: every tile while it still moves fast, then every 4th
+            if (p.share_j > 0 && valid_q && !warm_mode && (it - warm < p.share_early || (it - warm) % p.share_period == 0)) {
+                // right after a warm-up pass: wait (bounded — a hint, never a correctness condition) until every list of
                 // this query has published
                 uint32_t spins = (warm > 0 && it == warm) ? 2048u : 1u;
-                uint32_t lo;
+                const int lists_with_rows = (num_c_tiles < p.num_slabs ? num_c_tiles : p.num_slabs) * H;
+                uint32_t b;
                 for (;;) {
-                    lo = 0xFFFFFFFFu;
-                    const volatile uint32_t* gp = p.gthr + qx;
-#pragma unroll 6
-                    for (int l = 0; l < num_lists; ++l) lo = min(lo, gp[(size_t)l * p.n_queries]);
-                    if (lo > 0x00800001u || --spins == 0u) break;
+                    int n_pub;
+                    b = shared_bound(n_pub);
+                    if (n_pub >= lists_with_rows || --spins == 0u) break;
                     __nanosleep(128);
                 }
-                if (lo > 0x00800001u) {  // every list has published something above -inf
-                    thr_shared = __uint_as_float(srag_f32_from_orderable(lo - 2u));
+                if (b > 0x00800001u) {  // share_need lists have published something above -inf
+                    thr_shared = fmaxf(thr_shared, __uint_as_float(srag_f32_from_orderable(b - 2u)));
                     thr = fmaxf(thr_own, thr_shared);
                 }
             }
@@ -616,18 +725,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     process(vb, ch + 1, h1, l1);
                 }
             }
-            if (p.share_j > 0 && valid_q) {
-                float tj = topj[0];
-#pragma unroll
-                for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
-                if (tj > -INFINITY) {
-                    const uint32_t o = srag_f32_orderable(__float_as_uint(tj));
-                    if (o > published) {  // single writer per slot: a plain (volatile) store
-                        *reinterpret_cast<volatile uint32_t*>(p.gthr + (size_t)my_list * p.n_queries + qx) = o;
-                        published = o;
-                    }
-                }
-            }
+            if (p.share_j > 0 && valid_q) publish();
         }
         // nothing to flush: every thread's heap already is its slice of `partial`
     }
@@ -985,17 +1083,29 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
     prm.progress = pl.window > 0 ? reinterpret_cast<int*>(ws + pl.partial_bytes + pl.gthr_bytes) : nullptr;
     prm.gthr = reinterpret_cast<uint32_t*>(ws + pl.partial_bytes);
     {
-        // sharing needs j = ceil(k / lists) <= 8 tracked scores and a short list of slots to poll
+        // sharing: every list tracks its j best scores (j <= 8 registers) and the bound is the ceil(k / j)-th largest
+        // published value (<= 16 registers, <= lists): the smallest such j
         const int lists = pl.num_slabs * (ew / 4);
-        const int j = (k + lists - 1) / lists;
-        // polling many lists costs a little per refresh: with one q-tile (148 lists) it only pays for large k
-        // (k = 100, B = 128: 18.1 -> 5.8 ms; k = 10: 3.5 -> 3.8 ms)
-        const bool worth = lists <= 80 || (lists <= 160 && k >= 32);
-        prm.share_j = (env_int("SRAG_TOPK_SHARE", 1) != 0 && lists >= 2 && worth && j <= 8) ? j : 0;
+        int j = (k + lists - 1) / lists;
+        if (j < (k + 15) / 16) j = (k + 15) / 16;
+        // Polling many lists costs ~33 instructions per list and refresh. With one q-tile (148 lists) the bound is
+        // therefore re-read on the first two tiles and then every 64th only — the prescan's bound does most of the work:
+        // B = 256, k = 10, 10 M rows: 4.70 -> 4.02 ms (0.80 of the roofline), B = 128: 3.38 -> 3.08, B = 32: 3.27 -> 3.12;
+        // a handful of queries (B = 8: 2.96 -> 3.08 ms, HBM-bound at 0.98 already) gain nothing and stay without.
+        const int share_env = env_int("SRAG_TOPK_SHARE", 1);   // 0 off, 1 default rule, 2 wherever possible (A/B runs)
+        const bool worth = lists <= 80 || (lists <= 160 && (k >= 32 || n_queries >= 24)) || share_env == 2;
+        prm.share_j = (share_env != 0 && lists >= 2 && worth && j <= 8) ? j : 0;
+        prm.share_period = env_int("SRAG_TOPK_SHARE_PERIOD", lists <= 80 ? 4 : k >= 32 ? 16 : 64);   // (large k: the bound moves longer)
+        if (prm.share_period < 1) prm.share_period = 1;
+        prm.share_early = env_int("SRAG_TOPK_SHARE_EARLY", lists <= 80 ? 8 : 2);
+        prm.share_need = prm.share_j > 0 ? (k + prm.share_j - 1) / prm.share_j : 0;
+        prm.prescan = prm.share_j > 0 && env_int("SRAG_TOPK_PRESCAN", 1) != 0;
     }
     prm.window = pl.window;
-    // warm-up tiles (see the epilogue): only where a push is expensive (large k) and a shared threshold exists
-    prm.warm = (prm.share_j > 0 && k >= env_int("SRAG_TOPK_WARM_MIN_K", 32) && !rq && ew == 4) ? env_int("SRAG_TOPK_WARM", 8) : 0;
+    // large k (a push is a deep sift): the instantiation with append-until-full lists, plus `warm` warm-up tiles (see the
+    // epilogue; SRAG_TOPK_WARM=0 leaves the cold start to the tile-0 prescan alone)
+    const bool warm_inst = prm.share_j > 0 && k >= env_int("SRAG_TOPK_WARM_MIN_K", 32) && !rq && ew == 4;
+    prm.warm = warm_inst ? env_int("SRAG_TOPK_WARM", 0) : 0;
     if (prm.warm < 0) prm.warm = 0;
     prm.debug = env_int("SRAG_TOPK_DEBUG", 0);
     prm.row_tags = n_rows > 0 ? row_tags : nullptr;
@@ -1033,7 +1143,7 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
                 srag_set_error("the metadata filter is not available with SRAG_TOPK_RQ / SRAG_TOPK_EPI_WARPS overrides");
                 return SRAG_E_INVALID;
             }
-            if (prm.warm > 0)
+            if (warm_inst)
                 rc = pl.cta_group == 2 ? launch_main<2, false, 4, true, true>(pl, tq, tc, prm, st)
                                        : launch_main<1, false, 4, true, true>(pl, tq, tc, prm, st);
             else
@@ -1041,12 +1151,12 @@ static int topk_search_impl(const void* corpus_bf16, const float* row_scale, int
                                        : launch_main<1, false, 4, true>(pl, tq, tc, prm, st);
         } else
         switch (sel) {
-            case 0: rc = prm.warm > 0 ? launch_main<1, false, 4, false, true>(pl, tq, tc, prm, st)
+            case 0: rc = warm_inst ? launch_main<1, false, 4, false, true>(pl, tq, tc, prm, st)
                                       : launch_main<1, false, 4>(pl, tq, tc, prm, st); break;
             case 1: rc = launch_main<1, false, 8>(pl, tq, tc, prm, st); break;
             case 2: rc = launch_main<1, true, 4>(pl, tq, tc, prm, st); break;
             case 3: rc = launch_main<1, true, 8>(pl, tq, tc, prm, st); break;
-            case 4: rc = prm.warm > 0 ? launch_main<2, false, 4, false, true>(pl, tq, tc, prm, st)
+            case 4: rc = warm_inst ? launch_main<2, false, 4, false, true>(pl, tq, tc, prm, st)
                                       : launch_main<2, false, 4>(pl, tq, tc, prm, st); break;
             case 5: rc = launch_main<2, false, 8>(pl, tq, tc, prm, st); break;
             case 6: rc = launch_main<2, true, 4>(pl, tq, tc, prm, st); break;
