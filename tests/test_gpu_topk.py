@@ -209,3 +209,30 @@ def test_k1_against_reference_ranked_lists(topk_golden):
         s1, i1 = col.search_batch(torch.from_numpy(Q[qi:qi + 1]), k)
         check_topk_against_full_scores(s1.cpu().numpy(), i1.cpu().numpy(), ref_full[qi:qi + 1], k, TIGHT)
     cl.delete_collection("t_golden")
+
+
+@pytest.mark.parametrize("b,k", [(1024, 10), (1024, 100), (64, 10), (64, 100), (300, 33)])
+def test_shared_bound_ties_at_the_boundary_and_skewed_lists(b, k):
+    """The shared bound is the ceil(k/j)-th largest of the lists' published j-th best scores and tile 0 is scanned twice
+    (maxima first). Adversarial layouts for it: (a) hundreds of EXACT copies of the query's best row spread over every
+    list, so the k-th boundary falls inside one tie group that spans all lists (lowest rows must win); (b) all of a
+    query's top-k inside ONE tile of one list while every other list publishes low maxima; (c) copies inside tile 0 of a
+    list only (what the prescan sees) with better rows arriving later."""
+    rng = np.random.default_rng(1000 * b + k)
+    n, d = 120_000, 64
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    Q = rng.standard_normal((b, d)).astype(np.float32)
+    v = rng.standard_normal((3, d)).astype(np.float32)
+    spread = np.arange(37, n, 301)[:390]                 # (a) 390 copies, one every 301 rows: every tile range, every list
+    C[spread] = v[0]
+    Q[0] = v[0]
+    C[70_000:70_000 + 2 * k] = v[1] + 0.01 * rng.standard_normal((2 * k, d)).astype(np.float32)   # (b) one tile of one list
+    Q[1] = v[1]
+    C[1000:1000 + k // 2 + 1] = v[2] + 0.2 * rng.standard_normal((k // 2 + 1, d)).astype(np.float32)  # (c) weak copies in a first tile ...
+    C[100_000:100_000 + k] = v[2] + 0.01 * rng.standard_normal((k, d)).astype(np.float32)          # ... better ones much later
+    Q[2] = v[2]
+    Q[b - 1] = v[0]                                      # the last lane of the last q-tile sees the tie group too
+    s, i = _check(C, Q, k)
+    assert i[0].tolist() == spread[:k].tolist() and i[b - 1].tolist() == spread[:k].tolist()
+    assert set(i[1].tolist()) <= set(range(70_000, 70_000 + 2 * k))
+    assert set(i[2].tolist()) == set(range(100_000, 100_000 + k))
