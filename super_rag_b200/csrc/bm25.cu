@@ -776,6 +776,17 @@ constexpr int SUB_CAND = 64;
 // the writes (Mem Busy 76 % -> 55 %), but 256 / 512-byte copies are too small for the TMA path and the one-lane issue
 // block + try_wait loop add instructions: C3 12.3 ms against 9.86 ms with LDGSTS. Kept selectable for A/B runs.
 constexpr bool SUB_STAGE_TMA = SRAG_BM25_STAGE_TMA != 0;
+#ifndef SRAG_BM25_ZERO_TMA
+#define SRAG_BM25_ZERO_TMA 1
+#endif
+// How a warp's 2048 accumulators are cleared between items: 0 = 16 STS.128 per lane (64 LSU wavefronts per item: 17 % of
+// all the kernel's shared-memory wavefronts on C3, the pipe it is bound by); 1 = ONE 8 KB bulk copy (cp.async.bulk, the
+// TMA / async proxy — no LSU wavefronts) from a zero page that stays in L2, issued when the item's candidates have been
+// read out and awaited behind the first fetches of the next item, so its latency hides under theirs.
+constexpr bool SUB_ZERO_TMA = SRAG_BM25_ZERO_TMA != 0;
+// 128 windows of 8 KB, one per warp (mod 128): 3000 warps copying the SAME 64 lines would queue on a few L2 slices
+constexpr int SUB_ZERO_WINDOWS = 128;
+__device__ __align__(128) float g_bm25_zero_page[SUB_ZERO_WINDOWS * BM25_SUB_DOCS];   // never written
 
 // One warp's accumulators with a trash slot on either side, and the staging buffers of its round pipeline.
 // Slices are padded to whole groups of 8 postings; a padding posting carries impact +0.0 and an offset that lands on a
@@ -795,6 +806,7 @@ struct SubWarpTile {
     alignas(16) float4 stage_imp[SUB_DEPTH][32];
     alignas(16) uint2 stage_off[SUB_DEPTH][32];
     alignas(8) uint64_t stage_bar[SUB_DEPTH];   // TMA staging: one mbarrier per stage (count 1 + transaction bytes)
+    alignas(8) uint64_t zero_bar;               // bulk-copy zeroing of acc
 };
 __host__ __device__ constexpr uint32_t sub_trash_offset(int sub_in_block) {
     return sub_in_block == 0 ? (uint32_t)BM25_SUB_DOCS * 4u : (uint32_t)sub_in_block * (BM25_SUB_DOCS * 4u) - 4u;
@@ -873,9 +885,34 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
             for (int i = 0; i < SUB_DEPTH; ++i) ptx::mbar_init(&sm->tile[w].stage_bar[i], 1);
             ptx::fence_mbar_init();
         }
+        if constexpr (SUB_ZERO_TMA) {
+            ptx::mbar_init(&sm->tile[w].zero_bar, 1);
+            ptx::fence_mbar_init();
+        }
     }
     __syncwarp();
     uint32_t stage_phase = 0;   // TMA staging: bit i = parity the next wait on stage i expects
+    // bulk-copy zeroing: acc_clean = the accumulators are all zero (or a copy that makes them so is in flight: zero_wait)
+    bool acc_clean = false, zero_wait = false;
+    uint32_t zero_phase = 0;
+    const float* zero_src = g_bm25_zero_page + (size_t)((blockIdx.x * SUB_WARPS + w) % SUB_ZERO_WINDOWS) * BM25_SUB_DOCS;
+    auto zero_issue = [&]() {   // every lane is done with acc (reads and writes): order them before the async-proxy write
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            ptx::mbar_arrive_expect_tx(&tile->zero_bar, BM25_SUB_DOCS * 4u);
+            ptx::bulk_load_1d(acc, zero_src, BM25_SUB_DOCS * 4u, &tile->zero_bar);
+        }
+        acc_clean = true;
+        zero_wait = true;
+    };
+    auto zero_await = [&]() {
+        if (zero_wait) {
+            ptx::mbar_wait_lean(&tile->zero_bar, zero_phase);
+            zero_phase ^= 1u;
+            zero_wait = false;
+        }
+    };
 
     // Items of this warp: first, first + step, ... as (query, j-th sub-block of the pass); stepping is an add with carry.
     struct Item { int q, j; };
@@ -981,9 +1018,12 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                 const uint32_t rounds = __shfl_sync(FULL, incl, 31);
                 if (rounds == 0) continue;
                 if (!zeroed) {
-                    float4* a4 = reinterpret_cast<float4*>(acc);
+                    if (!SUB_ZERO_TMA || !acc_clean) {
+                        float4* a4 = reinterpret_cast<float4*>(acc);
 #pragma unroll
-                    for (int i = 0; i < BM25_SUB_DOCS / 128; ++i) a4[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int i = 0; i < BM25_SUB_DOCS / 128; ++i) a4[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    acc_clean = false;
                     if (lane == 0) *cand_count = 0;
                     zeroed = true;
                 }
@@ -1075,6 +1115,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                         if (i < n_chunk) fetch(i, i, metas[i]);
                         if constexpr (!SUB_STAGE_TMA) cp_async_commit();
                     }
+                    if constexpr (SUB_ZERO_TMA) zero_await();   // the zeros have landed before the first add
                     for (int r = 0; r < n_chunk; r += SUB_DEPTH) {
 #pragma unroll
                         for (int i = 0; i < SUB_DEPTH; ++i) {
@@ -1124,6 +1165,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                     if ((lane & (sample_group - 1)) == 0)
                         partial[((size_t)q * per_q + ssub) * per_sub + lane / sample_group] = key;
                     __syncwarp();
+                    if constexpr (SUB_ZERO_TMA) zero_issue();
                 }
             } else if (zeroed) {
                 __syncwarp();
@@ -1146,6 +1188,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
                     }
                 }
                 __syncwarp();
+                if constexpr (SUB_ZERO_TMA) zero_issue();
             }
         }
         // rotate the lookahead
@@ -1166,6 +1209,7 @@ bm25_sub_kernel(const uint32_t* __restrict__ slice_ptr /* [vocab][n_sub + 1], in
         tau1 = s1 >= 0 && !SAMPLE ? __ldg(tau + (size_t)x1.q * k + (k - 1)) : 0.f;
         t3 = term_of(x3, s3, 0);
     }
+    if constexpr (SUB_ZERO_TMA) zero_await();   // no copy into this CTA's shared memory may outlive it
 }
 
 // Flagged queries are redone by bm25_items_kernel into per-block lists: clear everything but the sample's top-k.
