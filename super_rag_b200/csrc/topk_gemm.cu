@@ -470,15 +470,21 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             for (int i = 0; i < 16; ++i) best[i] = 0u;
             const volatile uint32_t* gp = p.gthr + qx;
             int cnt = 0;
-#pragma unroll 2
-            for (int l = 0; l < num_lists; ++l) {
-                uint32_t v = gp[(size_t)l * p.n_queries];
-                cnt += v > 0x00800001u;
+#pragma unroll 1
+            for (int l0 = 0; l0 < num_lists; l0 += 8) {   // 8 slots per L2 round trip (the loads are issued together)
+                uint32_t vv[8];
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {  // keep the 16 largest sorted (descending)
-                    const uint32_t hi = max(best[i], v);
-                    v = min(best[i], v);
-                    best[i] = hi;
+                for (int u = 0; u < 8; ++u) vv[u] = l0 + u < num_lists ? gp[(size_t)(l0 + u) * p.n_queries] : 0u;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    uint32_t v = vv[u];
+                    cnt += v > 0x00800001u;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {  // keep the 16 largest sorted (descending)
+                        const uint32_t hi = max(best[i], v);
+                        v = min(best[i], v);
+                        best[i] = hi;
+                    }
                 }
             }
             uint32_t r = best[0];
@@ -500,6 +506,11 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
         };
 
+        // (Tried and dropped: the push path out of line, once per kernel — spill the chunk's 32 scores to local memory when
+        // one passes and call a routine that loops over them, state in local memory. The kernels shrank from 5.1 K / 7.9 K to
+        // 2.8 K instructions, but a push became ~2000 cycles of dependent local-memory accesses: 1.25 M rows, B = 1024:
+        // k = 10 1.87 -> 2.54 ms, k = 100 3.04 -> 6.8 ms. The cold start is bound by the LATENCY of the push path in the
+        // epilogue warps, not by instruction fetch.)
         // Cold start. With empty heaps and no bound every early score is a push, and because the 32 lanes of a warp
         // (32 queries) push at different columns, a warp pays a sift's dependent L2 round trips at nearly EVERY column of
         // its first tiles: one tile per unit took 0.41 ms against 0.03 ms in steady state — a fixed ~0.25 ms per search,
