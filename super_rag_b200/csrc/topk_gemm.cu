@@ -170,6 +170,19 @@ __device__ __noinline__ float heap_build(uint64_t* heap, int k) {
     return root == SRAG_KEY_EMPTY ? -INFINITY : __uint_as_float(srag_key_score_bits(root));
 }
 
+// sv[e] for a run-time e without touching memory: a 5-level select tree (31 FSEL) over registers
+__device__ __forceinline__ float select32(const float (&sv)[32], int e) {
+    float a[16], b[8], c[4];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = (e & 1) ? sv[2 * i + 1] : sv[2 * i];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) b[i] = (e & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[i] = (e & 4) ? b[2 * i + 1] : b[2 * i];
+    const float d0 = (e & 8) ? c[1] : c[0], d1 = (e & 8) ? c[3] : c[2];
+    return (e & 16) ? d1 : d0;
+}
+
 // ---------------------------------------------------------------------------------------
 // main kernel
 // ---------------------------------------------------------------------------------------
@@ -540,19 +553,33 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 uint32_t v[32];
                 ptx::tmem_ld_32x32(t_addr0 + (uint32_t)ch * 32u, v);
                 ptx::tmem_ld_wait_dep(v);
+                float x[32];
+                float mx = -INFINITY;
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
-                    float x = __uint_as_float(v[e]) * sc[ch * 32 + e];   // the product the main pass computes (NaN never passes)
-                    if (x > tj && (!filtered || eligible(row_base0 + (uint32_t)(ch * 32 + e)))) {
+                    x[e] = __uint_as_float(v[e]) * sc[ch * 32 + e];   // the product the main pass computes (NaN never passes)
+                    mx = fmaxf(mx, x[e]);
+                }
+                if (mx > tj) {
+                    uint32_t mask = 0u;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const float hi = fmaxf(topj[i], x);
-                            x = fminf(topj[i], x);
-                            topj[i] = hi;
+                    for (int e = 0; e < 32; ++e) mask |= (x[e] > tj ? 1u : 0u) << e;
+#pragma unroll 1
+                    while (mask) {
+                        const int e = __ffs(mask) - 1;
+                        mask &= mask - 1u;
+                        float y = select32(x, e);
+                        if (y > tj && (!filtered || eligible(row_base0 + (uint32_t)(ch * 32 + e)))) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const float hi = fmaxf(topj[i], y);
+                                y = fminf(topj[i], y);
+                                topj[i] = hi;
+                            }
+                            tj = topj[0];
+#pragma unroll
+                            for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
                         }
-                        tj = topj[0];
-#pragma unroll
-                        for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
                     }
                 }
             }
@@ -673,44 +700,48 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 const float mx = fmaxf(fmaxf(g[0], g[1]), fmaxf(g[2], g[3]));
                 if (!__any_sync(0xFFFFFFFFu, mx > thr)) return;
                 if (mx > thr) {
+                    // Rare path, ONE copy of the push code per chunk reader instead of one per column: a bit mask of the
+                    // columns that beat the threshold, then a loop over its set bits in ascending row order (the score is
+                    // re-read from the registers with a select tree and re-checked: the threshold only rises). It used to be
+                    // inlined at each of the 64 unrolled compare sites — 2 K (plain) to 4.7 K (append + filter)
+                    // instructions that run a few times per tile and are never in the instruction cache (L0 6 KB, L1.5
+                    // 32 KB): ncu on a cold-start-dominated run (k = 100, 1.25 M rows) put 30 % of all stall samples on
+                    // `no_inst` at those sites. A loop also lets every lane work on ITS next passing column in the same
+                    // iteration, where the unrolled sites serialised a warp over the union of its lanes' columns.
                     const uint32_t r0 = row_base + (uint32_t)ch * 32u;
+                    uint32_t mask = 0u;
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        if (g[q] > thr) {
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                if (sv[q * 8 + e] > thr && (!filtered || eligible(r0 + q * 8 + e)))
-                                {
-                                    float v = sv[q * 8 + e];
-                                    if (!WARM || !warm_mode) {
-                                        if constexpr (WARM) {
-                                            // (only in the warm-up instantiations: in the plain kernels the extra branch and
-                                            // call site at each of the 64 unrolled push sites cost the HBM-bound plans 25 %
-                                            // — B = 128, k = 10: 3.9 -> 4.9 ms — for no gain at small k)
-                                            if (heap_cnt < p.k) {   // not full yet: append (the threshold stays where it is)
-                                                heap[heap_cnt + 3] = srag_pack_key(__float_as_uint(v), r0 + q * 8 + e);
-                                                if (++heap_cnt == p.k) thr_own = heap_build(heap, p.k);
-                                            } else {
-                                                thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
-                                            }
-                                        } else {
-                                            thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + q * 8 + e);
-                                        }
-                                        thr = fmaxf(thr_own, thr_shared);
+                    for (int e = 0; e < 32; ++e) mask |= (sv[e] > thr ? 1u : 0u) << e;
+#pragma unroll 1
+                    while (mask) {
+                        const int e = __ffs(mask) - 1;
+                        mask &= mask - 1u;
+                        float v = select32(sv, e);
+                        if (v > thr && (!filtered || eligible(r0 + (uint32_t)e))) {
+                            if (!WARM || !warm_mode) {
+                                if constexpr (WARM) {
+                                    if (heap_cnt < p.k) {   // not full yet: append (the threshold stays where it is)
+                                        heap[heap_cnt + 3] = srag_pack_key(__float_as_uint(v), r0 + (uint32_t)e);
+                                        if (++heap_cnt == p.k) thr_own = heap_build(heap, p.k);
+                                    } else {
+                                        thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + (uint32_t)e);
                                     }
-#pragma unroll
-                                    for (int i = 0; i < 8; ++i) {  // keep the 8 best scores sorted (descending)
-                                        const float hi = fmaxf(topj[i], v);
-                                        v = fminf(topj[i], v);
-                                        topj[i] = hi;
-                                    }
-                                    if (WARM && warm_mode) {  // warm-up: only the j best matter; the filter is the j-th best so far
-                                        float tj = topj[0];
-#pragma unroll
-                                        for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
-                                        thr = tj;
-                                    }
+                                } else {
+                                    thr_own = heap_replace_root(heap, p.k, __float_as_uint(v), r0 + (uint32_t)e);
                                 }
+                                thr = fmaxf(thr_own, thr_shared);
+                            }
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {  // keep the 8 best scores sorted (descending)
+                                const float hi = fmaxf(topj[i], v);
+                                v = fminf(topj[i], v);
+                                topj[i] = hi;
+                            }
+                            if (WARM && warm_mode) {  // warm-up: only the j best matter; the filter is the j-th best so far
+                                float tj = topj[0];
+#pragma unroll
+                                for (int i = 1; i < 8; ++i) tj = (i < p.share_j) ? topj[i] : tj;
+                                thr = tj;
                             }
                         }
                     }
