@@ -38,7 +38,10 @@ namespace {
 constexpr int BM25_BLOCK_DOCS = SRAG_BM25_WARPS == 4 ? 8192 : 16384;  // fp32 accumulators per CTA
 // Index granularity: block_ptr holds one offset per (term, BM25_SUB_DOCS documents). A tile of bm25_items_kernel is
 // BM25_SUBS consecutive sub-blocks; bm25_sub_kernel gives one sub-block to one warp.
-constexpr int BM25_SUB_DOCS = 2048;
+#ifndef SRAG_BM25_SUB_DOCS
+#define SRAG_BM25_SUB_DOCS 2048
+#endif
+constexpr int BM25_SUB_DOCS = SRAG_BM25_SUB_DOCS;   // (a build-time knob for A/B runs: the index layout follows it)
 // Slices of the searched layout start on, and are padded to, whole GROUPS of BM25_GROUP postings (16 bytes of 16-bit
 // offsets, 32 bytes of impacts: the unit of a bulk copy); slice_ptr counts groups.
 constexpr int BM25_GROUP = 8;

@@ -236,3 +236,38 @@ def test_shared_bound_ties_at_the_boundary_and_skewed_lists(b, k):
     assert i[0].tolist() == spread[:k].tolist() and i[b - 1].tolist() == spread[:k].tolist()
     assert set(i[1].tolist()) <= set(range(70_000, 70_000 + 2 * k))
     assert set(i[2].tolist()) == set(range(100_000, 100_000 + k))
+
+
+@pytest.mark.parametrize("env", [
+    {"SRAG_TOPK_RQ": "1"},                                   # resident-query plan (queries parked in TMEM + shared memory)
+    {"SRAG_TOPK_EPI_WARPS": "8"},                            # two column slices per unit: twice the lists per query
+    {"SRAG_TOPK_RQ": "1", "SRAG_TOPK_EPI_WARPS": "8"},
+    {"SRAG_TOPK_PRESCAN": "0"},                              # no tile-0 prescan: the bound appears after the first tiles
+    {"SRAG_TOPK_SHARE": "0"},                                # every list on its own k-th best
+    {"SRAG_TOPK_SHARE": "2", "SRAG_TOPK_SHARE_PERIOD": "1"}, # sharing wherever possible, bound re-read on every tile
+    {"SRAG_TOPK_WARM": "4"},                                 # warm-up tiles (k >= 32 instantiation) on top of the prescan
+    {"SRAG_TOPK_WINDOW": "0"},                               # no L2 pacing
+], ids=lambda e: ",".join(f"{k[10:]}={v}" for k, v in e.items()))
+def test_selectable_plans_and_knobs_keep_parity(env):
+    """Every plan / knob that DESIGN.md calls selectable returns the same exact top-k: both unit shapes, top-10 and
+    top-100, ties and tombstones included (the knobs are read per call, so they can be set in-process)."""
+    rng = np.random.default_rng(77)
+    n, d = 30_000, 128
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    C[15_000:15_040] = C[5:45]                       # exact duplicates: lower row first
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        for b, k in [(300, 10), (1024, 100), (64, 100), (9, 1)]:
+            Q = rng.standard_normal((b, d)).astype(np.float32)
+            Q[:5] = C[5:10] + 0.01 * Q[:5]
+            s, i = _check(C, Q, k, deleted=[7, 15_002])      # row 7 and its copy: query 2's two exact matches are gone
+            if k >= 2:
+                assert i[0, 0] == 5 and i[0, 1] == 15_000 and i[1, 0] == 6 and i[1, 1] == 15_001
+                assert 7 not in i[2] and 15_002 not in i[2]
+    finally:
+        for k_, v in old.items():
+            if v is None:
+                os.environ.pop(k_, None)
+            else:
+                os.environ[k_] = v
