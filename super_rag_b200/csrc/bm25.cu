@@ -1632,6 +1632,11 @@ static int bm25_search_impl(const uint32_t* block_ptr, const uint16_t* post_doc,
         if (!rc) rc = srag_func_smem_optin(reinterpret_cast<const void*>(&bm25_sub_kernel<true, true>), (int)sizeof(SubSmem));
         if (!rc) rc = srag_current_device_props(&sm_count, nullptr, nullptr);
         if (rc) return rc;
+        // SRAG_BM25_SMS: scan on fewer SMs (see SRAG_TOPK_SMS)
+        if (const char* e = getenv("SRAG_BM25_SMS")) {
+            const int lim = atoi(e);
+            if (lim >= 1 && lim < sm_count) sm_count = lim;
+        }
     }
     uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
     uint64_t* partial = reinterpret_cast<uint64_t*>(ws);

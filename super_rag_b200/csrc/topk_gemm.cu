@@ -952,6 +952,12 @@ int device_sm_count(int* sms) {
         srag_set_error("device compute capability %d.x is not sm_100", major);
         return SRAG_E_UNSUPPORTED;
     }
+    // SRAG_TOPK_SMS: scan on fewer SMs (an even number), leaving the rest to a kernel on another stream (§6b: K1 and K2
+    // of the hybrid pipeline side by side). Read per call; sizes the plan AND the workspace, so set it before both.
+    if (const char* e = getenv("SRAG_TOPK_SMS")) {
+        const int lim = atoi(e) & ~1;
+        if (lim >= 2 && lim < *sms) *sms = lim;
+    }
     return SRAG_OK;
 }
 
