@@ -243,6 +243,34 @@ class ShardedVectorIndex:
         g.replay()
         return out_s, out_i
 
+    def submit_batch(self, queries: torch.Tensor, k: int, out_scores: Optional[torch.Tensor] = None,
+                     out_ids: Optional[torch.Tensor] = None) -> PendingSearch:
+        """`search_batch` without waiting: the host-to-device copy of the queries goes to a copy stream of the index (so
+        it overlaps the scan of the batch submitted before), the scan, exchange and merge to the current stream, and the
+        results are copied into `out_scores` / `out_ids` (pinned host tensors [B, k] fp32 / int64) when given. A caller
+        that keeps two batches in flight — submit i + 1, then wait for i — never leaves the GPU idle between batches;
+        every batch still pays its own copies."""
+        dev = self.rows.device
+        cur = torch.cuda.current_stream(dev)
+        if queries.device != dev:
+            if getattr(self, "_copy_stream", None) is None:
+                self._copy_stream = torch.cuda.Stream(dev)
+            with torch.cuda.stream(self._copy_stream):
+                q = queries.to(dev, non_blocking=True)
+            q.record_stream(cur)
+            cur.wait_stream(self._copy_stream)
+        else:
+            q = queries
+        s, i = self.search_batch(q, k)
+        if out_scores is not None:
+            out_scores.copy_(s, non_blocking=True)
+            out_ids.copy_(i, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record(cur)
+        if out_scores is not None:
+            return PendingSearch(out_scores, out_ids, done, keep=(s, i, q))
+        return PendingSearch(s, i, done, keep=(q,))
+
     def search_batch(self, queries: torch.Tensor, k: int):
         """Public API: fp32/bf16 queries on host (pinned) or device -> global top-k on this rank's device."""
         q = queries.to(self.rows.device, non_blocking=True)
@@ -254,6 +282,23 @@ class ShardedVectorIndex:
         else:
             qb, qs = self.ops.ingest_rows(q.contiguous(), self.metric)
         return self.search_device(qb, qs, k)
+
+
+class PendingSearch:
+    """A search whose kernels and copies have been enqueued (`ShardedVectorIndex.submit_batch`)."""
+
+    def __init__(self, scores, ids, done: "torch.cuda.Event", keep=()):
+        self.scores, self.ids, self._done, self._keep = scores, ids, done, keep
+
+    def ready(self) -> bool:
+        return self._done.query()
+
+    def wait(self):
+        """Block the host until the results are in `scores` / `ids` (the host buffers given to submit_batch, else device
+        tensors) and return them."""
+        self._done.synchronize()
+        self._keep = ()
+        return self.scores, self.ids
 
 
 class ShardedBm25Index:

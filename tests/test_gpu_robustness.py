@@ -162,3 +162,38 @@ def test_sharded_paths_over_nccl(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "PARITY OK" in r.stdout, r.stdout[-3000:]
+
+
+def test_submit_batch_keeps_two_batches_in_flight():
+    """submit_batch = search_batch without waiting: host queries go through the index's copy stream, results land in the
+    caller's pinned buffers; with two batches in flight every batch gets ITS answer (distinct queries per batch)."""
+    import torch
+    from super_rag_b200 import ops
+    from super_rag_b200.sharded import ShardedVectorIndex
+    rng = np.random.default_rng(21)
+    n, d, b, k = 50_000, 256, 200, 10
+    C = rng.standard_normal((n, d)).astype(np.float32)
+    cb, cs = ops.ingest_rows(torch.from_numpy(C).cuda(), "cosine")
+    index = ShardedVectorIndex(cb, cs, id_base=1000)
+    batches = []
+    for t in range(5):
+        Q = rng.standard_normal((b, d)).astype(np.float32)
+        Q[:50] = C[rng.integers(0, n, 50)] + 0.05 * Q[:50]
+        batches.append(torch.from_numpy(Q).pin_memory())
+    want = [tuple(x.cpu() for x in index.search_batch(q, k)) for q in batches]
+    outs = [(torch.empty(b, k).pin_memory(), torch.empty(b, k, dtype=torch.int64).pin_memory()) for _ in range(2)]
+    pend, got = None, []
+    for t, q in enumerate(batches):
+        nxt = index.submit_batch(q, k, *outs[t & 1])
+        if pend is not None:
+            s, i = pend.wait()
+            got.append((s.clone(), i.clone()))
+        pend = nxt
+    s, i = pend.wait()
+    got.append((s.clone(), i.clone()))
+    for t in range(5):
+        assert torch.equal(got[t][1], want[t][1]) and torch.equal(got[t][0], want[t][0]), t
+    # device queries, no host buffers: the results stay on the device
+    p = index.submit_batch(batches[0].cuda(), k)
+    s, i = p.wait()
+    assert s.is_cuda and torch.equal(i.cpu(), want[0][1]) and p.ready()
