@@ -493,6 +493,14 @@ def run_ours(args):
         main_ms, fin_ms, n_prof = ops.prof_read()
         ops.prof_enable(False)
 
+    # the dominant kernel's time on every rank (the step waits for the slowest at the exchange)
+    k1_per_rank = [main_ms / max(1, n_prof)]
+    if world > 1:
+        t = torch.tensor([main_ms / max(1, n_prof)], dtype=torch.float64, device=dev)
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        k1_per_rank = [float(x.item()) for x in allt]
+
     # sanity: planted queries must retrieve their source row first (cheap, no oracle)
     ok = True
     if planted is not None:
@@ -550,6 +558,7 @@ def run_ours(args):
         roof["kernel"] = "topk_gemm_kernel"
         roof["kernel_ms"] = t_main * 1e3
         roof["finalize_ms"] = fin_ms / max(1, n_prof)
+        roof["kernel_ms_per_rank"] = k1_per_rank
         roof["algorithmic_flop_per_launch"] = flops
         roof["algorithmic_bytes_per_launch"] = byts
         roof["traffic"] = None
