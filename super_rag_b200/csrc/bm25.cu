@@ -825,6 +825,9 @@ struct SubSmem {
 __device__ __forceinline__ void cp_async_8(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
+// (.cg = L1 bypass. ncu counts 6.7 shared-memory wavefronts per LDGSTS.E.BYPASS.128 against 2.6 for the LDS.128 that reads
+// the same bytes back — 27 % of the kernel's shared-memory wavefronts; the .ca form through L1 has the ideal count but
+// thrashes the 29 KB of L1 left beside 222 KB of shared memory: C3 9.50 -> 10.01 ms, stop-word queries 36.8 -> 40.7 ms.)
 __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ptx::smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
