@@ -262,14 +262,27 @@ class ShardedVectorIndex:
         else:
             q = queries
         s, i = self.search_batch(q, k)
-        if out_scores is not None:
+        done = torch.cuda.Event()
+        if out_scores is None:
+            done.record(cur)
+            return PendingSearch(s, i, done, keep=(q,))
+        if self.use_graph and self._graphs:
+            # the results are the captured graph's own buffers, rewritten by the next replay: copy them out in stream order
             out_scores.copy_(s, non_blocking=True)
             out_ids.copy_(i, non_blocking=True)
-        done = torch.cuda.Event()
-        done.record(cur)
-        if out_scores is not None:
-            return PendingSearch(out_scores, out_ids, done, keep=(s, i, q))
-        return PendingSearch(s, i, done, keep=(q,))
+            done.record(cur)
+        else:
+            # copy-back on its own stream: the next batch's scan does not queue behind two small device-to-host copies
+            if getattr(self, "_d2h_stream", None) is None:
+                self._d2h_stream = torch.cuda.Stream(dev)
+            self._d2h_stream.wait_stream(cur)
+            with torch.cuda.stream(self._d2h_stream):
+                out_scores.copy_(s, non_blocking=True)
+                out_ids.copy_(i, non_blocking=True)
+                done.record(self._d2h_stream)
+            s.record_stream(self._d2h_stream)
+            i.record_stream(self._d2h_stream)
+        return PendingSearch(out_scores, out_ids, done, keep=(s, i, q))
 
     def search_batch(self, queries: torch.Tensor, k: int):
         """Public API: fp32/bf16 queries on host (pinned) or device -> global top-k on this rank's device."""
