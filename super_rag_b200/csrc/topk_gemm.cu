@@ -476,7 +476,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (n_iter > 0) load_scales(tile_of(0), nxt);
 
         // share_need-th largest published value of this query's lists (orderable bits; <= 0x00800001 = not there yet)
-        // and how many lists have published at all
+        // and how many lists have REPORTED at all (a value, or the mark 1 = "scanned, nothing to publish yet")
         auto shared_bound = [&](int& n_pub) -> uint32_t {
             uint32_t best[16];
 #pragma unroll
@@ -491,7 +491,7 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     uint32_t v = vv[u];
-                    cnt += v > 0x00800001u;
+                    cnt += v != 0u;   // reported: a real value, or the "nothing yet" mark 1
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {  // keep the 16 largest sorted (descending)
                         const uint32_t hi = max(best[i], v);
@@ -516,7 +516,17 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     *reinterpret_cast<volatile uint32_t*>(p.gthr + (size_t)my_list * p.n_queries + qx) = o;
                     published = o;
                 }
+            } else if (published == 0u) {
+                // fewer than j eligible rows so far (deleted rows, a selective metadata filter): say so, or everyone who
+                // waits for all lists after the prescan would wait out the whole bound on every search
+                *reinterpret_cast<volatile uint32_t*>(p.gthr + (size_t)my_list * p.n_queries + qx) = 1u;
+                published = 1u;
             }
+        };
+        auto now_ns = [&]() -> uint64_t {
+            uint64_t t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            return t;
         };
 
         // (Tried and dropped: the push path out of line, once per kernel — spill the chunk's 32 scores to local memory when
@@ -586,11 +596,12 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             if (valid_q) {
                 publish();
                 const int lists_with_rows = (num_c_tiles < p.num_slabs ? num_c_tiles : p.num_slabs) * H;
-                uint32_t spins = 512u, b;
+                const uint64_t t_end = now_ns() + 40000u;   // <= 40 us: the lists' units start together, tile 0 takes ~10
+                uint32_t b;
                 for (;;) {
                     int n_pub;
                     b = shared_bound(n_pub);
-                    if (n_pub >= lists_with_rows || --spins == 0u) break;
+                    if (n_pub >= lists_with_rows || now_ns() > t_end) break;
                     __nanosleep(64);
                 }
                 if (b > 0x00800001u) {
@@ -637,13 +648,14 @@ topk_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             if (p.share_j > 0 && valid_q && !warm_mode && (it - warm < p.share_early || (it - warm) % p.share_period == 0)) {
                 // right after a warm-up pass: wait (bounded — a hint, never a correctness condition) until every list of
                 // this query has published
-                uint32_t spins = (warm > 0 && it == warm) ? 2048u : 1u;
+                const bool after_warm = warm > 0 && it == warm;
+                const uint64_t t_end = after_warm ? now_ns() + 100000u : 0u;
                 const int lists_with_rows = (num_c_tiles < p.num_slabs ? num_c_tiles : p.num_slabs) * H;
                 uint32_t b;
                 for (;;) {
                     int n_pub;
                     b = shared_bound(n_pub);
-                    if (n_pub >= lists_with_rows || --spins == 0u) break;
+                    if (!after_warm || n_pub >= lists_with_rows || now_ns() > t_end) break;
                     __nanosleep(128);
                 }
                 if (b > 0x00800001u) {  // share_need lists have published something above -inf
